@@ -1,0 +1,337 @@
+// C ABI of libfdb200.so: context, error reporting, and the host-buffer pipelines around K1.
+// Declarations and reference citations live in include/fdb200.h.
+
+#include <stdarg.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <new>
+
+#include "fdb_internal.cuh"
+
+// ---------------------------------------------------------------- errors
+static thread_local char g_err[512] = "";
+
+void fdb_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char* fdb_last_error(void) { return g_err; }
+extern "C" int fdb_version(void) { return FDB_VERSION_NUM; }
+
+// ---------------------------------------------------------------- context
+namespace {
+
+constexpr int64_t kSmallRows = 16384;            // serving-size batches go through pinned staging
+constexpr int64_t kDefaultChunkRows = 1 << 20;   // rows per pipeline chunk for large host batches
+constexpr int kScratchSets = FDB_PIPE_SLOTS + 1; // one per pipeline slot + one for _dev callers
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+        if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+size_t elem_size(int dtype) { return dtype == FDB_F64 ? 8 : 4; }
+
+void free_pipeline(fdb_ctx* ctx) {
+    for (auto& s : ctx->slot) {
+        cudaFree(s.d_in); cudaFree(s.d_out); cudaFree(s.d_p); cudaFree(s.d_z); cudaFree(s.d_cls);
+        s.d_in = s.d_out = s.d_p = s.d_z = nullptr;
+        s.d_cls = nullptr;
+    }
+    ctx->chunk_rows = 0;
+    ctx->chunk_elem = 0;
+}
+
+int64_t chunk_rows_cap() {
+    const char* env = getenv("FDB_CHUNK_ROWS");
+    if (env) {
+        long long v = atoll(env);
+        if (v >= 4) return (int64_t)(v & ~3LL);
+    }
+    return kDefaultChunkRows;
+}
+
+// Device chunk buffers for the host pipeline, grown on demand (never shrunk).
+int ensure_pipeline(fdb_ctx* ctx, int64_t rows, size_t elem) {
+    int64_t want = rows < chunk_rows_cap() ? rows : chunk_rows_cap();
+    want = (want + 3) & ~int64_t(3);
+    if (want < 4) want = 4;
+    if (ctx->chunk_rows >= want && ctx->chunk_elem >= elem) return FDB_OK;
+    if (ctx->chunk_rows > want) want = ctx->chunk_rows;
+    if (ctx->chunk_elem > elem) elem = ctx->chunk_elem;
+    if (ctx->chunk_rows > 0) {
+        for (auto& s : ctx->slot) FDB_CUDA(cudaStreamSynchronize(s.stream));
+        free_pipeline(ctx);
+    }
+    for (auto& s : ctx->slot) {
+        FDB_CUDA(cudaMalloc(&s.d_in, (size_t)want * FDB_F * elem));
+        FDB_CUDA(cudaMalloc(&s.d_out, (size_t)want * FDB_F * elem));
+        FDB_CUDA(cudaMalloc(&s.d_p, (size_t)want * elem * 2));
+        FDB_CUDA(cudaMalloc(&s.d_z, (size_t)want * elem));
+        FDB_CUDA(cudaMalloc((void**)&s.d_cls, (size_t)want));
+    }
+    ctx->chunk_rows = want;
+    ctx->chunk_elem = elem;
+    return FDB_OK;
+}
+
+bool is_device_accessible_host(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+}
+
+int check_common(const fdb_ctx* ctx, int dtype, int64_t n_rows, const void* x) {
+    FDB_REQUIRE(ctx != nullptr, FDB_ERR_ARG, "ctx is NULL");
+    FDB_REQUIRE(dtype == FDB_F32 || dtype == FDB_F64, FDB_ERR_ARG, "unknown dtype %d", dtype);
+    FDB_REQUIRE(n_rows >= 0, FDB_ERR_ARG, "n_rows is negative");
+    FDB_REQUIRE(n_rows == 0 || x != nullptr, FDB_ERR_ARG, "x is NULL");
+    return FDB_OK;
+}
+
+// Shared body of the *_host entry points: chunked 3-stream pipeline, or the pinned-staging
+// fast path for serving-size batches.
+int run_host(fdb_ctx* ctx, int dtype, int64_t n, const void* x, const LinearParams& prm, bool divide,
+             void* proba, int proba_cols, void* logit, void* phi, uint8_t* cls, double* abs_sum) {
+    DeviceGuard guard(ctx->device);
+    FDB_REQUIRE(guard.ok, FDB_ERR_CUDA, "cannot select device %d", ctx->device);
+    const size_t es = elem_size(dtype);
+    if (abs_sum) memset(abs_sum, 0, 32 * sizeof(double));
+    if (n == 0) return FDB_OK;
+    int rc = ensure_pipeline(ctx, n, es);
+    if (rc != FDB_OK) return rc;
+
+    const char* xs = static_cast<const char*>(x);
+    char* ph = static_cast<char*>(phi);
+    char* pp = static_cast<char*>(proba);
+    char* pz = static_cast<char*>(logit);
+    const size_t row_b = FDB_F * es;
+
+    if (n <= kSmallRows) {
+        // serving path: one stream, everything through the context's pinned staging buffer
+        fdb_pipe_slot& s = ctx->slot[0];
+        char* st = static_cast<char*>(ctx->h_stage);
+        const bool x_pinned = is_device_accessible_host(x);
+        const void* src = x;
+        if (!x_pinned) { memcpy(st, x, (size_t)n * row_b); src = st; }
+        FDB_CUDA(cudaMemcpyAsync(s.d_in, src, (size_t)n * row_b, cudaMemcpyHostToDevice, s.stream));
+        rc = fdb_launch_linear_pass(ctx, s.stream, dtype, n, s.d_in, prm, divide, proba ? s.d_p : nullptr, proba_cols,
+                                    logit ? s.d_z : nullptr, phi ? s.d_out : nullptr, cls ? s.d_cls : nullptr,
+                                    abs_sum ? ctx->d_abs_sum : nullptr, ctx->d_partials, ctx->d_ticket);
+        if (rc != FDB_OK) return rc;
+        // outputs land in staging (offsets keep 16-byte alignment), then one memcpy each
+        char* o_phi = st + (size_t)kSmallRows * row_b;
+        char* o_p = o_phi + (size_t)kSmallRows * row_b;
+        char* o_z = o_p + (size_t)kSmallRows * es * 2;
+        char* o_c = o_z + (size_t)kSmallRows * es;
+        char* o_a = o_c + (size_t)kSmallRows;
+        if (phi) FDB_CUDA(cudaMemcpyAsync(o_phi, s.d_out, (size_t)n * row_b, cudaMemcpyDeviceToHost, s.stream));
+        if (proba) FDB_CUDA(cudaMemcpyAsync(o_p, s.d_p, (size_t)n * es * proba_cols, cudaMemcpyDeviceToHost, s.stream));
+        if (logit) FDB_CUDA(cudaMemcpyAsync(o_z, s.d_z, (size_t)n * es, cudaMemcpyDeviceToHost, s.stream));
+        if (cls) FDB_CUDA(cudaMemcpyAsync(o_c, s.d_cls, (size_t)n, cudaMemcpyDeviceToHost, s.stream));
+        if (abs_sum) FDB_CUDA(cudaMemcpyAsync(o_a, ctx->d_abs_sum, 32 * sizeof(double), cudaMemcpyDeviceToHost, s.stream));
+        FDB_CUDA(cudaStreamSynchronize(s.stream));
+        if (phi) memcpy(ph, o_phi, (size_t)n * row_b);
+        if (proba) memcpy(pp, o_p, (size_t)n * es * proba_cols);
+        if (logit) memcpy(pz, o_z, (size_t)n * es);
+        if (cls) memcpy(cls, o_c, (size_t)n);
+        if (abs_sum) memcpy(abs_sum, o_a, 32 * sizeof(double));
+        return FDB_OK;
+    }
+
+    // bulk path: chunk c runs on slot c % 3; stream order protects each slot's buffers, and the
+    // three streams overlap H2D(c+1), kernel(c) and D2H(c-1).  Pinned caller buffers DMA
+    // directly; pageable ones are staged by the driver (correct, just slower).
+    int64_t chunk = (n + 11) / 12;                      // aim for >= 12 chunks so the three stages overlap
+    if (chunk < 4 * kSmallRows) chunk = 4 * kSmallRows;
+    chunk = (chunk + 3) & ~int64_t(3);
+    if (chunk > ctx->chunk_rows) chunk = ctx->chunk_rows;
+    const int64_t n_chunks = (n + chunk - 1) / chunk;
+    double* h_abs = nullptr;     // per-chunk |phi| sums land in the pinned staging buffer
+    if (abs_sum) {
+        FDB_REQUIRE((size_t)n_chunks * 32 * sizeof(double) <= ctx->h_stage_bytes, FDB_ERR_ARG,
+                    "too many chunks (%lld) for the |phi| summary; raise FDB_CHUNK_ROWS", (long long)n_chunks);
+        h_abs = static_cast<double*>(ctx->h_stage);
+    }
+    for (int64_t c = 0; c < n_chunks; ++c) {
+        fdb_pipe_slot& s = ctx->slot[c % FDB_PIPE_SLOTS];
+        const int set = (int)(c % FDB_PIPE_SLOTS);
+        const int64_t r0 = c * chunk;
+        const int64_t rows = (n - r0) < chunk ? (n - r0) : chunk;
+        cudaError_t e = cudaMemcpyAsync(s.d_in, xs + (size_t)r0 * row_b, (size_t)rows * row_b, cudaMemcpyHostToDevice, s.stream);
+        if (e == cudaSuccess) {
+            rc = fdb_launch_linear_pass(ctx, s.stream, dtype, rows, s.d_in, prm, divide, proba ? s.d_p : nullptr, proba_cols,
+                                        logit ? s.d_z : nullptr, phi ? s.d_out : nullptr, cls ? s.d_cls : nullptr,
+                                        abs_sum ? ctx->d_abs_sum + 32 * (set + 1) : nullptr,
+                                        ctx->d_partials + (size_t)(set + 1) * FDB_MAX_GRID * 32, ctx->d_ticket + set + 1);
+            if (rc != FDB_OK) return rc;
+        }
+        if (e == cudaSuccess && phi) e = cudaMemcpyAsync(ph + (size_t)r0 * row_b, s.d_out, (size_t)rows * row_b, cudaMemcpyDeviceToHost, s.stream);
+        if (e == cudaSuccess && proba) e = cudaMemcpyAsync(pp + (size_t)r0 * es * proba_cols, s.d_p, (size_t)rows * es * proba_cols, cudaMemcpyDeviceToHost, s.stream);
+        if (e == cudaSuccess && logit) e = cudaMemcpyAsync(pz + (size_t)r0 * es, s.d_z, (size_t)rows * es, cudaMemcpyDeviceToHost, s.stream);
+        if (e == cudaSuccess && cls) e = cudaMemcpyAsync(cls + r0, s.d_cls, (size_t)rows, cudaMemcpyDeviceToHost, s.stream);
+        if (e == cudaSuccess && abs_sum) e = cudaMemcpyAsync(h_abs + c * 32, ctx->d_abs_sum + 32 * (set + 1), 32 * sizeof(double), cudaMemcpyDeviceToHost, s.stream);
+        if (e != cudaSuccess) {
+            fdb_set_error("host pipeline copy failed: %s", cudaGetErrorString(e));
+            for (auto& t : ctx->slot) cudaStreamSynchronize(t.stream);
+            return FDB_ERR_CUDA;
+        }
+    }
+    cudaError_t e = cudaSuccess;
+    for (auto& s : ctx->slot) {
+        cudaError_t e2 = cudaStreamSynchronize(s.stream);
+        if (e == cudaSuccess) e = e2;
+    }
+    if (abs_sum && e == cudaSuccess) {
+        for (int64_t c = 0; c < n_chunks; ++c)
+            for (int k = 0; k < 31; ++k) abs_sum[k] += h_abs[c * 32 + k];
+    }
+    FDB_CUDA(e);
+    return FDB_OK;
+}
+
+void fill_params(LinearParams& p, const double* sub, const double* mul, double bias) {
+    for (int k = 0; k < FDB_F; ++k) {
+        p.sub[k] = sub ? sub[k] : 0.0;
+        p.mul[k] = mul[k];
+    }
+    p.bias = bias;
+}
+
+}  // namespace
+
+extern "C" int fdb_ctx_create(int device, fdb_ctx** out) {
+    FDB_REQUIRE(out != nullptr, FDB_ERR_ARG, "out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    FDB_REQUIRE(e == cudaSuccess && count > 0, FDB_ERR_CUDA, "no CUDA device available (%s); libfdb200 has no CPU fallback",
+                e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    FDB_REQUIRE(device >= 0 && device < count, FDB_ERR_ARG, "device %d out of range (0..%d)", device, count - 1);
+    DeviceGuard guard(device);
+    FDB_REQUIRE(guard.ok, FDB_ERR_CUDA, "cannot select device %d", device);
+    fdb_ctx* ctx = new (std::nothrow) fdb_ctx();
+    FDB_REQUIRE(ctx != nullptr, FDB_ERR_NOMEM, "out of host memory");
+    ctx->device = device;
+    int rc = FDB_OK;
+    do {
+        cudaDeviceProp prop;
+        if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) break;
+        ctx->sm_count = prop.multiProcessorCount;
+        if (prop.major < 10) {
+            fdb_set_error("device %d is sm_%d%d; libfdb200 is built for sm_100a (B200) only", device, prop.major, prop.minor);
+            rc = FDB_ERR_CUDA;
+            break;
+        }
+        if ((e = cudaMalloc((void**)&ctx->d_partials, (size_t)kScratchSets * FDB_MAX_GRID * 32 * sizeof(double))) != cudaSuccess) break;
+        if ((e = cudaMalloc((void**)&ctx->d_ticket, kScratchSets * sizeof(unsigned int))) != cudaSuccess) break;
+        if ((e = cudaMemset(ctx->d_ticket, 0, kScratchSets * sizeof(unsigned int))) != cudaSuccess) break;
+        if ((e = cudaMalloc((void**)&ctx->d_abs_sum, kScratchSets * 32 * sizeof(double))) != cudaSuccess) break;
+        for (auto& s : ctx->slot)
+            if ((e = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking)) != cudaSuccess) break;
+        if (e != cudaSuccess) break;
+        ctx->h_stage_bytes = (size_t)kSmallRows * (2 * FDB_F * 8 + 3 * 8 + 1) + 32 * sizeof(double) + 256;
+        if ((e = cudaMallocHost(&ctx->h_stage, ctx->h_stage_bytes)) != cudaSuccess) break;
+    } while (0);
+    if (e != cudaSuccess || rc != FDB_OK) {
+        if (e != cudaSuccess) {
+            fdb_set_error("context creation failed: %s", cudaGetErrorString(e));
+            rc = e == cudaErrorMemoryAllocation ? FDB_ERR_NOMEM : FDB_ERR_CUDA;
+        }
+        fdb_ctx_destroy(ctx);
+        return rc;
+    }
+    *out = ctx;
+    return FDB_OK;
+}
+
+extern "C" int fdb_ctx_destroy(fdb_ctx* ctx) {
+    if (!ctx) return FDB_OK;
+    DeviceGuard guard(ctx->device);
+    cudaDeviceSynchronize();
+    free_pipeline(ctx);
+    for (auto& s : ctx->slot)
+        if (s.stream) cudaStreamDestroy(s.stream);
+    cudaFree(ctx->d_partials);
+    cudaFree(ctx->d_ticket);
+    cudaFree(ctx->d_abs_sum);
+    if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+    delete ctx;
+    return FDB_OK;
+}
+
+extern "C" int fdb_ctx_device(const fdb_ctx* ctx) { return ctx ? ctx->device : -1; }
+extern "C" int fdb_ctx_sm_count(const fdb_ctx* ctx) { return ctx ? ctx->sm_count : 0; }
+
+extern "C" int fdb_pinned_alloc(size_t bytes, void** out) {
+    FDB_REQUIRE(out != nullptr, FDB_ERR_ARG, "out is NULL");
+    FDB_CUDA(cudaMallocHost(out, bytes ? bytes : 1));
+    return FDB_OK;
+}
+
+extern "C" int fdb_pinned_free(void* p) {
+    if (p) FDB_CUDA(cudaFreeHost(p));
+    return FDB_OK;
+}
+
+// ---------------------------------------------------------------- K1 entry points
+extern "C" int fdb_transform_dev(fdb_ctx* ctx, void* stream, int dtype, int64_t n_rows, const void* x,
+                                 const double* mean, const double* scale, void* out) {
+    int rc = check_common(ctx, dtype, n_rows, x);
+    if (rc != FDB_OK) return rc;
+    FDB_REQUIRE(mean && scale, FDB_ERR_ARG, "mean/scale is NULL");
+    FDB_REQUIRE(n_rows == 0 || out != nullptr, FDB_ERR_ARG, "out is NULL");
+    FDB_REQUIRE(fdb_aligned16(x) && fdb_aligned16(out), FDB_ERR_ALIGN, "x and out must be 16-byte aligned");
+    LinearParams p;
+    fill_params(p, mean, scale, 0.0);
+    return fdb_launch_linear_pass(ctx, (cudaStream_t)stream, dtype, n_rows, x, p, true, nullptr, 1, nullptr, out,
+                                  nullptr, nullptr, nullptr, nullptr);
+}
+
+extern "C" int fdb_transform_host(fdb_ctx* ctx, int dtype, int64_t n_rows, const void* x, const double* mean,
+                                  const double* scale, void* out) {
+    int rc = check_common(ctx, dtype, n_rows, x);
+    if (rc != FDB_OK) return rc;
+    FDB_REQUIRE(mean && scale, FDB_ERR_ARG, "mean/scale is NULL");
+    FDB_REQUIRE(n_rows == 0 || out != nullptr, FDB_ERR_ARG, "out is NULL");
+    LinearParams p;
+    fill_params(p, mean, scale, 0.0);
+    return run_host(ctx, dtype, n_rows, x, p, true, nullptr, 1, nullptr, out, nullptr, nullptr);
+}
+
+extern "C" int fdb_linear_pass_dev(fdb_ctx* ctx, void* stream, int dtype, int64_t n_rows, const void* x,
+                                   const double* sub, const double* mul, double bias, void* proba, int proba_cols,
+                                   void* logit, void* phi, uint8_t* cls, double* abs_sum) {
+    int rc = check_common(ctx, dtype, n_rows, x);
+    if (rc != FDB_OK) return rc;
+    FDB_REQUIRE(mul != nullptr, FDB_ERR_ARG, "mul is NULL");
+    FDB_REQUIRE(proba_cols == 1 || proba_cols == 2, FDB_ERR_ARG, "proba_cols must be 1 or 2");
+    FDB_REQUIRE(fdb_aligned16(x) && fdb_aligned16(phi), FDB_ERR_ALIGN, "x and phi must be 16-byte aligned");
+    LinearParams p;
+    fill_params(p, sub, mul, bias);
+    return fdb_launch_linear_pass(ctx, (cudaStream_t)stream, dtype, n_rows, x, p, false, proba, proba_cols, logit, phi, cls,
+                                  abs_sum, ctx->d_partials, ctx->d_ticket);
+}
+
+extern "C" int fdb_linear_pass_host(fdb_ctx* ctx, int dtype, int64_t n_rows, const void* x, const double* sub,
+                                    const double* mul, double bias, void* proba, int proba_cols, void* logit, void* phi,
+                                    uint8_t* cls, double* abs_sum) {
+    int rc = check_common(ctx, dtype, n_rows, x);
+    if (rc != FDB_OK) return rc;
+    FDB_REQUIRE(mul != nullptr, FDB_ERR_ARG, "mul is NULL");
+    FDB_REQUIRE(proba_cols == 1 || proba_cols == 2, FDB_ERR_ARG, "proba_cols must be 1 or 2");
+    LinearParams p;
+    fill_params(p, sub, mul, bias);
+    return run_host(ctx, dtype, n_rows, x, p, false, proba, proba_cols, logit, phi, cls, abs_sum);
+}

@@ -1,0 +1,288 @@
+// K1 - fused linear pass over 30-feature rows (sm_100a).
+//
+// One streaming read of x produces every requested output of the reference's scoring and
+// linear-SHAP calls (see include/fdb200.h, fdb_linear_pass_dev):
+//     phi[r][k] = (x[r][k] - sub[k]) * mul[k]      (or (x - sub) / mul for StandardScaler.transform)
+//     logit[r]  = bias + sum_k phi[r][k];  proba = sigmoid(logit);  cls = logit > 0
+//     abs_sum[k] = sum_r |phi[r][k]|
+//
+// Layout.  A row is 30 elements = 120 B (f32) / 240 B (f64): not a multiple of 16 B per row
+// in f32, so the matrix is read as a flat stream of 16-byte vectors.  A warp iteration moves
+// one 480-byte "group" = 30 vectors (4 f32 rows or 2 f64 rows): each 16-lane half-warp takes
+// 15 consecutive vectors (lane 15 of each half idles), so a half-warp owns exactly 2 f32 rows
+// (60 floats) or 1 f64 row.  The feature index of every register element therefore depends
+// only on the lane, so sub/mul live in registers, phi is pure element-wise on coalesced
+// 16-byte loads/stores, and the row dot products are 4-step xor-shuffle reductions inside
+// the half-warp (f32: the two rows of a half are reduced together by swapping partials in
+// the first step).  The kernel is HBM-bound: 244 B/row (f32, proba+phi) against ~150 flops.
+//
+// |phi| column sums: per-lane accumulators (fixed feature per register), fixed-order block
+// reduction, per-CTA partials in ctx scratch, last-arriving CTA folds them in CTA order ->
+// bitwise deterministic for a given grid.
+
+#include "fdb_internal.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+
+template <typename T> struct Lane;
+template <> struct Lane<float> {
+    using V = float4;
+    static constexpr int EPL = 4;   // elements per lane
+    static constexpr int RPW = 4;   // rows per warp iteration
+};
+template <> struct Lane<double> {
+    using V = double2;
+    static constexpr int EPL = 2;
+    static constexpr int RPW = 2;
+};
+
+template <typename T> struct KParams {
+    T sub[FDB_F];
+    T mul[FDB_F];
+    T bias;
+};
+
+__device__ __forceinline__ void unpack(const float4& v, float (&e)[4]) { e[0] = v.x; e[1] = v.y; e[2] = v.z; e[3] = v.w; }
+__device__ __forceinline__ void unpack(const double2& v, double (&e)[2]) { e[0] = v.x; e[1] = v.y; }
+__device__ __forceinline__ float4 pack(const float (&e)[4]) { return make_float4(e[0], e[1], e[2], e[3]); }
+__device__ __forceinline__ double2 pack(const double (&e)[2]) { return make_double2(e[0], e[1]); }
+
+__device__ __forceinline__ float sigmoidT(float z) { return __frcp_rn(1.0f + __expf(-z)); }
+__device__ __forceinline__ double sigmoidT(double z) { return 1.0 / (1.0 + exp(-z)); }
+
+// proba_cols == 2 writes the sklearn layout [1 - p, p] (SK:linear_model/_base.py:438-440)
+template <typename T>
+__device__ __forceinline__ void emit_row(int64_t row, T z, T* __restrict__ proba, int proba_cols,
+                                         T* __restrict__ logit, uint8_t* __restrict__ cls) {
+    if (logit) logit[row] = z;
+    if (proba) {
+        const T p = sigmoidT(z);
+        if (proba_cols == 2) {
+            if constexpr (sizeof(T) == 4) reinterpret_cast<float2*>(proba)[row] = make_float2(1.0f - p, p);
+            else reinterpret_cast<double2*>(proba)[row] = make_double2(1.0 - p, p);
+        } else {
+            proba[row] = p;
+        }
+    }
+    if (cls) cls[row] = z > T(0) ? 1 : 0;
+}
+
+template <typename T, bool DIVIDE>
+__global__ void __launch_bounds__(kThreads)
+linear_pass_kernel(const T* __restrict__ x, int64_t n_rows, const KParams<T> prm, T* __restrict__ proba,
+                   int proba_cols, T* __restrict__ logit, T* __restrict__ phi, uint8_t* __restrict__ cls,
+                   double* __restrict__ abs_sum, double* __restrict__ partials, unsigned int* __restrict__ ticket) {
+    using V = typename Lane<T>::V;
+    constexpr int EPL = Lane<T>::EPL;
+    constexpr int RPW = Lane<T>::RPW;
+
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int j = lane & 15;
+    const int half = lane >> 4;
+    const bool active = j < 15;
+    const bool want_rows = (proba != nullptr) | (logit != nullptr) | (cls != nullptr);
+    const bool want_abs = abs_sum != nullptr;
+
+    T sub[EPL], mul[EPL];
+#pragma unroll
+    for (int k = 0; k < EPL; ++k) {
+        const int f = (EPL * j + k) % FDB_F;
+        sub[k] = prm.sub[f];
+        mul[k] = prm.mul[f];
+    }
+
+    const int64_t n_groups = n_rows / RPW;
+    const int64_t total_warps = (int64_t)gridDim.x * kWarps;
+    const int64_t warp_id = (int64_t)blockIdx.x * kWarps + warp;
+    const V* __restrict__ xv = reinterpret_cast<const V*>(x);
+    V* __restrict__ pv = reinterpret_cast<V*>(phi);
+    const int lane_vec = half * 15 + j;
+
+    float acc32[EPL];
+    double acc64[EPL];
+#pragma unroll
+    for (int k = 0; k < EPL; ++k) { acc32[k] = 0.f; acc64[k] = 0.0; }
+    int since_flush = 0;
+
+    auto process = [&](const V& v, int64_t g) {
+        T e[EPL];
+        unpack(v, e);
+#pragma unroll
+        for (int k = 0; k < EPL; ++k) {
+            T d = e[k] - sub[k];
+            e[k] = DIVIDE ? d / mul[k] : d * mul[k];
+        }
+        if (phi != nullptr && active) __stcs(pv + g * 30 + lane_vec, pack(e));
+        if (!DIVIDE) {
+            if (want_abs && active) {
+#pragma unroll
+                for (int k = 0; k < EPL; ++k) {
+                    if constexpr (sizeof(T) == 4) acc32[k] += fabsf((float)e[k]);   // flushed to f64 every 32 iterations
+                    else acc64[k] += fabs((double)e[k]);
+                }
+            }
+            if (want_rows) {
+                T keep;
+                if constexpr (EPL == 4) {
+                    // half-warp = 2 rows: lanes 0..6 row A, lane 7 splits, lanes 8..14 row B
+                    const T lo = e[0] + e[1], hi = e[2] + e[3];
+                    T a = (j < 7) ? lo + hi : (j == 7 ? lo : T(0));
+                    T b = (j > 7) ? lo + hi : (j == 7 ? hi : T(0));
+                    if (!active) { a = T(0); b = T(0); }
+                    const bool low = j < 8;
+                    keep = low ? a : b;
+                    const T send = low ? b : a;
+                    keep += __shfl_xor_sync(0xffffffffu, send, 8);
+                } else {
+                    keep = active ? e[0] + e[1] : T(0);
+                    keep += __shfl_xor_sync(0xffffffffu, keep, 8);
+                }
+                keep += __shfl_xor_sync(0xffffffffu, keep, 4);
+                keep += __shfl_xor_sync(0xffffffffu, keep, 2);
+                keep += __shfl_xor_sync(0xffffffffu, keep, 1);
+                if constexpr (EPL == 4) {
+                    if ((j & 7) == 0) emit_row<T>(g * RPW + half * 2 + (j >> 3), keep + prm.bias, proba, proba_cols, logit, cls);
+                } else {
+                    if (j == 0) emit_row<T>(g * RPW + half, keep + prm.bias, proba, proba_cols, logit, cls);
+                }
+            }
+        }
+    };
+
+    const V zero = {};
+    for (int64_t g = warp_id; g < n_groups; g += 2 * total_warps) {
+        const int64_t g1 = g + total_warps;
+        const bool has1 = g1 < n_groups;
+        V v0 = zero, v1 = zero;
+        if (active) {
+            v0 = __ldcs(xv + g * 30 + lane_vec);
+            if (has1) v1 = __ldcs(xv + g1 * 30 + lane_vec);
+        }
+        process(v0, g);
+        if (has1) process(v1, g1);
+        if (want_abs && ++since_flush == 32) {
+#pragma unroll
+            for (int k = 0; k < EPL; ++k) { acc64[k] += (double)acc32[k]; acc32[k] = 0.f; }
+            since_flush = 0;
+        }
+    }
+
+    // tail rows (n_rows % RPW of them): warp 0 of CTA 0, one feature per lane
+    double tail_abs = 0.0;
+    if (blockIdx.x == 0 && warp == 0) {
+        for (int64_t r = n_groups * RPW; r < n_rows; ++r) {
+            T e = T(0);
+            if (lane < FDB_F) {
+                const T d = x[r * FDB_F + lane] - prm.sub[lane];
+                e = DIVIDE ? d / prm.mul[lane] : d * prm.mul[lane];
+                if (phi != nullptr) phi[r * FDB_F + lane] = e;
+                tail_abs += fabs((double)e);
+            }
+            if (!DIVIDE && want_rows) {
+                T s = e;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+                if (lane == 0) emit_row<T>(r, s + prm.bias, proba, proba_cols, logit, cls);
+            }
+        }
+    }
+
+    if constexpr (!DIVIDE) {
+    if (!want_abs) return;
+
+    // ---- |phi| column sums: fixed-order CTA reduction, then last-CTA fold ----------------
+    __shared__ double s_acc[kWarps][32][EPL];
+    __shared__ double s_tail[32];
+    __shared__ bool s_last;
+#pragma unroll
+    for (int k = 0; k < EPL; ++k) s_acc[warp][lane][k] = active ? acc64[k] + (double)acc32[k] : 0.0;
+    if (warp == 0) s_tail[lane] = tail_abs;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        double tot = 0.0;
+        if (threadIdx.x < FDB_F) {
+            const int f = threadIdx.x;
+            for (int w = 0; w < kWarps; ++w) {
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    // flat positions of feature f inside a half-warp's 15 vectors
+                    for (int e = f; e < 15 * EPL; e += FDB_F) tot += s_acc[w][h * 16 + e / EPL][e % EPL];
+                }
+            }
+            tot += s_tail[f];
+        }
+        partials[(size_t)blockIdx.x * 32 + threadIdx.x] = tot;
+        __threadfence();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+    __syncthreads();
+    if (s_last && threadIdx.x < 32) {
+        __threadfence();
+        double tot = 0.0;
+        if (threadIdx.x < FDB_F) {
+            for (unsigned b = 0; b < gridDim.x; ++b) tot += __ldcg(partials + (size_t)b * 32 + threadIdx.x);
+        } else if (threadIdx.x == FDB_F) {
+            tot = (double)n_rows;
+        }
+        abs_sum[threadIdx.x] = tot;
+        if (threadIdx.x == 0) *ticket = 0u;
+    }
+    }  // !DIVIDE
+}
+
+template <typename T>
+int launch_typed(fdb_ctx* ctx, cudaStream_t st, int64_t n_rows, const void* x, const LinearParams& prm,
+                 bool divide, void* proba, int proba_cols, void* logit, void* phi, uint8_t* cls, double* abs_sum,
+                 double* partials, unsigned int* ticket) {
+    KParams<T> kp;
+    for (int k = 0; k < FDB_F; ++k) {
+        kp.sub[k] = (T)prm.sub[k];
+        kp.mul[k] = (T)prm.mul[k];
+    }
+    kp.bias = (T)prm.bias;
+    const int64_t n_groups = n_rows / Lane<T>::RPW;
+    int64_t want = (n_groups + 2 * kWarps - 1) / (2 * kWarps);   // 2 groups per warp minimum
+    if (want < 1) want = 1;
+    // persistent grid-stride launch: exactly the resident CTA count (multiple of the SM count)
+    static int per_sm[2] = {0, 0};
+    int& occ = per_sm[divide ? 1 : 0];
+    if (occ == 0) {
+        int v = 0;
+        cudaError_t e = divide
+            ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, linear_pass_kernel<T, true>, kThreads, 0)
+            : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, linear_pass_kernel<T, false>, kThreads, 0);
+        FDB_CUDA(e);
+        occ = v > 0 ? v : 1;
+    }
+    int64_t cap = (int64_t)ctx->sm_count * occ;
+    if (cap > FDB_MAX_GRID) cap = FDB_MAX_GRID;
+    const int grid = (int)(want < cap ? want : cap);
+    if (divide) {
+        linear_pass_kernel<T, true><<<grid, kThreads, 0, st>>>(
+            (const T*)x, n_rows, kp, nullptr, 1, nullptr, (T*)phi, nullptr, nullptr, nullptr, nullptr);
+    } else {
+        linear_pass_kernel<T, false><<<grid, kThreads, 0, st>>>(
+            (const T*)x, n_rows, kp, (T*)proba, proba_cols, (T*)logit, (T*)phi, cls, abs_sum, partials, ticket);
+    }
+    FDB_CUDA(cudaGetLastError());
+    return FDB_OK;
+}
+
+}  // namespace
+
+int fdb_launch_linear_pass(fdb_ctx* ctx, cudaStream_t st, int dtype, int64_t n_rows, const void* x,
+                           const LinearParams& prm, bool divide, void* proba, int proba_cols, void* logit,
+                           void* phi, uint8_t* cls, double* abs_sum, double* partials, unsigned int* ticket) {
+    if (n_rows == 0) {
+        if (abs_sum) FDB_CUDA(cudaMemsetAsync(abs_sum, 0, 32 * sizeof(double), st));
+        return FDB_OK;
+    }
+    if (dtype == FDB_F32)
+        return launch_typed<float>(ctx, st, n_rows, x, prm, divide, proba, proba_cols, logit, phi, cls, abs_sum, partials, ticket);
+    return launch_typed<double>(ctx, st, n_rows, x, prm, divide, proba, proba_cols, logit, phi, cls, abs_sum, partials, ticket);
+}

@@ -1,0 +1,108 @@
+/*
+ * fdb200.h - C ABI of libfdb200.so, the B200 (sm_100a) implementation of the
+ * fraud-detection batch scoring + SHAP hot path.
+ *
+ * The reference (wtfashwin/fraud-detection) is pure Python: its "plugin interface" for
+ * this path is duck-typed sklearn/shap objects held in module globals
+ * (SCALER.transform, MODEL.predict/predict_proba, EXPL.shap_values).  The Python
+ * classes in fraud_detection_b200/ mirror that surface and bind the entry points below
+ * through ctypes; each declaration cites the reference call it replaces.  Paths are
+ * relative to the reference repository; "SK:" is scikit-learn's source tree.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / C++ types cross this boundary;
+ *   - every function returns FDB_OK (0) or a negative FDB_ERR_* code and never aborts;
+ *     fdb_last_error() gives the message for the calling thread;
+ *   - "_dev" entry points take DEVICE pointers and a cudaStream_t passed as void*
+ *     (NULL = legacy default stream); they enqueue work and return without synchronising;
+ *   - "_host" entry points take HOST pointers (pinned or pageable), run the
+ *     H2D -> kernel -> D2H pipeline themselves and return when the outputs are complete;
+ *   - matrices are row-major, 30 features per row (Time, V1..V28, Amount);
+ *   - dtype: FDB_F32 or FDB_F64 selects the element type of every x / out / phi / proba
+ *     buffer of that call (parameters are always passed as host doubles).
+ *   - there is no CPU fallback: without a CUDA device every compute call fails with
+ *     FDB_ERR_CUDA.
+ */
+#ifndef FDB200_H
+#define FDB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FDB_N_FEATURES 30
+
+enum { FDB_F32 = 0, FDB_F64 = 1 };
+
+enum {
+    FDB_OK = 0,
+    FDB_ERR_ARG = -1,     /* bad argument (null, negative size, unknown dtype) -> ValueError */
+    FDB_ERR_ALIGN = -2,   /* device buffer not 16-byte aligned                  -> ValueError */
+    FDB_ERR_CUDA = -3,    /* CUDA runtime error / no device                     -> RuntimeError */
+    FDB_ERR_NOMEM = -4,   /* allocation failed                                  -> MemoryError */
+    FDB_ERR_STATE = -5    /* plan/context used in the wrong state               -> RuntimeError */
+};
+
+typedef struct fdb_ctx fdb_ctx;   /* one per (process, device); owns streams and workspaces */
+
+int fdb_version(void);
+const char* fdb_last_error(void);
+
+/* Context.  Create lazily, after fork (api/app.py runs under gunicorn prefork workers and
+ * Celery prefork, SURVEY 8(b) "Threading / processes"). */
+int fdb_ctx_create(int device, fdb_ctx** out);
+int fdb_ctx_destroy(fdb_ctx* ctx);
+int fdb_ctx_device(const fdb_ctx* ctx);
+int fdb_ctx_sm_count(const fdb_ctx* ctx);
+
+/* Pinned host memory helpers for callers that want DMA-able buffers. */
+int fdb_pinned_alloc(size_t bytes, void** out);
+int fdb_pinned_free(void* p);
+
+/* ---------------------------------------------------------------------------------
+ * K1a  StandardScaler.transform:  out = (x - mean) / scale
+ * Replaces SCALER.transform(X) at api/app.py:194, explain_model.py:19,
+ * predict_single.py:25, deploy.py:33 (body SK:preprocessing/_data.py:1092-1135).
+ * ------------------------------------------------------------------------------- */
+int fdb_transform_dev(fdb_ctx* ctx, void* stream, int dtype, int64_t n_rows, const void* x,
+                      const double* mean, const double* scale, void* out);
+int fdb_transform_host(fdb_ctx* ctx, int dtype, int64_t n_rows, const void* x,
+                       const double* mean, const double* scale, void* out);
+
+/* ---------------------------------------------------------------------------------
+ * K1b  fused linear pass over rows (one read of x, every requested output in one pass):
+ *        phi[r][k] = (x[r][k] - sub[k]) * mul[k]                 exact linear SHAP
+ *        logit[r]  = bias + sum_k phi[r][k]
+ *        proba[r]  = 1 / (1 + exp(-logit[r]))
+ *        cls[r]    = logit[r] > 0
+ *        abs_sum[k] = sum_r |phi[r][k]|  (k < 30), abs_sum[30] = n_rows, abs_sum[31] = 0
+ * Any of phi / logit / proba / cls / abs_sum may be NULL (not written).
+ * With sub = 0, mul = coef_, bias = intercept_ this is
+ *   decision_function / predict_proba / predict     (api/app.py:209,223; xai_tasks.py:97;
+ *   evaluate_model.py:26-27; SK:linear_model/_base.py:366-440);
+ * with sub = background mean, mul = coef_ it is LinearExplainer.shap_values
+ *   (explain_model.py:27, api/worker.py:75) and coef*x of xai_tasks.py:106-107;
+ * with the scaler folded in (sub = mean_ + scale_*mu_bg, mul = coef_/scale_,
+ * bias = expected_value) it scores and explains RAW rows in one pass.
+ * abs_sum is the device-side input of the global mean|SHAP| summary
+ * (explain_model.py:39) that ranks all-reduce across GPUs.
+ * proba_cols = 1 writes proba[r] = p; proba_cols = 2 writes the predict_proba layout
+ * proba[r][0] = 1 - p, proba[r][1] = p.  cls is uint8; abs_sum is 32 doubles on the device
+ * (dev) / host (host).  A _dev call that asks for abs_sum uses per-context scratch: at most
+ * one such launch per context may be in flight.  A non-finite abs_sum[k] means column k of
+ * the input held a NaN or infinity.
+ * ------------------------------------------------------------------------------- */
+int fdb_linear_pass_dev(fdb_ctx* ctx, void* stream, int dtype, int64_t n_rows, const void* x,
+                        const double* sub, const double* mul, double bias,
+                        void* proba, int proba_cols, void* logit, void* phi, uint8_t* cls, double* abs_sum);
+int fdb_linear_pass_host(fdb_ctx* ctx, int dtype, int64_t n_rows, const void* x,
+                         const double* sub, const double* mul, double bias,
+                         void* proba, int proba_cols, void* logit, void* phi, uint8_t* cls, double* abs_sum);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FDB200_H */
