@@ -4,7 +4,7 @@ rebuilt for NVIDIA B200 (sm_100a).
 Host side mirrors the reference's duck-typed call surface (``transform``, ``predict``,
 ``predict_proba``, ``explainer.shap_values``); underneath is ``libfdb200.so`` - a C-ABI
 library of hand-written CUDA kernels, bound with ctypes.  Importing this package requires
-the built library (``python -m fraud_detection_b200.build``); there is no CPU fallback.
+the built library (``python fraud_detection_b200/build.py``); there is no CPU fallback.
 
 ``device`` (torch tensor in / tensor out) and ``distributed`` are imported on demand so the
 serving classes do not pull torch into a gunicorn/Celery worker.

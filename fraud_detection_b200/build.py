@@ -1,6 +1,6 @@
 """Build libfdb200.so in-tree with nvcc for sm_100a (no torch linkage, C ABI only).
 
-    python -m fraud_detection_b200.build [--force] [--verbose]
+    python fraud_detection_b200/build.py [--force] [--verbose]
 
 The shared object lands next to this file so it travels with the repo snapshot to the GPU
 box; it is git-ignored.  nvcc cross-compiles without a GPU.
@@ -37,13 +37,25 @@ def sources() -> list[str]:
     return sorted(glob.glob(os.path.join(CSRC, "*.cu")))
 
 
+def _source_hash() -> str:
+    """Content hash of everything the library is built from (mtimes do not survive a snapshot copy)."""
+    import hashlib
+    h = hashlib.sha256(" ".join(NVCC_FLAGS).encode())
+    deps = sources() + sorted(glob.glob(os.path.join(CSRC, "*.cuh"))) + \
+        sorted(glob.glob(os.path.join(os.path.dirname(PKG_DIR), "include", "*.h")))
+    for d in deps:
+        h.update(os.path.basename(d).encode())
+        with open(d, "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()
+
+
 def _stale() -> bool:
-    if not os.path.exists(LIB_PATH):
+    stamp = os.path.join(BUILD_DIR, "src.sha256")
+    if not os.path.exists(LIB_PATH) or not os.path.exists(stamp):
         return True
-    t = os.path.getmtime(LIB_PATH)
-    deps = sources() + glob.glob(os.path.join(CSRC, "*.cuh")) + \
-        glob.glob(os.path.join(os.path.dirname(PKG_DIR), "include", "*.h")) + [os.path.abspath(__file__)]
-    return any(os.path.getmtime(d) > t for d in deps)
+    with open(stamp, "r", encoding="utf-8") as fh:
+        return fh.read().strip() != _source_hash()
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
@@ -71,6 +83,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise RuntimeError(f"link failed:\n{r.stdout}")
     with open(os.path.join(BUILD_DIR, "build.log"), "w", encoding="utf-8") as fh:
         fh.write("\n".join(log))
+    with open(os.path.join(BUILD_DIR, "src.sha256"), "w", encoding="utf-8") as fh:
+        fh.write(_source_hash())
     if verbose:
         print("\n".join(log))
     return LIB_PATH
