@@ -29,7 +29,7 @@ def _load() -> C.CDLL:
     if not os.path.exists(LIB_PATH):
         raise ImportError(
             f"{LIB_PATH} is missing: build the CUDA extension first "
-            "(python -m fraud_detection_b200.build). There is no CPU fallback.")
+            "(python fraud_detection_b200/build.py). There is no CPU fallback.")
     return C.CDLL(LIB_PATH, mode=C.RTLD_LOCAL)
 
 
@@ -50,6 +50,7 @@ _SIGS = {
     "fdb_transform_host": (_i, [_vp, _i, _i64, _vp, _dp, _dp, _vp]),
     "fdb_linear_pass_dev": (_i, [_vp, _vp, _i, _i64, _vp, _dp, _dp, C.c_double, _vp, _i, _vp, _vp, _vp, _vp]),
     "fdb_linear_pass_host": (_i, [_vp, _i, _i64, _vp, _dp, _dp, C.c_double, _vp, _i, _vp, _vp, _vp, _vp]),
+    "fdb_linear_pass_noalloc": (_i, [_vp, _i, _i64, _vp, _dp, _dp, C.c_double, _vp, _i, _vp, _vp, _vp, _vp]),
 }
 
 

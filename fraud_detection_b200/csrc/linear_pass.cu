@@ -286,3 +286,138 @@ int fdb_launch_linear_pass(fdb_ctx* ctx, cudaStream_t st, int dtype, int64_t n_r
         return launch_typed<float>(ctx, st, n_rows, x, prm, divide, proba, proba_cols, logit, phi, cls, abs_sum, partials, ticket);
     return launch_typed<double>(ctx, st, n_rows, x, prm, divide, proba, proba_cols, logit, phi, cls, abs_sum, partials, ticket);
 }
+
+// =======================================================================================
+// fdb_linear_pass_noalloc - the fused linear pass for callers that must not allocate.
+//
+// Who this is for.  fdb_linear_pass_dev needs an fdb_ctx, and creating a context calls
+// cudaMalloc for the |phi| column-sum scratch.  Some users of this library cannot do that:
+//   * a scoring thread inside a serving process whose device memory is already owned in
+//     full by another allocator (a framework's caching pool, a fixed MIG/MPS slice budget),
+//     where a late cudaMalloc either fails or eats into memory promised to someone else;
+//   * a latency-critical request path, where cudaMalloc/cudaFree synchronise the whole
+//     device and stall every other stream for the duration of the call;
+//   * code that is only allowed to enqueue work on a stream it was handed and has no
+//     place in its lifecycle where allocating (and later freeing) would be legal.
+// For them this one entry point runs the same kernel with its scratch in a fixed array that
+// is part of the library image: nothing is allocated, by us or by any library we call.
+//
+// The price is a size limit.  The scratch holds the per-CTA partial sums for at most
+// FDB_NOALLOC_MAX_CTAS CTAs (128 KiB + one 256-byte line for the arrival ticket), which
+// covers FDB_NOALLOC_MAX_ROWS = 16384 rows per call in either dtype - the serving-size
+// batches of /predict and the XAI task.  Larger batches are refused with FDB_ERR_ARG; use
+// fdb_linear_pass_dev for those.  Every GPU that loads libfdb200.so carries the array until
+// the process exits, whether or not this entry point is ever called.
+//
+// Sharing.  There is one array per device, shared by every call on that device.  It keeps
+// whatever the previous call left in it; the only part that has to start at zero is the
+// arrival ticket, which is cleared on the caller's stream before each launch.  Two calls
+// whose kernels can overlap on the same GPU (different streams, or different host threads
+// with their own streams) race on the array and give wrong column sums: order them on one
+// stream or with events.  Calls that do not request abs_sum do not touch the array.
+//
+// Set-up.  The first call on each device looks up the array's device address
+// (cudaGetSymbolAddress, with that device current) and remembers it.  That lookup is host
+// work which may initialise the CUDA module, so make the first call on every device you
+// use during start-up, before any stream capture begins; later calls only enqueue a 4-byte
+// memset and the kernel.
+// =======================================================================================
+#include <mutex>
+
+#define FDB_NOALLOC_MAX_CTAS 512
+#define FDB_NOALLOC_MAX_DEVICES 64
+
+// Per-CTA partial sums ([FDB_NOALLOC_MAX_CTAS][32] doubles) followed by the ticket line.
+// In host code this name is only a handle for the runtime's symbol lookup - it is not a
+// device address and must never be handed to a kernel as one.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[FDB_NOALLOC_MAX_CTAS * 32 * sizeof(double) + 256];
+
+namespace {
+
+std::mutex g_noalloc_mu;
+unsigned char* g_noalloc_ptr[FDB_NOALLOC_MAX_DEVICES] = {};
+int g_noalloc_sms[FDB_NOALLOC_MAX_DEVICES] = {};
+
+// Device address of the scratch array on the CURRENT device (looked up once per device).
+int noalloc_scratch(unsigned char** out, int* sm_count) {
+    int dev = -1;
+    FDB_CUDA(cudaGetDevice(&dev));
+    FDB_REQUIRE(dev >= 0 && dev < FDB_NOALLOC_MAX_DEVICES, FDB_ERR_ARG, "device index %d not supported", dev);
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (g_noalloc_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        FDB_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        int sms = 0;
+        FDB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        g_noalloc_sms[dev] = sms;
+        g_noalloc_ptr[dev] = static_cast<unsigned char*>(p);
+    }
+    *out = g_noalloc_ptr[dev];
+    *sm_count = g_noalloc_sms[dev];
+    return FDB_OK;
+}
+
+template <typename T>
+int launch_noalloc(cudaStream_t st, int64_t n_rows, const void* x, const LinearParams& prm, void* proba,
+                   int proba_cols, void* logit, void* phi, uint8_t* cls, double* abs_sum) {
+    KParams<T> kp;
+    for (int k = 0; k < FDB_F; ++k) {
+        kp.sub[k] = (T)prm.sub[k];
+        kp.mul[k] = (T)prm.mul[k];
+    }
+    kp.bias = (T)prm.bias;
+    // same CTA count as the allocating entry point picks for a batch this small (two groups
+    // per warp), so the column sums fold in the same order and agree bit for bit
+    const int64_t n_groups = n_rows / Lane<T>::RPW;
+    int64_t want = (n_groups + 2 * kWarps - 1) / (2 * kWarps);
+    if (want < 1) want = 1;
+    FDB_REQUIRE(want <= FDB_NOALLOC_MAX_CTAS, FDB_ERR_ARG,
+                "fdb_linear_pass_noalloc: %lld rows need %lld CTAs of scratch but the built-in array holds %d",
+                (long long)n_rows, (long long)want, FDB_NOALLOC_MAX_CTAS);
+    double* partials = nullptr;
+    unsigned int* ticket = nullptr;
+    if (abs_sum != nullptr) {
+        unsigned char* base = nullptr;
+        int sms = 0;
+        int rc = noalloc_scratch(&base, &sms);
+        if (rc != FDB_OK) return rc;
+        partials = reinterpret_cast<double*>(base);
+        ticket = reinterpret_cast<unsigned int*>(base + (size_t)FDB_NOALLOC_MAX_CTAS * 32 * sizeof(double));
+        // the array keeps the last call's contents; only the ticket must start at zero
+        FDB_CUDA(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st));
+    }
+    linear_pass_kernel<T, false><<<(int)want, kThreads, 0, st>>>(
+        (const T*)x, n_rows, kp, (T*)proba, proba_cols, (T*)logit, (T*)phi, cls, abs_sum, partials, ticket);
+    FDB_CUDA(cudaGetLastError());
+    return FDB_OK;
+}
+
+}  // namespace
+
+extern "C" int fdb_linear_pass_noalloc(void* stream, int dtype, int64_t n_rows, const void* x, const double* sub,
+                                       const double* mul, double bias, void* proba, int proba_cols, void* logit,
+                                       void* phi, uint8_t* cls, double* abs_sum) {
+    FDB_REQUIRE(dtype == FDB_F32 || dtype == FDB_F64, FDB_ERR_ARG, "unknown dtype %d", dtype);
+    FDB_REQUIRE(n_rows >= 0, FDB_ERR_ARG, "n_rows is negative");
+    FDB_REQUIRE(n_rows <= FDB_NOALLOC_MAX_ROWS, FDB_ERR_ARG,
+                "fdb_linear_pass_noalloc handles at most %d rows per call (got %lld); larger batches need "
+                "fdb_linear_pass_dev, which allocates its scratch through an fdb_ctx",
+                FDB_NOALLOC_MAX_ROWS, (long long)n_rows);
+    FDB_REQUIRE(n_rows == 0 || x != nullptr, FDB_ERR_ARG, "x is NULL");
+    FDB_REQUIRE(mul != nullptr, FDB_ERR_ARG, "mul is NULL");
+    FDB_REQUIRE(proba_cols == 1 || proba_cols == 2, FDB_ERR_ARG, "proba_cols must be 1 or 2");
+    FDB_REQUIRE(fdb_aligned16(x) && fdb_aligned16(phi), FDB_ERR_ALIGN, "x and phi must be 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_rows == 0) {
+        if (abs_sum) FDB_CUDA(cudaMemsetAsync(abs_sum, 0, 32 * sizeof(double), st));
+        return FDB_OK;
+    }
+    LinearParams p;
+    for (int k = 0; k < FDB_F; ++k) {
+        p.sub[k] = sub ? sub[k] : 0.0;
+        p.mul[k] = mul[k];
+    }
+    p.bias = bias;
+    if (dtype == FDB_F32) return launch_noalloc<float>(st, n_rows, x, p, proba, proba_cols, logit, phi, cls, abs_sum);
+    return launch_noalloc<double>(st, n_rows, x, p, proba, proba_cols, logit, phi, cls, abs_sum);
+}

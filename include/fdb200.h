@@ -102,6 +102,24 @@ int fdb_linear_pass_host(fdb_ctx* ctx, int dtype, int64_t n_rows, const void* x,
                          const double* sub, const double* mul, double bias,
                          void* proba, int proba_cols, void* logit, void* phi, uint8_t* cls, double* abs_sum);
 
+/* ---------------------------------------------------------------------------------
+ * The fused linear pass of K1b for callers that are not allowed to allocate device memory
+ * (no counterpart in the reference - it exists for embedders of this library, not for
+ * parity).  Same arguments and results as fdb_linear_pass_dev, all pointers are DEVICE
+ * pointers, but there is no fdb_ctx: the kernel's scratch is a fixed array built into the
+ * library image, so the call performs no cudaMalloc/cudaFree and calls nothing that does.
+ * It runs on the current device.  Limits and rules:
+ *   - at most FDB_NOALLOC_MAX_ROWS rows per call; more returns FDB_ERR_ARG;
+ *   - one scratch array per device, shared by all calls: calls that request abs_sum and
+ *     may overlap on the same GPU race with each other - serialise them;
+ *   - the first call on a device looks the array up (host-side set-up); make it during
+ *     start-up, before any stream capture.
+ * ------------------------------------------------------------------------------- */
+#define FDB_NOALLOC_MAX_ROWS 16384
+int fdb_linear_pass_noalloc(void* stream, int dtype, int64_t n_rows, const void* x,
+                            const double* sub, const double* mul, double bias,
+                            void* proba, int proba_cols, void* logit, void* phi, uint8_t* cls, double* abs_sum);
+
 #ifdef __cplusplus
 }
 #endif
