@@ -315,7 +315,7 @@ def run_b200(args):
                     "api": "fdb_linear_pass_host (pinned host in/out, 3-stream chunked pipeline)"},
             "gpu_launches": args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": "linear_pass_kernel<float,false>", "kernel_ms": kernel_ms,
+                         "traffic": None, "kernel": "linear_pass_tma_kernel<float,false,true>", "kernel_ms": kernel_ms,
                          "algorithmic_bytes_per_launch": n * BYTES_PER_ROW, "peak_source": peak_src},
             "clocks": clocks.summary(),
         }

@@ -71,3 +71,9 @@ struct LinearParams {
 int fdb_launch_linear_pass(fdb_ctx* ctx, cudaStream_t st, int dtype, int64_t n_rows, const void* x,
                            const LinearParams& prm, bool divide, void* proba, int proba_cols, void* logit,
                            void* phi, uint8_t* cls, double* abs_sum, double* partials, unsigned int* ticket);
+
+// streaming (TMA bulk-copy) form of K1 for large batches - linear_pass_tma.cu
+int64_t fdb_linear_pass_tma_min_rows(const fdb_ctx* ctx, int dtype);
+int fdb_launch_linear_pass_tma(fdb_ctx* ctx, cudaStream_t st, int dtype, int64_t n_rows, const void* x,
+                               const LinearParams& prm, bool divide, void* proba, int proba_cols, void* logit,
+                               void* phi, uint8_t* cls, double* abs_sum, double* partials, unsigned int* ticket);

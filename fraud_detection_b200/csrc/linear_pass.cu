@@ -20,55 +20,16 @@
 // reduction, per-CTA partials in ctx scratch, last-arriving CTA folds them in CTA order ->
 // bitwise deterministic for a given grid.
 
-#include "fdb_internal.cuh"
+#include <stdlib.h>
+
+#include "linear_common.cuh"
+
+using namespace k1;
 
 namespace {
 
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
-
-template <typename T> struct Lane;
-template <> struct Lane<float> {
-    using V = float4;
-    static constexpr int EPL = 4;   // elements per lane
-    static constexpr int RPW = 4;   // rows per warp iteration
-};
-template <> struct Lane<double> {
-    using V = double2;
-    static constexpr int EPL = 2;
-    static constexpr int RPW = 2;
-};
-
-template <typename T> struct KParams {
-    T sub[FDB_F];
-    T mul[FDB_F];
-    T bias;
-};
-
-__device__ __forceinline__ void unpack(const float4& v, float (&e)[4]) { e[0] = v.x; e[1] = v.y; e[2] = v.z; e[3] = v.w; }
-__device__ __forceinline__ void unpack(const double2& v, double (&e)[2]) { e[0] = v.x; e[1] = v.y; }
-__device__ __forceinline__ float4 pack(const float (&e)[4]) { return make_float4(e[0], e[1], e[2], e[3]); }
-__device__ __forceinline__ double2 pack(const double (&e)[2]) { return make_double2(e[0], e[1]); }
-
-__device__ __forceinline__ float sigmoidT(float z) { return __frcp_rn(1.0f + __expf(-z)); }
-__device__ __forceinline__ double sigmoidT(double z) { return 1.0 / (1.0 + exp(-z)); }
-
-// proba_cols == 2 writes the sklearn layout [1 - p, p] (SK:linear_model/_base.py:438-440)
-template <typename T>
-__device__ __forceinline__ void emit_row(int64_t row, T z, T* __restrict__ proba, int proba_cols,
-                                         T* __restrict__ logit, uint8_t* __restrict__ cls) {
-    if (logit) logit[row] = z;
-    if (proba) {
-        const T p = sigmoidT(z);
-        if (proba_cols == 2) {
-            if constexpr (sizeof(T) == 4) reinterpret_cast<float2*>(proba)[row] = make_float2(1.0f - p, p);
-            else reinterpret_cast<double2*>(proba)[row] = make_double2(1.0 - p, p);
-        } else {
-            proba[row] = p;
-        }
-    }
-    if (cls) cls[row] = z > T(0) ? 1 : 0;
-}
 
 template <typename T, bool DIVIDE>
 __global__ void __launch_bounds__(kThreads)
@@ -282,6 +243,9 @@ int fdb_launch_linear_pass(fdb_ctx* ctx, cudaStream_t st, int dtype, int64_t n_r
         if (abs_sum) FDB_CUDA(cudaMemsetAsync(abs_sum, 0, 32 * sizeof(double), st));
         return FDB_OK;
     }
+    if (n_rows >= fdb_linear_pass_tma_min_rows(ctx, dtype) && getenv("FDB_K1_NO_TMA") == nullptr)
+        return fdb_launch_linear_pass_tma(ctx, st, dtype, n_rows, x, prm, divide, proba, proba_cols, logit, phi, cls,
+                                          abs_sum, partials, ticket);
     if (dtype == FDB_F32)
         return launch_typed<float>(ctx, st, n_rows, x, prm, divide, proba, proba_cols, logit, phi, cls, abs_sum, partials, ticket);
     return launch_typed<double>(ctx, st, n_rows, x, prm, divide, proba, proba_cols, logit, phi, cls, abs_sum, partials, ticket);
