@@ -51,6 +51,12 @@ _SIGS = {
     "fdb_linear_pass_dev": (_i, [_vp, _vp, _i, _i64, _vp, _dp, _dp, C.c_double, _vp, _i, _vp, _vp, _vp, _vp]),
     "fdb_linear_pass_host": (_i, [_vp, _i, _i64, _vp, _dp, _dp, C.c_double, _vp, _i, _vp, _vp, _vp, _vp]),
     "fdb_linear_pass_noalloc": (_i, [_vp, _i, _i64, _vp, _dp, _dp, C.c_double, _vp, _i, _vp, _vp, _vp, _vp]),
+    "fdb_kshap_plan_create": (_i, [_vp, _dp, C.c_double, _i, _vp, _i, _i, _vp, _vp, _i, C.POINTER(_vp)]),
+    "fdb_kshap_plan_destroy": (_i, [_vp]),
+    "fdb_kshap_expected_value": (C.c_double, [_vp]),
+    "fdb_kshap_plan_info": (_i, [_vp, C.POINTER(C.c_int)]),
+    "fdb_kshap_explain_dev": (_i, [_vp, _vp, _i64, _vp, _vp, _i, _vp, _vp, _vp]),
+    "fdb_kshap_explain_host": (_i, [_vp, _i64, _vp, _vp, _i, _vp, _vp]),
 }
 
 

@@ -1,0 +1,462 @@
+// Kernel SHAP on the B200: plan (per model/background/mask-set state), the SIMT reference
+// evaluator, K3 (constrained weighted least squares) and the C-ABI entry points.
+// The tensor-core evaluator (K2) lives in kshap_eval_tc.cu.
+//
+// Algorithm restated from shap.KernelExplainer (see oracle/kernel_shap.py for the step list):
+//   ey[r][m]  = mean_b sigmoid( sum_k (1 - z_mk) w_k bg_bk + sum_k z_mk w_k x_rk + c )        (evaluate)
+//   eyAdj     = link(ey) - link(fnull);  d = link(f(x)) - link(fnull)
+//   X = Z[:, :29] - Z[:, 29];  y = eyAdj - Z[:, 29] d;  w = (X'WX)^-1 X'W y;  phi[29] = d - sum(w)   (solve)
+// X'WX depends only on the mask set, so it is inverted once per set at plan creation
+// (kshap_wls_prepare) and every explained row costs one X'W y accumulation and one 29x29
+// mat-vec (kshap_wls_solve, one warp per row).
+
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <new>
+#include <vector>
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include "kshap_internal.cuh"
+
+namespace {
+
+constexpr int kNV = FDB_F - 1;   // 29 unknowns after eliminating the last feature
+
+__device__ __forceinline__ float link_apply(float v, int link) { return link == 1 ? logf(v / (1.0f - v)) : v; }
+
+// ---------------------------------------------------------------------------------------
+// bits -> A operand image (tcgen05 canonical K-major no-swizzle layout, 128 masks x 32 k per tile)
+//   a[m][k] = 1 - z_mk (k < 30), a[m][30] = 1 (bias lane), a[m][31] = 0
+__global__ void kshap_expand_masks(const uint32_t* __restrict__ bits, uint16_t* __restrict__ aimg, int64_t total,
+                                   uint16_t one) {
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // global mask index (set * m_pad + m)
+    if (idx >= total) return;
+    const uint32_t b = bits[idx];
+    const uint32_t abar = (~b & 0x3FFFFFFFu) | (1u << 30);
+    const int64_t tile = idx >> 7;
+    const int row = (int)(idx & 127);
+    uint4* dst = reinterpret_cast<uint4*>(aimg + tile * (128 * 32)) + (row >> 3) * 32 + (row & 7);   // 16-byte units
+#pragma unroll
+    for (int kc = 0; kc < 4; ++kc) {
+        uint32_t w[4];
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            const int k = kc * 8 + p * 2;
+            w[p] = (((abar >> k) & 1u) ? (uint32_t)one : 0u) | (((abar >> (k + 1)) & 1u) ? ((uint32_t)one << 16) : 0u);
+        }
+        dst[kc * 8] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// Per mask set: A = X'WX (29x29, f64), c2 = X'W z29, then A^-1 by Gauss-Jordan (SPD, no pivoting).
+// One warp per set; lane i owns row i of A while accumulating.
+__global__ void __launch_bounds__(32) kshap_wls_prepare(const uint32_t* __restrict__ bits, const float* __restrict__ kw,
+                                                        int m_pad, float* __restrict__ ainv, float* __restrict__ c2out,
+                                                        int* __restrict__ status) {
+    __shared__ double A[kNV][kNV + 1];
+    __shared__ double I[kNV][kNV + 1];
+    const int s = blockIdx.x;
+    const int lane = threadIdx.x;
+    const uint32_t* sb = bits + (size_t)s * m_pad;
+    const float* sk = kw + (size_t)s * m_pad;
+    double a[kNV];
+#pragma unroll
+    for (int j = 0; j < kNV; ++j) a[j] = 0.0;
+    double c2 = 0.0;
+    for (int m = 0; m < m_pad; ++m) {
+        const double w = (double)sk[m];
+        if (w == 0.0) continue;
+        const uint32_t b = sb[m];
+        const bool z29 = (b >> 29) & 1u;
+        const uint32_t zp = z29 ? ~b : b;          // x_i x_j = zp_i zp_j ; x_i = z29 ? -zp_i : zp_i
+        if ((zp >> lane) & 1u) {
+#pragma unroll
+            for (int j = 0; j < kNV; ++j)
+                if ((zp >> j) & 1u) a[j] += w;
+            if (z29) c2 -= w;
+        }
+    }
+    if (lane < kNV) {
+#pragma unroll
+        for (int j = 0; j < kNV; ++j) {
+            A[lane][j] = a[j];
+            I[lane][j] = (j == lane) ? 1.0 : 0.0;
+        }
+        c2out[(size_t)s * 32 + lane] = (float)c2;
+    } else {
+        c2out[(size_t)s * 32 + lane] = 0.f;
+    }
+    __syncwarp();
+    bool singular = false;
+    for (int k = 0; k < kNV; ++k) {
+        const double pk = A[k][k];
+        if (!(fabs(pk) > 1e-300)) { singular = true; break; }
+        const double inv = 1.0 / pk;
+        __syncwarp();
+        if (lane < kNV) {
+            A[k][lane] *= inv;
+            I[k][lane] *= inv;
+        }
+        __syncwarp();
+        for (int i = 0; i < kNV; ++i) {
+            if (i == k) continue;
+            const double f = A[i][k];
+            __syncwarp();
+            if (lane < kNV) {
+                A[i][lane] -= f * A[k][lane];
+                I[i][lane] -= f * I[k][lane];
+            }
+        }
+        __syncwarp();
+    }
+    for (int i = 0; i < kNV; ++i)
+        ainv[((size_t)s * kNV + i) * 32 + lane] = (lane < kNV && !singular) ? (float)I[i][lane] : 0.f;
+    if (lane == 0) status[s] = singular ? 1 : 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// SIMT evaluator: one thread per (row, mask), plain fp32 FMAs and full-precision expf.
+// The GPU-side cross-check of K2 and the evaluator for shapes K2 does not take.
+__global__ void __launch_bounds__(128) kshap_eval_simt(const float* __restrict__ x, int64_t row_offset,
+                                                       const int32_t* __restrict__ set_idx, int n_sets,
+                                                       const uint32_t* __restrict__ bits, int m_pad,
+                                                       const float* __restrict__ P, int n_bg,
+                                                       const float* __restrict__ wq, float* __restrict__ ey) {
+    __shared__ float q[32];
+    const int r = blockIdx.y;
+    const int m = blockIdx.x * 128 + threadIdx.x;
+    if (threadIdx.x < 32) q[threadIdx.x] = threadIdx.x < FDB_F ? wq[threadIdx.x] * x[(size_t)r * FDB_F + threadIdx.x] : 0.f;
+    __syncthreads();
+    const int s = set_idx ? set_idx[r] : (n_sets == 1 ? 0 : (int)((row_offset + r) % n_sets));
+    const uint32_t b = bits[(size_t)s * m_pad + m];
+    float sq = 0.f;
+#pragma unroll
+    for (int k = 0; k < FDB_F; ++k) sq += ((b >> k) & 1u) ? q[k] : 0.f;
+    float acc = 0.f;
+    for (int j = 0; j < n_bg; ++j) {
+        const float* pr = P + (size_t)j * 32;
+        float g = pr[30];   // intercept
+#pragma unroll
+        for (int k = 0; k < FDB_F; ++k) g += ((b >> k) & 1u) ? 0.f : pr[k];
+        acc += 1.0f / (1.0f + expf(-(g + sq)));
+    }
+    ey[(size_t)r * m_pad + m] = acc / (float)n_bg;
+}
+
+// ---------------------------------------------------------------------------------------
+// K3: one warp per explained row.
+__global__ void __launch_bounds__(128) kshap_wls_solve(
+    const float* __restrict__ x, int64_t row_offset, int n_rows, const int32_t* __restrict__ set_idx, int n_sets,
+    const uint32_t* __restrict__ bits, const float* __restrict__ kw, int m_pad, const float* __restrict__ ey,
+    const float* __restrict__ ainv, const float* __restrict__ c2, const float* __restrict__ wcoef, float intercept,
+    float fnull, int link, float* __restrict__ phi, double* __restrict__ abs_sum, int accumulate,
+    int64_t total_rows, double* __restrict__ partials, unsigned int* __restrict__ ticket) {
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const float lnull = link_apply(fnull, link);
+    const float wk = lane < FDB_F ? wcoef[lane] : 0.f;
+    double abs_acc = 0.0;
+    for (int r = blockIdx.x * 4 + warp; r < n_rows; r += gridDim.x * 4) {
+        const int s = set_idx ? set_idx[r] : (n_sets == 1 ? 0 : (int)((row_offset + r) % n_sets));
+        float z = lane < FDB_F ? wk * x[(size_t)r * FDB_F + lane] : 0.f;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) z += __shfl_xor_sync(0xffffffffu, z, o);
+        // link(f(x)): under the logit link it is the row's logit itself (no round trip through sigmoid)
+        const float lfx = link == 1 ? z + intercept : 1.0f / (1.0f + expf(-(z + intercept)));
+        const float d = lfx - lnull;
+        const uint32_t* sb = bits + (size_t)s * m_pad;
+        const float* sk = kw + (size_t)s * m_pad;
+        const float* er = ey + (size_t)r * m_pad;
+        float g = 0.f;
+        for (int m0 = 0; m0 < m_pad; m0 += 32) {
+            const uint32_t b = sb[m0 + lane];
+            const float kwv = sk[m0 + lane];
+            float v = kwv != 0.f ? kwv * (link_apply(er[m0 + lane], link) - lnull) : 0.f;
+            const bool z29 = (b >> 29) & 1u;
+            const float vp = z29 ? -v : v;          // x_mj * v = zp_j ? vp : 0
+            const uint32_t bp = z29 ? ~b : b;
+#pragma unroll
+            for (int t = 0; t < 32; ++t) {
+                const float vt = __shfl_sync(0xffffffffu, vp, t);
+                const uint32_t bt = __shfl_sync(0xffffffffu, bp, t);
+                g += ((bt >> lane) & 1u) ? vt : 0.f;
+            }
+        }
+        const float rhs = lane < kNV ? g - d * c2[(size_t)s * 32 + lane] : 0.f;
+        const float* ai = ainv + (size_t)s * kNV * 32;
+        float w = 0.f;
+#pragma unroll
+        for (int i = 0; i < kNV; ++i) w += ai[i * 32 + lane] * __shfl_sync(0xffffffffu, rhs, i);
+        float sumw = lane < kNV ? w : 0.f;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sumw += __shfl_xor_sync(0xffffffffu, sumw, o);
+        float p = lane < kNV ? w : (lane == kNV ? d - sumw : 0.f);
+        if (fabsf(p) < 1e-10f) p = 0.f;
+        if (lane < FDB_F) phi[(size_t)r * FDB_F + lane] = p;
+        abs_acc += fabs((double)p);
+    }
+    if (abs_sum == nullptr) return;
+    __shared__ double s_acc[4][32];
+    __shared__ bool s_last;
+    s_acc[warp][lane] = abs_acc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        partials[(size_t)blockIdx.x * 32 + lane] = s_acc[0][lane] + s_acc[1][lane] + s_acc[2][lane] + s_acc[3][lane];
+        __threadfence();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+    __syncthreads();
+    if (s_last && threadIdx.x < 32) {
+        __threadfence();
+        double tot = 0.0;
+        if (lane < FDB_F) {
+            for (unsigned b = 0; b < gridDim.x; ++b) tot += __ldcg(partials + (size_t)b * 32 + lane);
+            if (accumulate) tot += abs_sum[lane];
+        } else if (lane == FDB_F) {
+            tot = (double)total_rows;
+        }
+        abs_sum[lane] = tot;
+        if (lane == 0) *ticket = 0u;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+uint16_t f32_to_bf16(float f) { return __bfloat16_as_ushort(__float2bfloat16_rn(f)); }
+float bf16_to_f32(uint16_t h) { return __bfloat162float(__ushort_as_bfloat16(h)); }
+uint16_t f32_to_f16(float f) { return __half_as_ushort(__float2half_rn(f)); }
+float f16_to_f32(uint16_t h) { return __half2float(__ushort_as_half(h)); }
+
+void free_plan(fdb_kshap_plan* p) {
+    if (!p) return;
+    cudaFree(p->d_bits); cudaFree(p->d_kw); cudaFree(p->d_P); cudaFree(p->d_wq); cudaFree(p->d_bimg); cudaFree(p->d_aimg);
+    cudaFree(p->d_ainv); cudaFree(p->d_c2); cudaFree(p->d_status); cudaFree(p->d_ey); cudaFree(p->d_x); cudaFree(p->d_phi);
+    cudaFree(p->d_set); cudaFree(p->d_abs);
+    delete p;
+}
+
+}  // namespace
+
+// Split v into `n` 16-bit pieces (f16 or bf16) whose sum reproduces v to ~n*11 / n*8 bits.
+void fdb_kshap_split(double v, int fmt, int n, uint16_t* out) {
+    double rem = v;
+    for (int i = 0; i < n; ++i) {
+        const uint16_t h = fmt == 0 ? f32_to_f16((float)rem) : f32_to_bf16((float)rem);
+        out[i] = h;
+        rem -= (double)(fmt == 0 ? f16_to_f32(h) : bf16_to_f32(h));
+    }
+}
+
+extern "C" int fdb_kshap_plan_create(fdb_ctx* ctx, const double* coef, double intercept, int n_bg, const double* bg,
+                                     int n_sets, int n_masks, const uint32_t* bits, const double* kw, int link,
+                                     fdb_kshap_plan** out) {
+    FDB_REQUIRE(ctx && coef && bg && bits && kw && out, FDB_ERR_ARG, "NULL argument");
+    *out = nullptr;
+    FDB_REQUIRE(n_bg >= 1 && n_bg <= FDB_KSHAP_MAX_BG, FDB_ERR_ARG, "background rows must be in [1, %d], got %d", FDB_KSHAP_MAX_BG, n_bg);
+    FDB_REQUIRE(n_sets >= 1 && n_masks >= 1, FDB_ERR_ARG, "need at least one mask set and one mask");
+    FDB_REQUIRE(link == 0 || link == 1, FDB_ERR_ARG, "link must be 0 (identity) or 1 (logit)");
+    if (cudaSetDevice(ctx->device) != cudaSuccess) { fdb_set_error("cannot select device %d", ctx->device); return FDB_ERR_CUDA; }
+    fdb_kshap_plan* p = new (std::nothrow) fdb_kshap_plan();
+    FDB_REQUIRE(p != nullptr, FDB_ERR_NOMEM, "out of host memory");
+    p->ctx = ctx;
+    p->n_bg = n_bg;
+    p->nb_pad = (n_bg + 15) & ~15;
+    p->n_masks = n_masks;
+    p->m_pad = (n_masks + 127) & ~127;
+    p->n_sets = n_sets;
+    p->link = link;
+    p->intercept = intercept;
+    memcpy(p->coef, coef, sizeof(double) * FDB_F);
+    const size_t SM = (size_t)n_sets * p->m_pad;
+
+    // ---- host-side constant preparation (parameters, not rows) -----------------------------
+    const double LOG2E = 1.4426950408889634074;
+    std::vector<float> P((size_t)n_bg * 32, 0.f);
+    double fnull = 0.0, vmax = 0.0;
+    for (int b = 0; b < n_bg; ++b) {
+        double z = intercept;
+        for (int k = 0; k < FDB_F; ++k) {
+            const double pk = coef[k] * bg[(size_t)b * FDB_F + k];
+            P[(size_t)b * 32 + k] = (float)pk;
+            z += pk;
+            vmax = fmax(vmax, fabs(LOG2E * pk));
+        }
+        P[(size_t)b * 32 + 30] = (float)intercept;
+        fnull += 1.0 / (1.0 + exp(-z));
+    }
+    vmax = fmax(vmax, fabs(LOG2E * intercept));
+    p->fnull = fnull / n_bg;
+    const char* force = getenv("FDB_KSHAP_FMT");
+    p->fmt = (vmax < 16384.0) ? 0 : 1;                 // f16 x 2 splits unless the operand would overflow half
+    if (force) p->fmt = atoi(force) ? 1 : 0;
+    p->nsplit = p->fmt == 0 ? 2 : 3;
+    // B operand image: [split][row-group][k-chunk][8 rows][8 elems], value -log2e * w_k * bg_bk, col 30 = -log2e * c
+    std::vector<uint16_t> bimg((size_t)p->nsplit * p->nb_pad * 32, 0);
+    for (int b = 0; b < n_bg; ++b)
+        for (int k = 0; k < 31; ++k) {
+            const double v = -LOG2E * (k < FDB_F ? coef[k] * bg[(size_t)b * FDB_F + k] : intercept);
+            uint16_t parts[3];
+            fdb_kshap_split(v, p->fmt, p->nsplit, parts);
+            for (int sidx = 0; sidx < p->nsplit; ++sidx)
+                bimg[(size_t)sidx * p->nb_pad * 32 + (size_t)(b >> 3) * 256 + (k >> 3) * 64 + (b & 7) * 8 + (k & 7)] = parts[sidx];
+        }
+    std::vector<uint32_t> hbits(SM, 0u);
+    std::vector<float> hkw(SM, 0.f);
+    for (int s = 0; s < n_sets; ++s)
+        for (int m = 0; m < n_masks; ++m) {
+            hbits[(size_t)s * p->m_pad + m] = bits[(size_t)s * n_masks + m] & 0x3FFFFFFFu;
+            hkw[(size_t)s * p->m_pad + m] = (float)kw[(size_t)s * n_masks + m];
+        }
+    float wq[32] = {0};
+    for (int k = 0; k < FDB_F; ++k) wq[k] = (float)coef[k];
+
+    int rc = FDB_OK;
+    cudaError_t e = cudaSuccess;
+    do {
+#define TRY(x) if ((e = (x)) != cudaSuccess) break
+        TRY(cudaMalloc((void**)&p->d_bits, SM * 4));
+        TRY(cudaMalloc((void**)&p->d_kw, SM * 4));
+        TRY(cudaMalloc((void**)&p->d_P, P.size() * 4));
+        TRY(cudaMalloc((void**)&p->d_wq, 32 * 4));
+        TRY(cudaMalloc((void**)&p->d_bimg, bimg.size() * 2));
+        TRY(cudaMalloc((void**)&p->d_aimg, SM * 32 * 2));
+        TRY(cudaMalloc((void**)&p->d_ainv, (size_t)n_sets * kNV * 32 * 4));
+        TRY(cudaMalloc((void**)&p->d_c2, (size_t)n_sets * 32 * 4));
+        TRY(cudaMalloc((void**)&p->d_status, (size_t)n_sets * 4));
+        p->batch_rows = FDB_KSHAP_BATCH_ROWS;
+        TRY(cudaMalloc((void**)&p->d_ey, (size_t)p->batch_rows * p->m_pad * 4));
+        TRY(cudaMalloc((void**)&p->d_x, (size_t)p->batch_rows * FDB_F * 4));
+        TRY(cudaMalloc((void**)&p->d_phi, (size_t)p->batch_rows * FDB_F * 4));
+        TRY(cudaMalloc((void**)&p->d_set, (size_t)p->batch_rows * 4));
+        TRY(cudaMalloc((void**)&p->d_abs, 32 * 8));
+        TRY(cudaMemcpy(p->d_bits, hbits.data(), SM * 4, cudaMemcpyHostToDevice));
+        TRY(cudaMemcpy(p->d_kw, hkw.data(), SM * 4, cudaMemcpyHostToDevice));
+        TRY(cudaMemcpy(p->d_P, P.data(), P.size() * 4, cudaMemcpyHostToDevice));
+        TRY(cudaMemcpy(p->d_wq, wq, 32 * 4, cudaMemcpyHostToDevice));
+        TRY(cudaMemcpy(p->d_bimg, bimg.data(), bimg.size() * 2, cudaMemcpyHostToDevice));
+        const uint16_t one = p->fmt == 0 ? 0x3C00 : 0x3F80;
+        kshap_expand_masks<<<(unsigned)((SM + 255) / 256), 256>>>(p->d_bits, p->d_aimg, (int64_t)SM, one);
+        TRY(cudaGetLastError());
+        kshap_wls_prepare<<<n_sets, 32>>>(p->d_bits, p->d_kw, p->m_pad, p->d_ainv, p->d_c2, p->d_status);
+        TRY(cudaGetLastError());
+        TRY(cudaDeviceSynchronize());
+        std::vector<int> st(n_sets);
+        TRY(cudaMemcpy(st.data(), p->d_status, (size_t)n_sets * 4, cudaMemcpyDeviceToHost));
+        for (int s = 0; s < n_sets; ++s)
+            if (st[s]) {
+                fdb_set_error("mask set %d gives a singular weighted least-squares system (X'WX); "
+                              "use more samples or fewer features", s);
+                rc = FDB_ERR_ARG;
+                break;
+            }
+#undef TRY
+    } while (0);
+    if (e != cudaSuccess) {
+        fdb_set_error("kernel-SHAP plan creation failed: %s", cudaGetErrorString(e));
+        rc = e == cudaErrorMemoryAllocation ? FDB_ERR_NOMEM : FDB_ERR_CUDA;
+    }
+    if (rc != FDB_OK) { free_plan(p); return rc; }
+    *out = p;
+    return FDB_OK;
+}
+
+extern "C" int fdb_kshap_plan_destroy(fdb_kshap_plan* p) {
+    if (p) {
+        cudaSetDevice(p->ctx->device);
+        cudaDeviceSynchronize();
+        free_plan(p);
+    }
+    return FDB_OK;
+}
+
+extern "C" double fdb_kshap_expected_value(const fdb_kshap_plan* p) {
+    if (!p) return 0.0;
+    return p->link == 1 ? log(p->fnull / (1.0 - p->fnull)) : p->fnull;
+}
+
+extern "C" int fdb_kshap_plan_info(const fdb_kshap_plan* p, int* info8) {
+    FDB_REQUIRE(p && info8, FDB_ERR_ARG, "NULL argument");
+    info8[0] = p->n_bg; info8[1] = p->nb_pad; info8[2] = p->n_masks; info8[3] = p->m_pad;
+    info8[4] = p->n_sets; info8[5] = p->fmt; info8[6] = p->nsplit; info8[7] = (int)p->batch_rows;
+    return FDB_OK;
+}
+
+extern "C" int fdb_kshap_explain_dev(fdb_kshap_plan* p, void* stream, int64_t n_rows, const float* x,
+                                     const int32_t* set_idx, int evaluator, float* phi, float* ey_out, double* abs_sum) {
+    FDB_REQUIRE(p != nullptr, FDB_ERR_ARG, "plan is NULL");
+    FDB_REQUIRE(n_rows >= 0, FDB_ERR_ARG, "n_rows is negative");
+    FDB_REQUIRE(n_rows == 0 || (x && phi), FDB_ERR_ARG, "x / phi is NULL");
+    FDB_REQUIRE(evaluator == FDB_KSHAP_EVAL_TC || evaluator == FDB_KSHAP_EVAL_SIMT, FDB_ERR_ARG, "unknown evaluator %d", evaluator);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_rows == 0) {
+        if (abs_sum) FDB_CUDA(cudaMemsetAsync(abs_sum, 0, 32 * sizeof(double), st));
+        return FDB_OK;
+    }
+    fdb_ctx* ctx = p->ctx;
+    for (int64_t r0 = 0; r0 < n_rows; r0 += p->batch_rows) {
+        const int nb = (int)((n_rows - r0) < p->batch_rows ? (n_rows - r0) : p->batch_rows);
+        const float* xb = x + r0 * FDB_F;
+        const int32_t* sb = set_idx ? set_idx + r0 : nullptr;
+        if (evaluator == FDB_KSHAP_EVAL_TC) {
+            int rc = fdb_kshap_launch_eval_tc(p, st, xb, r0, nb, sb, p->d_ey);
+            if (rc != FDB_OK) return rc;
+        } else {
+            dim3 grid(p->m_pad / 128, nb);
+            kshap_eval_simt<<<grid, 128, 0, st>>>(xb, r0, sb, p->n_sets, p->d_bits, p->m_pad, p->d_P, p->n_bg, p->d_wq, p->d_ey);
+            FDB_CUDA(cudaGetLastError());
+        }
+        if (ey_out)
+            FDB_CUDA(cudaMemcpy2DAsync(ey_out + r0 * p->n_masks, (size_t)p->n_masks * 4, p->d_ey, (size_t)p->m_pad * 4,
+                                       (size_t)p->n_masks * 4, nb, cudaMemcpyDeviceToDevice, st));
+        int grid = (nb + 3) / 4;
+        const int cap = ctx->sm_count * 8;
+        if (grid > cap) grid = cap;
+        kshap_wls_solve<<<grid, 128, 0, st>>>(xb, r0, nb, sb, p->n_sets, p->d_bits, p->d_kw, p->m_pad, p->d_ey, p->d_ainv,
+                                             p->d_c2, p->d_wq, (float)p->intercept, (float)p->fnull, p->link,
+                                             phi + r0 * FDB_F, abs_sum, r0 > 0 ? 1 : 0, n_rows, ctx->d_partials,
+                                             ctx->d_ticket);
+        FDB_CUDA(cudaGetLastError());
+    }
+    return FDB_OK;
+}
+
+extern "C" int fdb_kshap_explain_host(fdb_kshap_plan* p, int64_t n_rows, const float* x, const int32_t* set_idx,
+                                      int evaluator, float* phi, double* abs_sum) {
+    FDB_REQUIRE(p != nullptr, FDB_ERR_ARG, "plan is NULL");
+    FDB_REQUIRE(n_rows >= 0, FDB_ERR_ARG, "n_rows is negative");
+    FDB_REQUIRE(n_rows == 0 || (x && phi), FDB_ERR_ARG, "x / phi is NULL");
+    if (abs_sum) memset(abs_sum, 0, 32 * sizeof(double));
+    if (n_rows == 0) return FDB_OK;
+    fdb_ctx* ctx = p->ctx;
+    FDB_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->slot[0].stream;
+    for (int64_t r0 = 0; r0 < n_rows; r0 += p->batch_rows) {
+        const int64_t nb = (n_rows - r0) < p->batch_rows ? (n_rows - r0) : p->batch_rows;
+        FDB_CUDA(cudaMemcpyAsync(p->d_x, x + r0 * FDB_F, (size_t)nb * FDB_F * 4, cudaMemcpyHostToDevice, st));
+        if (set_idx) FDB_CUDA(cudaMemcpyAsync(p->d_set, set_idx + r0, (size_t)nb * 4, cudaMemcpyHostToDevice, st));
+        // default set mapping must see global row numbers: shift through an explicit index when needed
+        const int32_t* sidx = set_idx ? p->d_set : nullptr;
+        if (!set_idx && p->n_sets > 1 && r0 > 0) {
+            std::vector<int32_t> tmp((size_t)nb);
+            for (int64_t i = 0; i < nb; ++i) tmp[(size_t)i] = (int32_t)((r0 + i) % p->n_sets);
+            FDB_CUDA(cudaMemcpyAsync(p->d_set, tmp.data(), (size_t)nb * 4, cudaMemcpyHostToDevice, st));
+            FDB_CUDA(cudaStreamSynchronize(st));
+            sidx = p->d_set;
+        }
+        int rc = fdb_kshap_explain_dev(p, st, nb, p->d_x, sidx, evaluator, p->d_phi, nullptr, abs_sum ? p->d_abs : nullptr);
+        if (rc != FDB_OK) return rc;
+        FDB_CUDA(cudaMemcpyAsync(phi + r0 * FDB_F, p->d_phi, (size_t)nb * FDB_F * 4, cudaMemcpyDeviceToHost, st));
+        double habs[32];
+        if (abs_sum) FDB_CUDA(cudaMemcpyAsync(habs, p->d_abs, sizeof(habs), cudaMemcpyDeviceToHost, st));
+        FDB_CUDA(cudaStreamSynchronize(st));
+        if (abs_sum)
+            for (int k = 0; k < FDB_F; ++k) abs_sum[k] += habs[k];
+    }
+    if (abs_sum) abs_sum[FDB_F] = (double)n_rows;
+    return FDB_OK;
+}

@@ -1,0 +1,41 @@
+// Internal declarations of the Kernel SHAP part of libfdb200.so.
+#pragma once
+
+#include "fdb_internal.cuh"
+
+#define FDB_KSHAP_MAX_BG 1024          // background rows the tensor-core evaluator keeps resident in smem
+#define FDB_KSHAP_BATCH_ROWS 8192      // explained rows per evaluate->solve round (bounds the ey scratch)
+
+struct fdb_kshap_plan {
+    fdb_ctx* ctx = nullptr;
+    int n_bg = 0, nb_pad = 0;          // background rows, padded to 16
+    int n_masks = 0, m_pad = 0;        // coalitions per set, padded to 128
+    int n_sets = 0;
+    int link = 0;                      // 0 identity, 1 logit
+    int fmt = 0, nsplit = 2;           // tcgen05 operand format: 0 = f16 x 2 splits, 1 = bf16 x 3 splits
+    double coef[FDB_F] = {0};
+    double intercept = 0.0;
+    double fnull = 0.0;                // mean_b f(bg_b)
+    int64_t batch_rows = 0;
+    // device state
+    uint32_t* d_bits = nullptr;        // [S][m_pad] coalition bit masks (bit k = feature k present)
+    float* d_kw = nullptr;             // [S][m_pad] kernel weights (0 for padding)
+    float* d_P = nullptr;              // [B][32] w_k * bg_bk, column 30 = intercept (SIMT evaluator)
+    float* d_wq = nullptr;             // [32] w_k
+    uint16_t* d_bimg = nullptr;        // B operand, smem image: [split][nb_pad/8][4][8][8]
+    uint16_t* d_aimg = nullptr;        // A operand tiles, smem image: [S][m_pad/128][16][4][8][8]
+    float* d_ainv = nullptr;           // [S][29][32] (X'WX)^-1
+    float* d_c2 = nullptr;             // [S][32]     X'W z29
+    int* d_status = nullptr;           // [S] 1 = singular
+    float* d_ey = nullptr;             // [batch_rows][m_pad] scratch between evaluate and solve
+    float* d_x = nullptr;              // host-API staging
+    float* d_phi = nullptr;
+    int32_t* d_set = nullptr;
+    double* d_abs = nullptr;
+};
+
+void fdb_kshap_split(double v, int fmt, int n, uint16_t* out);
+
+// K2: tcgen05 evaluator (kshap_eval_tc.cu).  ey[r][m] for rows [0, n_rows) of x.
+int fdb_kshap_launch_eval_tc(fdb_kshap_plan* p, cudaStream_t st, const float* x, int64_t row_offset, int n_rows,
+                             const int32_t* set_idx, float* ey);

@@ -108,3 +108,200 @@ class B200LinearExplainer:
             _lib.np_ptr(abs_sum)))
         mean_abs = abs_sum[:N_FEATURES] / max(A.shape[0], 1)
         return phi.astype(np.float64, copy=False), mean_abs, mean_abs.argsort()[-3:][::-1]
+
+
+# =========================================================================================
+# Kernel SHAP
+# =========================================================================================
+EVAL_TC, EVAL_SIMT = 0, 1
+_LINKS = {"identity": 0, "logit": 1}
+
+
+def _linear_model_of(model):
+    """Accept what a reference-style caller would hand to KernelExplainer for this model:
+    the estimator, its bound ``predict_proba`` (``lambda X: model.predict_proba(X)[:, 1]`` cannot
+    be introspected, so pass the estimator or the bound method instead), or ``(coef, intercept)``."""
+    owner = getattr(model, "__self__", None)
+    if owner is not None and hasattr(owner, "coef_"):
+        model = owner
+    return _parse_model(model)
+
+
+class KernelShapPlan:
+    """Owner of one native ``fdb_kshap_plan`` (model + background + coalition sets on the GPU)."""
+
+    def __init__(self, coef, intercept, background, bits, weights, link="identity", device=None):
+        import ctypes as C
+        bits = np.ascontiguousarray(bits, dtype=np.uint32)
+        weights = np.ascontiguousarray(weights, dtype=np.float64)
+        if bits.ndim == 1:
+            bits, weights = bits[None, :], weights[None, :]
+        if bits.shape != weights.shape:
+            raise ValueError("bits and weights must have the same shape (n_sets, n_masks)")
+        bg = np.ascontiguousarray(background, dtype=np.float64)
+        if bg.ndim != 2 or bg.shape[1] != N_FEATURES:
+            raise ValueError(f"background must be (n, {N_FEATURES})")
+        self.n_sets, self.n_masks = int(bits.shape[0]), int(bits.shape[1])
+        self.device = device
+        h = C.c_void_p()
+        _lib.check(_lib.lib.fdb_kshap_plan_create(
+            _lib.get_ctx(device), _lib.dvec(coef), float(intercept), int(bg.shape[0]), _lib.np_ptr(bg),
+            self.n_sets, self.n_masks, _lib.np_ptr(bits), _lib.np_ptr(weights), _LINKS[link], C.byref(h)))
+        self._h = h.value
+        self.expected_value = float(_lib.lib.fdb_kshap_expected_value(self._h))
+
+    def info(self) -> dict:
+        import ctypes as C
+        arr = (C.c_int * 8)()
+        _lib.check(_lib.lib.fdb_kshap_plan_info(self._h, arr))
+        keys = ("n_bg", "nb_pad", "n_masks", "m_pad", "n_sets", "fmt", "nsplit", "batch_rows")
+        return dict(zip(keys, list(arr)))
+
+    def explain_host(self, X32: np.ndarray, set_idx=None, evaluator=EVAL_TC, abs_sum=None) -> np.ndarray:
+        X32 = np.ascontiguousarray(X32, dtype=np.float32)
+        phi = np.empty_like(X32)
+        sidx = None if set_idx is None else np.ascontiguousarray(set_idx, dtype=np.int32)
+        _lib.check(_lib.lib.fdb_kshap_explain_host(self._h, X32.shape[0], _lib.np_ptr(X32), _lib.np_ptr(sidx),
+                                                   int(evaluator), _lib.np_ptr(phi), _lib.np_ptr(abs_sum)))
+        return phi
+
+    def explain_dev(self, x, set_idx=None, evaluator=EVAL_TC, phi=None, ey=None, abs_sum=None, stream=None):
+        """torch CUDA tensors in/out (float32 rows); enqueues on torch's current stream."""
+        import torch
+        if not (x.is_cuda and x.dtype == torch.float32 and x.is_contiguous() and x.dim() == 2 and x.shape[1] == N_FEATURES):
+            raise ValueError(f"x must be a contiguous float32 CUDA tensor of shape (N, {N_FEATURES})")
+        phi = torch.empty_like(x) if phi is None else phi
+        st = int(torch.cuda.current_stream(x.device).cuda_stream) if stream is None else int(stream)
+        _lib.check(_lib.lib.fdb_kshap_explain_dev(
+            self._h, st, x.shape[0], x.data_ptr(), None if set_idx is None else set_idx.data_ptr(), int(evaluator),
+            phi.data_ptr(), None if ey is None else ey.data_ptr(), None if abs_sum is None else abs_sum.data_ptr()))
+        return phi
+
+    def close(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            _lib.lib.fdb_kshap_plan_destroy(h)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class B200KernelExplainer:
+    """``shap.KernelExplainer(f, background)`` for f = P(class 1) of the logistic model.
+
+    ``shap_values(X, nsamples=..., l1_reg=False)`` follows the reference algorithm (see
+    oracle/kernel_shap.py): per explained row a fresh coalition sample is drawn from the global
+    ``np.random`` state (``mask_mode="per_row"``, what shap does), the coalition expectations
+    are evaluated by the tcgen05 kernel (K2) and the additivity-constrained weighted least
+    squares is solved per row (K3).  ``mask_mode="shared"`` draws ONE coalition set for all rows
+    - a different sampler from the reference, meant for throughput runs.
+    ``masks=(Z, kw)`` or a list of per-row pairs feeds exported reference masks instead.
+    Only ``l1_reg=False`` (plain WLS over all features) runs on the GPU.
+    """
+
+    def __init__(self, model, data, link="identity", device=None, keep_index=False, **kwargs):
+        if link not in _LINKS:
+            raise ValueError(f"link must be one of {list(_LINKS)}")
+        self.coef, self.intercept = _linear_model_of(model)
+        data = data.values if hasattr(data, "values") else data
+        self.data = np.ascontiguousarray(data, dtype=np.float64)
+        if self.data.ndim == 1:
+            self.data = self.data.reshape(1, -1)
+        if self.data.shape[1] != N_FEATURES:
+            raise ValueError(f"background must have {N_FEATURES} features")
+        if self.data.shape[0] > 100:
+            import warnings
+            warnings.warn(f"Using {self.data.shape[0]} background data samples could cause slower run times. "
+                          "Consider using shap.sample(data, K) or shap.kmeans(data, K) to summarize the background as K samples.")
+        self.link = link
+        self.device = device
+        z = self.data @ self.coef + self.intercept
+        self.fnull = float(np.mean(1.0 / (1.0 + np.exp(-z))))
+        self.expected_value = float(np.log(self.fnull / (1 - self.fnull))) if link == "logit" else self.fnull
+        self._shared_cache: dict = {}
+
+    # ------------------------------------------------------------------ helpers
+    def _varying(self, X: np.ndarray) -> np.ndarray:
+        """(R, 30) bool: feature differs from at least one background row (shap's varying_groups)."""
+        lo, hi = self.data.min(0), self.data.max(0)
+        const_col = np.isclose(lo, hi)
+        return ~(const_col[None, :] & np.isclose(X, lo[None, :]))
+
+    @staticmethod
+    def _pad_sets(sets):
+        n = max(len(b) for b, _ in sets)
+        bits = np.zeros((len(sets), n), dtype=np.uint32)
+        kw = np.zeros((len(sets), n), dtype=np.float64)
+        for i, (b, w) in enumerate(sets):
+            bits[i, :len(b)] = b
+            kw[i, :len(w)] = w
+        return bits, kw
+
+    def shap_values(self, X, nsamples="auto", l1_reg=False, mask_mode="per_row", masks=None, evaluator=EVAL_TC,
+                    random=None, silent=True, **kwargs):
+        from . import sampler
+        if l1_reg not in (False, 0):
+            raise NotImplementedError("only l1_reg=False (plain constrained WLS) runs on the B200 path; "
+                                      "feature-selecting l1_reg modes are listed as next in SURVEY.md 8(f)")
+        A, single = _plain_rows(X)
+        A64 = A.astype(np.float64, copy=False)
+        varying = self._varying(A64)
+        full = varying.all(1)
+        out = np.zeros(A.shape, dtype=np.float64)
+        # degenerate rows (shap: M == 0 -> zeros, M == 1 -> the single varying feature takes f(x) - E[f])
+        if not full.all():
+            for r in np.nonzero(~full)[0]:
+                nv = int(varying[r].sum())
+                if nv == 0:
+                    continue
+                if nv == 1:
+                    fx = float(B200LogisticRegressionProxy(self.coef, self.intercept, self.device).proba(A64[r:r + 1])[0])
+                    lf = (lambda v: np.log(v / (1 - v))) if self.link == "logit" else (lambda v: v)
+                    out[r, np.nonzero(varying[r])[0][0]] = lf(fx) - lf(self.fnull)
+                    continue
+                raise NotImplementedError("rows where 2..29 features vary against the background are not supported "
+                                          "on the B200 path yet (all 30, one or none are)")
+        rows = np.nonzero(full)[0]
+        if len(rows) == 0:
+            return out[0] if single else out
+        Xr = np.ascontiguousarray(A[rows], dtype=np.float32)
+        if masks is not None:
+            pairs = masks if isinstance(masks, list) else [masks]
+            sets = [(sampler.masks_to_bits(Z) if np.asarray(Z).ndim == 2 else np.asarray(Z, dtype=np.uint32), np.asarray(w))
+                    for Z, w in pairs]
+            if len(sets) not in (1, len(rows)):
+                raise ValueError("masks must be one (Z, kw) pair or one pair per explained row")
+        elif mask_mode == "shared":
+            key = (nsamples, id(random))
+            if key not in self._shared_cache:
+                self._shared_cache[key] = [sampler.sample_coalitions(N_FEATURES, nsamples, random)]
+            sets = self._shared_cache[key]
+        elif mask_mode == "per_row":
+            sets = [sampler.sample_coalitions(N_FEATURES, nsamples, random) for _ in range(len(rows))]
+        else:
+            raise ValueError("mask_mode must be 'per_row' or 'shared'")
+        bits, kw = self._pad_sets(sets)
+        plan = KernelShapPlan(self.coef, self.intercept, self.data, bits, kw, self.link, self.device)
+        try:
+            phi = plan.explain_host(Xr, None, evaluator)
+        finally:
+            plan.close()
+        out[rows] = phi
+        return out[0] if single else out
+
+
+class B200LogisticRegressionProxy:
+    """Tiny helper: P(class 1) of (coef, intercept) through the K1 host entry point."""
+
+    def __init__(self, coef, intercept, device=None):
+        self._coef_c, self.intercept, self.device = _lib.dvec(coef), float(intercept), device
+
+    def proba(self, X64: np.ndarray) -> np.ndarray:
+        X64 = np.ascontiguousarray(X64, dtype=np.float64)
+        p = np.empty((X64.shape[0],), dtype=np.float64)
+        _lib.check(_lib.lib.fdb_linear_pass_host(_lib.get_ctx(self.device), _lib.F64, X64.shape[0], _lib.np_ptr(X64), None,
+                                                 self._coef_c, self.intercept, _lib.np_ptr(p), 1, None, None, None, None))
+        return p

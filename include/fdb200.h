@@ -103,6 +103,38 @@ int fdb_linear_pass_host(fdb_ctx* ctx, int dtype, int64_t n_rows, const void* x,
                          void* proba, int proba_cols, void* logit, void* phi, uint8_t* cls, double* abs_sum);
 
 /* ---------------------------------------------------------------------------------
+ * Kernel SHAP (K2 evaluator + K3 solve).  Replaces
+ *   shap.KernelExplainer(f, background).shap_values(X, nsamples=..., l1_reg=False)
+ * with f = model.predict_proba(.)[:, 1] of the logistic model (BASELINE.json configs 3-4;
+ * shap==0.49.1 is pinned at requirements.txt:21, the reference holds no call site).
+ *
+ * A plan fixes the model (coef, intercept in the space of the rows being explained), the
+ * background (n_bg x 30, host doubles, at most 1024 rows) and one or more coalition mask
+ * sets: bits[s][m] has bit k set when feature k takes the explained row's value, kw[s][m]
+ * is the Shapley-kernel weight (maskMatrix / kernelWeights of the reference run).  With
+ * n_sets == 1 all rows share the set; otherwise row r uses set set_idx[r] (or r mod n_sets
+ * when set_idx is NULL), which reproduces the reference's per-row sampling.
+ * link: 0 identity, 1 logit.  evaluator: FDB_KSHAP_EVAL_TC (tcgen05 tensor cores) or
+ * FDB_KSHAP_EVAL_SIMT (plain fp32 CUDA cores; the cross-check).
+ * explain: x is n_rows x 30 float32; phi is n_rows x 30 float32 with
+ * sum_k phi[r][k] = link(f(x_r)) - expected_value exactly by construction; ey_out
+ * (optional, n_rows x n_masks) returns the coalition expectations; abs_sum as in K1b.
+ * A singular X'WX (too few coalitions) makes plan creation fail with FDB_ERR_ARG.
+ * ------------------------------------------------------------------------------- */
+typedef struct fdb_kshap_plan fdb_kshap_plan;
+enum { FDB_KSHAP_EVAL_TC = 0, FDB_KSHAP_EVAL_SIMT = 1 };
+int fdb_kshap_plan_create(fdb_ctx* ctx, const double* coef, double intercept, int n_bg, const double* bg,
+                          int n_sets, int n_masks, const uint32_t* bits, const double* kw, int link,
+                          fdb_kshap_plan** out);
+int fdb_kshap_plan_destroy(fdb_kshap_plan* plan);
+double fdb_kshap_expected_value(const fdb_kshap_plan* plan);
+int fdb_kshap_plan_info(const fdb_kshap_plan* plan, int* info8);
+int fdb_kshap_explain_dev(fdb_kshap_plan* plan, void* stream, int64_t n_rows, const float* x,
+                          const int32_t* set_idx, int evaluator, float* phi, float* ey_out, double* abs_sum);
+int fdb_kshap_explain_host(fdb_kshap_plan* plan, int64_t n_rows, const float* x, const int32_t* set_idx,
+                           int evaluator, float* phi, double* abs_sum);
+
+/* ---------------------------------------------------------------------------------
  * The fused linear pass of K1b for callers that are not allowed to allocate device memory
  * (no counterpart in the reference - it exists for embedders of this library, not for
  * parity).  Same arguments and results as fdb_linear_pass_dev, all pointers are DEVICE

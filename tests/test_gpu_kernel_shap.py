@@ -1,0 +1,183 @@
+"""GPU parity: Kernel SHAP (K2 tcgen05 evaluator + K3 constrained WLS) against the oracle.
+
+Both sides are fed the IDENTICAL coalition masks and kernel weights (BASELINE.json's parity
+rule).  Tolerances (north_star): phi within 1e-4 relative (taken against the largest |phi| of
+the row, since the smallest attributions of a row sit below float32 resolution of the sums they
+come from), additivity sum(phi) + E[f] = f(x) within 1e-5.  The oracle is parity-unpinned
+against the shap package (not installable here) - see oracle/__init__.py.
+"""
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+from oracle import kernel_shap as ks  # noqa: E402
+from oracle import scoring, synth  # noqa: E402
+
+TC, SIMT = 0, 1
+
+
+def _setup(params, n_bg, n_rows, seed=0):
+    bg = scoring.transform(params, synth.rows(n_bg, seed=43))
+    X = scoring.transform(params, synth.rows(n_rows, seed=100 + seed))
+    f = lambda A: scoring.predict_proba(params, A)[:, 1]  # noqa: E731
+    return bg, X, f
+
+
+def _oracle_rows(f, X, bg, sets, link="identity"):
+    fnull = float(f(bg).mean())
+    phi, ey = [], []
+    for i, x in enumerate(X):
+        Z, kw = sets[i % len(sets)]
+        e = ks.evaluate(f, x, bg, Z)
+        ey.append(e)
+        phi.append(ks.solve(Z, kw, e, float(f(x[None])[0]), fnull, link=link))
+    return np.array(phi), np.array(ey), fnull
+
+
+def _plan(params, bg, sets, link="identity"):
+    from fraud_detection_b200 import KernelShapPlan, sampler
+    n = max(len(kw) for _, kw in sets)
+    bits = np.zeros((len(sets), n), dtype=np.uint32)
+    w = np.zeros((len(sets), n))
+    for i, (Z, kw) in enumerate(sets):
+        bits[i, :len(kw)] = sampler.masks_to_bits(Z)
+        w[i, :len(kw)] = kw
+    return KernelShapPlan(params.coef, params.intercept, bg, bits, w, link)
+
+
+def _run(plan, X, evaluator, want_ey=True):
+    x = torch.from_numpy(np.ascontiguousarray(X, dtype=np.float32)).cuda()
+    ey = torch.empty((x.shape[0], plan.n_masks), dtype=torch.float32, device="cuda") if want_ey else None
+    abs_sum = torch.empty(32, dtype=torch.float64, device="cuda")
+    phi = plan.explain_dev(x, evaluator=evaluator, ey=ey, abs_sum=abs_sum)
+    torch.cuda.synchronize()
+    return phi.cpu().numpy().astype(np.float64), (ey.cpu().numpy() if want_ey else None), abs_sum.cpu().numpy()
+
+
+def _check_phi(phi, phi_ref, f, X, expected, rel=1e-4, link=lambda v: v):
+    scale = np.abs(phi_ref).max(1, keepdims=True)
+    assert np.all(np.abs(phi - phi_ref) <= rel * scale + 1e-9), float((np.abs(phi - phi_ref) / scale).max())
+    np.testing.assert_allclose(phi.sum(1) + expected, link(f(X)), rtol=0, atol=1e-5)
+
+
+@pytest.mark.parametrize("evaluator", [SIMT, TC])
+@pytest.mark.parametrize("nsamples,n_bg", [(2048, 100), (256, 100), (100, 37), (2048, 1)])
+def test_shared_masks_vs_oracle(params, evaluator, nsamples, n_bg):
+    bg, X, f = _setup(params, n_bg, 12)
+    Z, kw, _ = ks.sample_coalitions(30, nsamples, np.random.RandomState(0))
+    phi_ref, ey_ref, fnull = _oracle_rows(f, X, bg, [(Z, kw)])
+    plan = _plan(params, bg, [(Z, kw)])
+    assert abs(plan.expected_value - fnull) < 1e-12
+    phi, ey, abs_sum = _run(plan, X, evaluator)
+    np.testing.assert_allclose(ey, ey_ref, rtol=0, atol=2e-6)
+    _check_phi(phi, phi_ref, f, X, fnull)
+    np.testing.assert_allclose(abs_sum[:30], np.abs(phi).sum(0), rtol=1e-6)
+    assert abs_sum[30] == len(X)
+    plan.close()
+
+
+def test_tc_and_simt_evaluators_agree(params):
+    bg, X, f = _setup(params, 100, 40, seed=1)
+    Z, kw, _ = ks.sample_coalitions(30, 2048, np.random.RandomState(1))
+    plan = _plan(params, bg, [(Z, kw)])
+    phi_a, ey_a, _ = _run(plan, X, TC)
+    phi_b, ey_b, _ = _run(plan, X, SIMT)
+    np.testing.assert_allclose(ey_a, ey_b, rtol=0, atol=1e-6)
+    np.testing.assert_allclose(phi_a, phi_b, rtol=0, atol=2e-6)
+    info = plan.info()
+    assert info["m_pad"] == 2048 and info["nb_pad"] == 112 and info["nsplit"] in (2, 3)
+    plan.close()
+
+
+def test_per_row_masks_like_the_reference(params):
+    """The reference draws fresh coalitions for every explained row; feed the exported sets."""
+    bg, X, f = _setup(params, 100, 24, seed=2)
+    rs = np.random.RandomState(2)
+    sets = [ks.sample_coalitions(30, 2048, rs)[:2] for _ in range(len(X))]
+    phi_ref, ey_ref, fnull = _oracle_rows(f, X, bg, sets)
+    plan = _plan(params, bg, sets)
+    for ev in (TC, SIMT):
+        phi, ey, _ = _run(plan, X, ev)
+        np.testing.assert_allclose(ey, ey_ref, rtol=0, atol=2e-6)
+        _check_phi(phi, phi_ref, f, X, fnull)
+    plan.close()
+
+
+def test_config4_shapes_wide_background(params):
+    """nsamples=4096, 1000-row background: the evaluator walks the background in TMEM-sized chunks."""
+    bg, X, f = _setup(params, 1000, 6, seed=3)
+    Z, kw, _ = ks.sample_coalitions(30, 4096, np.random.RandomState(3))
+    phi_ref, ey_ref, fnull = _oracle_rows(f, X, bg, [(Z, kw)])
+    plan = _plan(params, bg, [(Z, kw)])
+    phi, ey, _ = _run(plan, X, TC)
+    np.testing.assert_allclose(ey, ey_ref, rtol=0, atol=2e-6)
+    _check_phi(phi, phi_ref, f, X, fnull)
+    plan.close()
+
+
+def test_logit_link(params):
+    bg, X, f = _setup(params, 50, 8, seed=4)
+    Z, kw, _ = ks.sample_coalitions(30, 1024, np.random.RandomState(4))
+    phi_ref, _, fnull = _oracle_rows(f, X, bg, [(Z, kw)], link="logit")
+    plan = _plan(params, bg, [(Z, kw)], link="logit")
+    lg = lambda v: np.log(v / (1 - v))  # noqa: E731
+    assert abs(plan.expected_value - lg(fnull)) < 1e-10
+    phi, _, _ = _run(plan, X, TC, want_ey=False)
+    scale = np.abs(phi_ref).max(1, keepdims=True)
+    assert np.all(np.abs(phi - phi_ref) <= 2e-3 * scale)          # float32 logit() of ey amplifies rounding
+    np.testing.assert_allclose(phi.sum(1) + lg(fnull), lg(f(X)), rtol=0, atol=2e-4)
+    plan.close()
+
+
+def test_many_rows_batches_and_determinism(params):
+    """More rows than one evaluate->solve batch (8192): batches stitch together, reruns are bitwise equal."""
+    bg, X, f = _setup(params, 20, 9000, seed=5)
+    Z, kw, _ = ks.sample_coalitions(30, 128, np.random.RandomState(5))
+    plan = _plan(params, bg, [(Z, kw)])
+    phi, _, abs_sum = _run(plan, X, TC, want_ey=False)
+    phi2, _, abs_sum2 = _run(plan, X, TC, want_ey=False)
+    assert np.array_equal(phi, phi2) and np.array_equal(abs_sum, abs_sum2)
+    idx = np.array([0, 1, 4095, 8191, 8192, 8999])
+    phi_ref, _, fnull = _oracle_rows(f, X[idx], bg, [(Z, kw)])
+    _check_phi(phi[idx], phi_ref, f, X[idx], fnull)
+    np.testing.assert_allclose(phi.sum(1) + fnull, f(X), rtol=0, atol=1e-5)
+    np.testing.assert_allclose(abs_sum[:30], np.abs(phi).sum(0), rtol=1e-6)
+    plan.close()
+
+
+def test_explainer_class_matches_oracle_with_same_seed(params):
+    from fraud_detection_b200 import B200KernelExplainer, B200LogisticRegression
+    bg, X, f = _setup(params, 100, 5, seed=6)
+    model = B200LogisticRegression(params.coef, params.intercept)
+    expl = B200KernelExplainer(model.predict_proba, bg)
+    assert abs(expl.expected_value - ks.expected_value(f, bg)) < 1e-12
+    phi = expl.shap_values(X, nsamples=2048, l1_reg=False, random=np.random.RandomState(7))
+    phi_ref = ks.shap_values(f, X, bg, nsamples=2048, l1_reg=False, random=np.random.RandomState(7))
+    _check_phi(phi, phi_ref, f, X, expl.expected_value)
+    one = expl.shap_values(X[0], nsamples=2048, random=np.random.RandomState(7))
+    assert one.shape == (30,)
+    np.testing.assert_allclose(one, phi[0], atol=1e-12)
+    shared = expl.shap_values(X, nsamples=2048, mask_mode="shared", random=np.random.RandomState(8))
+    np.testing.assert_allclose(shared.sum(1) + expl.expected_value, f(X), atol=1e-5)
+    with pytest.raises(NotImplementedError):
+        expl.shap_values(X, l1_reg="num_features(10)")
+
+
+def test_degenerate_rows_and_errors(params):
+    from fraud_detection_b200 import B200KernelExplainer, KernelShapPlan
+    bg = np.tile(np.arange(30.0), (5, 1))
+    expl = B200KernelExplainer((params.coef, params.intercept), bg)
+    f = lambda A: scoring.predict_proba(params, A)[:, 1]  # noqa: E731
+    x1 = bg[0].copy(); x1[3] += 1.0
+    phi = expl.shap_values(np.stack([bg[0], x1]), nsamples=256)
+    assert np.all(phi[0] == 0) and np.count_nonzero(phi[1]) == 1
+    np.testing.assert_allclose(phi[1, 3], f(x1[None])[0] - f(bg).mean(), atol=1e-12)
+    # too few coalitions -> singular normal matrix -> ValueError at plan creation, like shap's LinAlgError path
+    with pytest.raises(ValueError, match="singular"):
+        KernelShapPlan(params.coef, params.intercept, bg, np.array([1, 2, 3], dtype=np.uint32), np.ones(3))
+    with pytest.raises(ValueError):
+        KernelShapPlan(params.coef, params.intercept, np.zeros((2000, 30)), np.array([1], dtype=np.uint32), np.ones(1))
