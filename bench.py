@@ -48,6 +48,10 @@ def parse_args():
     ap.add_argument("--rows", type=int, default=int(os.environ.get("FDB_BENCH_ROWS", 100_000_000)),
                     help="rows per GPU resident in HBM (config 2: 1e8)")
     ap.add_argument("--e2e-rows", type=int, default=int(os.environ.get("FDB_BENCH_E2E_ROWS", 8_000_000)))
+    ap.add_argument("--kshap-rows", type=int, default=int(os.environ.get("FDB_BENCH_KSHAP_ROWS", 100_000)))
+    ap.add_argument("--kshap-per-row", type=int, default=1024)
+    ap.add_argument("--kshap-cpu-rows", type=int, default=256)
+    ap.add_argument("--no-kshap", action="store_true")
     ap.add_argument("--cpu-rows", type=int, default=int(os.environ.get("FDB_BENCH_CPU_ROWS", 4_000_000)))
     return ap.parse_args()
 
@@ -215,6 +219,111 @@ def synth_rows_device(torch, n, seed, device, chunk=10_000_000):
     return x
 
 
+
+# ------------------------------------------------------------------------------- Kernel SHAP (configs 3/4)
+def bench_kernel_shap(args, torch, dist, device, rank, world, prm, sm_max_mhz):
+    """Config 3: nsamples=2048, 100-row background, 100k explained rows per GPU, shared coalition set
+    (the throughput mode), plus a per-row-mask subset (the reference's sampler).  Returns a dict for
+    the JSON line; timing is CUDA events on the launching stream, max over ranks."""
+    from fraud_detection_b200 import KernelShapPlan, PinnedBuffer, sampler
+    from oracle import scoring, synth
+
+    rows, nsamples, n_bg = args.kshap_rows, 2048, 100
+    bg = scoring.transform(prm, synth.rows(n_bg, seed=43))
+    X = scoring.transform(prm, synth.rows(rows, seed=1000 + rank)).astype(np.float32)
+    bits, kw = sampler.sample_coalitions(30, nsamples, np.random.RandomState(0))
+    plan = KernelShapPlan(prm.coef, prm.intercept, bg, bits, kw, device=device.index)
+    x = torch.from_numpy(X).to(device)
+    phi = torch.empty_like(x)
+    abs_sum = torch.empty(32, dtype=torch.float64, device=device)
+    steps = max(3, min(args.steps, 10))
+
+    def sync():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, n):
+        for _ in range(3):
+            fn()
+        sync()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        sync()
+        t = torch.tensor([e0.elapsed_time(e1) / n], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    ms = timed(lambda: plan.explain_dev(x, phi=phi, abs_sum=abs_sum), steps)
+    sig = rows * len(bits) * n_bg
+    out = {
+        "workload": f"config3: Kernel SHAP nsamples={nsamples}, {n_bg}-row background, {rows} explained rows per GPU, "
+                    "shared coalition set, l1_reg=False, identity link, f=P(fraud)",
+        "value": rows * world / (ms * 1e-3), "unit": "explained rows/s", "ms_per_step": ms, "steps": steps,
+        "sigmoids_per_s": sig * world / (ms * 1e-3),
+        "gpu_launches_per_step": 2 * -(-rows // 8192),
+    }
+    # e2e through the host entry point (H2D of rows, D2H of phi inside the timed region)
+    hx, hphi = PinnedBuffer((rows, 30), np.float32), PinnedBuffer((rows, 30), np.float32)
+    hx.array[:] = X
+    import ctypes as C  # noqa: F401
+    from fraud_detection_b200 import _lib
+    habs = np.zeros(32)
+
+    def host_call():
+        _lib.check(_lib.lib.fdb_kshap_explain_host(plan._h, rows, _lib.np_ptr(hx.array), None, 0, _lib.np_ptr(hphi.array),
+                                                   _lib.np_ptr(habs)))
+    host_call()
+    sync()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        host_call()
+    dt = (time.perf_counter() - t0) / 3
+    t = torch.tensor([dt], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    out["e2e"] = {"value": rows * world / float(t.item()), "unit": "explained rows/s", "h2d_bytes_per_step": rows * 120,
+                  "d2h_bytes_per_step": rows * 120 + 256, "api": "fdb_kshap_explain_host (pinned host rows in, phi out)"}
+    plan.close()
+
+    # the reference's sampler: a different coalition set for every explained row
+    pr = args.kshap_per_row
+    rs = np.random.RandomState(1)
+    sets = [sampler.sample_coalitions(30, nsamples, rs) for _ in range(pr)]
+    plan2 = KernelShapPlan(prm.coef, prm.intercept, bg, np.stack([b for b, _ in sets]), np.stack([w for _, w in sets]),
+                           device=device.index)
+    x2, phi2 = x[:pr].contiguous(), torch.empty((pr, 30), dtype=torch.float32, device=device)
+    ms2 = timed(lambda: plan2.explain_dev(x2, phi=phi2), steps)
+    out["per_row_masks"] = {"rows": pr, "value": pr * world / (ms2 * 1e-3), "unit": "explained rows/s", "ms_per_step": ms2}
+    plan2.close()
+
+    # SFU roofline: sigmoid = ex2 + rcp = 2 MUFU ops; 16 MUFU lanes per SM per clock
+    sms = torch.cuda.get_device_properties(device).multi_processor_count
+    clock_hz = (sm_max_mhz or 1965) * 1e6
+    peak = 16.0 * sms * clock_hz
+    out["roofline"] = {"bound": "sfu", "achieved": 2.0 * sig / (ms * 1e-3) / 1e12, "peak": peak / 1e12, "unit": "T MUFU op/s",
+                       "frac": 2.0 * sig / (ms * 1e-3) / peak, "mufu_ops_per_sigmoid": 2,
+                       "peak_source": f"nominal 16 MUFU/clk/SM x {sms} SMs x {clock_hz / 1e9:.3f} GHz (no measured SFU peak on file)",
+                       "note": "whole step = K2 evaluator + K3 solve; the evaluator alone is ~84% of it"}
+    if rank == 0 and world == 1:
+        # CPU: the oracle restatement of shap.KernelExplainer on a handful of rows, extrapolated
+        from oracle import kernel_shap as ks
+        f = lambda A: scoring.predict_proba(prm, A)[:, 1]  # noqa: E731
+        n_cpu = args.kshap_cpu_rows
+        t0 = time.perf_counter()
+        ks.shap_values(f, X[:n_cpu].astype(np.float64), bg, nsamples=nsamples, l1_reg=False, random=np.random.RandomState(0))
+        dtc = time.perf_counter() - t0
+        out["cpu_baseline"] = {"value": n_cpu / dtc, "unit": "explained rows/s", "cores": 1, "kind": "port",
+                               "sample": f"{n_cpu} rows through oracle/kernel_shap.py (numpy restatement of shap.KernelExplainer, "
+                                         f"per-row sampling, one process; shap itself is not installable here) in {dtc:.1f}s; extrapolates "
+                                         f"to {rows / (n_cpu / dtc) / 3600:.1f} h for {rows} rows"}
+    return out
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -297,6 +406,9 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = ne * world * e2e_steps / float(t.item())
 
+    del hx, hp, hphi
+    kshap = None if args.no_kshap else bench_kernel_shap(args, torch, dist, device, rank, world, prm, clocks.max_mhz)
+
     if rank == 0:
         peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
         if os.path.exists(peaks_path):
@@ -319,6 +431,8 @@ def run_b200(args):
                          "algorithmic_bytes_per_launch": n * BYTES_PER_ROW, "peak_source": peak_src},
             "clocks": clocks.summary(),
         }
+        if kshap is not None:
+            line["kernel_shap"] = kshap
         if world == 1:
             cpu_threads = os.cpu_count() or 1
             v, secs, origin = time_cpu(args.cpu_rows, cpu_threads)
