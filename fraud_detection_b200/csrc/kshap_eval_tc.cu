@@ -6,21 +6,24 @@
 // never leaves the SM:
 //   A  (128 x 32, smem)  = [1 - z_m0 .. 1 - z_m29 | 1 | 0]           exactly 0/1 in f16/bf16
 //   B  (n_bg x 32, smem) = -log2e * [w_k bg_bk | c | 0]             split into 2 f16 (or 3 bf16) terms
-//   Bq (16 x 32, smem)   = rows 0..2: the 3-term split of [log2e w_k x_rk | -log2e sum_k w_k x_rk | 0]
-//   D  (TMEM, fp32)      = A B^T  (all split terms accumulate into the same columns) and A Bq^T
-// so that t[m][b] = D[m][b] + (Dq[m][0] + Dq[m][1] + Dq[m][2]) = -log2e * logit[m][b].  The epilogue
-// reads TMEM with tcgen05.ld (one coalition per thread = one TMEM lane), evaluates
-// sigmoid = rcp(1 + ex2(t)) on the SFU and keeps the running mean over b in a register; only
-// ey[r][m] (4 bytes per 128 x n_bg logits) goes to HBM.  Because A is exactly representable and the
+//   Bq (8 x 32, smem)    = 3-term split of [log2e w_k x_rk | -log2e sum_k w_k x_rk | 0], the SAME row 8 times;
+//                          its descriptor uses a row-group stride of 0, so the MMA sees that row broadcast
+//                          to every background column
+//   D  (TMEM, fp32)      = A B^T + A Bq^T   (all split terms accumulate into the same columns)
+// so that D[m][b] = -log2e * logit[m][b] leaves the tensor core finished.  The epilogue reads TMEM with
+// tcgen05.ld (one coalition per thread = one TMEM lane), evaluates sigmoid = 1 / (1 + ex2(D)) on the SFU -
+// four sigmoids share one reciprocal - and keeps the running mean over b in a register; only ey[r][m]
+// (4 bytes per 128 x n_bg logits) goes to HBM.  Because A is exactly representable and the
 // B splits carry >= 22 mantissa bits, the products are fp32-accurate although the MMA runs at
 // f16/bf16 rate.
 //
-// CTA = 12 warps, persistent, two independent pipelines g = 0,1 (each owns half of TMEM):
-//   warp g      producer : writes Bq for the item's row, bulk-copies (TMA, UBLKCP) the A tile image
-//   warp 2+g    MMA      : one lane issues tcgen05.mma / tcgen05.commit
-//   warps 4+4g..7+4g  epilogue: TMEM lane quarter (warp % 4), 32 coalitions per warp
+// CTA = 24 warps, persistent, four independent pipelines g = 0..3 (each owns 128 TMEM columns), so every
+// SM sub-partition always has four epilogue warps to hide SFU and TMEM latency:
+//   warp g           producer : writes Bq for the item's row, bulk-copies (TMA, UBLKCP) the A tile image
+//   warp 4+g         MMA      : one lane issues tcgen05.mma / tcgen05.commit
+//   warps 8+4g..11+4g epilogue: TMEM lane quarter (warp % 4), 32 coalitions per warp
 // The B operand stays resident in shared memory for the whole kernel.  Backgrounds wider than
-// 240 rows are processed in column chunks that reuse the pipeline's TMEM buffer.
+// 128 rows are processed in column chunks that reuse the pipeline's TMEM columns.
 
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
@@ -30,11 +33,12 @@
 
 namespace {
 
-constexpr int kThreadsTc = 384;
+constexpr int kPipes = 4;
+constexpr int kThreadsTc = (2 * kPipes + 4 * kPipes) * 32;   // 768
 constexpr int kATileBytes = 128 * 32 * 2;     // 8192
-constexpr int kBqBytes = 16 * 32 * 2;         // 1024
+constexpr int kBqBytes = 3 * 512;             // 3 splits x (4 k-chunks x 8 identical rows x 16 B)
 constexpr int kAStages = 2;
-constexpr int kPipeCols = 256;                // TMEM columns per pipeline
+constexpr int kPipeCols = 128;                // TMEM columns per pipeline
 constexpr uint32_t kLbo = 128;                // K-direction core-matrix stride (bytes)
 constexpr uint32_t kSbo = 512;                // 8-row-group stride (bytes)
 
@@ -48,19 +52,20 @@ struct TcParams {
     int64_t row_offset;
     int n_rows, n_sets, tiles, m_pad;
     int n_bg, nb_pad, nsplit, fmt;
-    int n_chunks, chunk_cols, buf_cols, nbuf;
+    int n_chunks, chunk_cols;
+    int wide;                                  // logit link: keep relative accuracy of tiny sigmoids
     float inv_bg;
 };
 
 struct PipeBars {
     uint64_t a_full[kAStages];
     uint64_t a_empty[kAStages];
-    uint64_t t_full[2];
-    uint64_t t_empty[2];
+    uint64_t t_full;
+    uint64_t t_empty;
 };
 
 struct TcBars {
-    PipeBars pipe[2];
+    PipeBars pipe[kPipes];
     uint64_t b_full;
     uint32_t tmem_base;
 };
@@ -73,39 +78,103 @@ __device__ __forceinline__ float from_h16(uint16_t h, int fmt) {
 }
 
 
-// smem carve-up (dynamic): [B image][A stages pipe0][A stages pipe1][Bq stages pipe0][Bq stages pipe1][barriers]
+// 2^x on the FMA pipe (Cody-Waite split + degree-5 minimax, max rel. error 2.3e-7 ~ ex2.approx), x in [-120, 31].
+// Used for a fixed share of the exponentials so the SFU (16 lanes/SM) and the FMA pipe (128 lanes/SM) finish together.
+__device__ __forceinline__ float ex2_poly(float x) {
+    const float magic = 12582912.f;                 // 1.5 * 2^23: rounds x to an integer held in the low mantissa bits
+    const float r = x + magic;
+    const float f = x - (r - magic);                // [-0.5, 0.5]
+    float p = 0.001327647129073739f;
+    p = fmaf(p, f, 0.009675540961325169f);
+    p = fmaf(p, f, 0.05550713092088699f);
+    p = fmaf(p, f, 0.24022120237350464f);
+    p = fmaf(p, f, 0.6931469440460205f);
+    p = fmaf(p, f, 1.0000001192092896f);
+    return __int_as_float(__float_as_int(p) + (__float_as_int(r) << 23));
+}
+
+__device__ __forceinline__ void release_tmem(uint64_t* bar, int lane) {
+    ptx::tc_fence_before();
+    __syncwarp();
+    if (lane == 0) ptx::mbar_arrive(bar);
+}
+
+// Share of the exponentials evaluated by ex2_poly instead of the SFU: bit i of the mask = element i of every
+// 8.  Measured on B200: with four epilogue warps per sub-partition the kernel is SFU-bound, and every
+// polynomial costs ~9 issue slots, so only a small share pays.
+#ifndef FDB_K2_POLY_MASK
+#define FDB_K2_POLY_MASK 0x00
+#endif
+constexpr uint32_t kPolyMask8 = FDB_K2_POLY_MASK;
+
+// sum_i sigmoid over 16 accumulator columns, t_i = D[m][b_i] = -log2e * logit.
+// Four sigmoids share ONE reciprocal: s0+s1+s2+s3 = (n01 p23 + n23 p01) / (p01 p23) with d_i = 1 + 2^t_i,
+// n_ab = d_a + d_b, p_ab = d_a d_b.  t is clamped to 30 so the product of four d stays below 2^121;
+// the clamp changes a sigmoid by < 1e-9 absolute.  Masked columns (beyond the background) are pinned at the
+// clamp, where the sigmoid is 1 / (1 + 2^30), and that known amount is subtracted again (no cancellation).
+template <bool MASKED, bool WIDE>
+__device__ __forceinline__ float sigmoid_sum16(const uint32_t (&r)[16], int nvalid) {
+    // WIDE (logit link): sigmoids down to ~1e-19 must keep their relative accuracy because logit(ey) is taken
+    // afterwards, so only TWO sigmoids share a reciprocal and the clamp moves to 62 (d0 d1 < 2^125).
+    constexpr float kClamp = WIDE ? 62.f : 30.f;
+    constexpr float kFloor = WIDE ? 2.16840434e-19f : 9.31322574e-10f;   // sigmoid at the clamp, 1 / (1 + 2^clamp)
+    float sum = 0.f;
+#pragma unroll
+    for (int q = 0; q < 16; q += 4) {
+        float d[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float t = fminf(__uint_as_float(r[q + i]), kClamp);
+            if (MASKED && q + i >= nvalid) t = kClamp;
+            const float e = ((kPolyMask8 >> ((q + i) & 7)) & 1u) ? ex2_poly(fmaxf(t, -120.f)) : ptx::ex2_approx(t);
+            d[i] = 1.0f + e;
+        }
+        const float n01 = d[0] + d[1], p01 = d[0] * d[1];
+        const float n23 = d[2] + d[3], p23 = d[2] * d[3];
+        if (WIDE) {
+            sum = fmaf(n01, ptx::rcp_approx(p01), sum);
+            sum = fmaf(n23, ptx::rcp_approx(p23), sum);
+        } else {
+            const float num = fmaf(n01, p23, n23 * p01);
+            sum = fmaf(num, ptx::rcp_approx(p01 * p23), sum);
+        }
+    }
+    return MASKED ? sum - (float)(16 - nvalid) * kFloor : sum;   // masked columns sit at the clamp; take them out again
+}
+
+template <bool WIDE>
+__device__ __forceinline__ float sigmoid_group(const uint32_t (&r)[16], int nvalid) {
+    return nvalid >= 16 ? sigmoid_sum16<false, WIDE>(r, 16) : sigmoid_sum16<true, WIDE>(r, nvalid);
+}
+
+// smem carve-up (dynamic): [B image][A stages x pipes][Bq stages x pipes][barriers]
 __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     const uint32_t b_bytes = (uint32_t)p.nsplit * p.nb_pad * 64;
     unsigned char* sB = smem;
-    unsigned char* sA = sB + b_bytes;                                   // [2 pipes][kAStages][8192]
-    unsigned char* sBq = sA + 2 * kAStages * kATileBytes;               // [2 pipes][kAStages][1024]
-    TcBars* bars = reinterpret_cast<TcBars*>(sBq + 2 * kAStages * kBqBytes);
+    unsigned char* sA = sB + b_bytes;                                       // [pipes][kAStages][8192]
+    unsigned char* sBq = sA + kPipes * kAStages * kATileBytes;              // [pipes][kAStages][1536]
+    TcBars* bars = reinterpret_cast<TcBars*>(sBq + kPipes * kAStages * kBqBytes);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int64_t n_items = (int64_t)p.n_rows * p.tiles;
-    const int64_t stride = (int64_t)gridDim.x * 2;
+    const int64_t stride = (int64_t)gridDim.x * kPipes;
 
     // ---- one-time set-up -----------------------------------------------------------------
-    for (uint32_t i = threadIdx.x; i < 2 * kAStages * kBqBytes / 16; i += blockDim.x)
-        reinterpret_cast<uint4*>(sBq)[i] = make_uint4(0, 0, 0, 0);     // rows 3..15 of every Bq stay zero
     if (threadIdx.x == 0) {
-        for (int g = 0; g < 2; ++g) {
+        for (int g = 0; g < kPipes; ++g) {
             for (int s = 0; s < kAStages; ++s) {
                 ptx::mbar_init(&bars->pipe[g].a_full[s], 1);
                 ptx::mbar_init(&bars->pipe[g].a_empty[s], 1);
             }
-            for (int b = 0; b < 2; ++b) {
-                ptx::mbar_init(&bars->pipe[g].t_full[b], 1);
-                ptx::mbar_init(&bars->pipe[g].t_empty[b], 4);
-            }
+            ptx::mbar_init(&bars->pipe[g].t_full, 1);
+            ptx::mbar_init(&bars->pipe[g].t_empty, 4);
         }
         ptx::mbar_init(&bars->b_full, 1);
         ptx::mbar_fence_init();
     }
-    if (warp == 2) ptx::tmem_alloc(&bars->tmem_base, 512);
-    ptx::fence_proxy_async_smem();
+    if (warp == kPipes) ptx::tmem_alloc(&bars->tmem_base, 512);
     ptx::tc_fence_before();
     __syncthreads();
     ptx::tc_fence_after();
@@ -120,34 +189,38 @@ __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcPa
         }
     }
 
-    if (warp < 2) {
+    if (warp < kPipes) {
         // =================================================================== producer of pipeline g
         const int g = warp;
         PipeBars& pb = bars->pipe[g];
         const float wk = lane < FDB_F ? p.wq[lane] : 0.f;
         int k = 0;
-        for (int64_t it = (int64_t)blockIdx.x * 2 + g; it < n_items; it += stride, ++k) {
+        for (int64_t it = (int64_t)blockIdx.x * kPipes + g; it < n_items; it += stride, ++k) {
             const int s = k % kAStages;
             const uint32_t ph = (k / kAStages) & 1;
             const int row = (int)(it / p.tiles);
             const int tile = (int)(it % p.tiles);
             const int set = p.set_idx ? p.set_idx[row] : (p.n_sets == 1 ? 0 : (int)((p.row_offset + row) % p.n_sets));
-            ptx::mbar_wait(&pb.a_empty[s], ph ^ 1);
-            // Bq rows 0..2 = 3-term split of [log2e w_k x_k (k<30) | -log2e sum_k w_k x_k | 0]
+            // Bq = 3-term split of [log2e w_k x_k (k<30) | -log2e sum_k w_k x_k | 0], each term stored as 8 equal rows
             float v = lane < FDB_F ? 1.4426950408889634f * wk * p.x[(size_t)row * FDB_F + lane] : 0.f;
             v = fminf(fmaxf(v, -30000.f), 30000.f);
             float tot = v;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
             if (lane == 30) v = fminf(fmaxf(-tot, -60000.f), 60000.f);
-            unsigned char* bq = sBq + (size_t)(g * kAStages + s) * kBqBytes + (lane >> 3) * 128 + (lane & 7) * 2;
+            uint16_t h[3];
             float rem = v;
 #pragma unroll
             for (int j = 0; j < 3; ++j) {
-                const uint16_t h = to_h16(rem, p.fmt);
-                *reinterpret_cast<uint16_t*>(bq + j * 16) = h;
-                rem -= from_h16(h, p.fmt);
+                h[j] = to_h16(rem, p.fmt);
+                rem -= from_h16(h[j], p.fmt);
             }
+            ptx::mbar_wait(&pb.a_empty[s], ph ^ 1);
+            unsigned char* bq = sBq + (size_t)(g * kAStages + s) * kBqBytes + (lane >> 3) * 128 + (lane & 7) * 2;
+#pragma unroll
+            for (int j = 0; j < 3; ++j)
+#pragma unroll
+                for (int rr = 0; rr < 8; ++rr) *reinterpret_cast<uint16_t*>(bq + j * 512 + rr * 16) = h[j];
             ptx::fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) {
@@ -157,30 +230,28 @@ __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcPa
                               kATileBytes, &pb.a_full[s]);
             }
         }
-    } else if (warp < 4) {
+    } else if (warp < 2 * kPipes) {
         // =================================================================== MMA issuer of pipeline g
-        const int g = warp - 2;
+        const int g = warp - kPipes;
         PipeBars& pb = bars->pipe[g];
         if (lane == 0) {
             ptx::mbar_wait(&bars->b_full, 0);
             const uint32_t a0 = ptx::smem_u32(sA + (size_t)g * kAStages * kATileBytes);
             const uint32_t q0 = ptx::smem_u32(sBq + (size_t)g * kAStages * kBqBytes);
             const uint32_t b0 = ptx::smem_u32(sB);
-            const uint32_t idesc_q = ptx::make_idesc_f16(p.fmt, 128, 16);
+            const uint32_t d = tmem_base + g * kPipeCols;
             int k = 0;
-            int64_t job = 0;
-            for (int64_t it = (int64_t)blockIdx.x * 2 + g; it < n_items; it += stride, ++k) {
+            uint32_t job = 0;
+            for (int64_t it = (int64_t)blockIdx.x * kPipes + g; it < n_items; it += stride, ++k) {
                 const int s = k % kAStages;
                 const uint32_t ph = (k / kAStages) & 1;
                 ptx::mbar_wait(&pb.a_full[s], ph);
                 ptx::tc_fence_after();
                 const uint32_t a_addr = a0 + s * kATileBytes;
+                const uint32_t q_addr = q0 + s * kBqBytes;
                 for (int c = 0; c < p.n_chunks; ++c, ++job) {
-                    const int buf = (int)(job % p.nbuf);
-                    const uint32_t tph = (uint32_t)((job / p.nbuf) & 1);
-                    ptx::mbar_wait(&pb.t_empty[buf], tph ^ 1);
+                    ptx::mbar_wait(&pb.t_empty, (job & 1) ^ 1);
                     ptx::tc_fence_after();
-                    const uint32_t d = tmem_base + g * kPipeCols + buf * p.buf_cols;
                     const int col0 = c * p.chunk_cols;
                     const int nc = (p.nb_pad - col0) < p.chunk_cols ? (p.nb_pad - col0) : p.chunk_cols;
                     const uint32_t idesc = ptx::make_idesc_f16(p.fmt, 128, nc);
@@ -195,15 +266,17 @@ __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcPa
                             acc = true;
                         }
                     }
-                    if (c == 0) {
+#pragma unroll
+                    for (int sp = 0; sp < 3; ++sp) {
 #pragma unroll
                         for (int ks = 0; ks < 2; ++ks) {
                             const uint64_t ad = ptx::make_desc_kmajor_noswizzle(a_addr + ks * 256, kLbo, kSbo);
-                            const uint64_t qd = ptx::make_desc_kmajor_noswizzle(q0 + s * kBqBytes + ks * 256, kLbo, kSbo);
-                            ptx::mma_f16(d + (p.buf_cols - 16), ad, qd, idesc_q, ks > 0);
+                            // row-group stride 0: the 8 stored rows are reused for every group of 8 columns
+                            const uint64_t qd = ptx::make_desc_kmajor_noswizzle(q_addr + sp * 512 + ks * 256, kLbo, 0);
+                            ptx::mma_f16(d, ad, qd, idesc, true);
                         }
                     }
-                    ptx::mma_commit(&pb.t_full[buf]);
+                    ptx::mma_commit(&pb.t_full);
                 }
                 ptx::mma_commit(&pb.a_empty[s]);
             }
@@ -211,47 +284,37 @@ __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcPa
         __syncwarp();
     } else {
         // =================================================================== epilogue of pipeline g
-        const int g = (warp - 4) >> 2;
+        const int g = (warp - 2 * kPipes) >> 2;
         const int qd = warp & 3;                     // TMEM lane quarter this warp may read
         PipeBars& pb = bars->pipe[g];
-        const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16) + g * kPipeCols;
-        int64_t job = 0;
-        for (int64_t it = (int64_t)blockIdx.x * 2 + g; it < n_items; it += stride) {
+        const uint32_t ta = tmem_base + ((uint32_t)(qd * 32) << 16) + g * kPipeCols;
+        uint32_t job = 0;
+        for (int64_t it = (int64_t)blockIdx.x * kPipes + g; it < n_items; it += stride) {
             const int row = (int)(it / p.tiles);
             const int tile = (int)(it % p.tiles);
-            float acc = 0.f, sq = 0.f;
+            float acc = 0.f;
             for (int c = 0; c < p.n_chunks; ++c, ++job) {
-                const int buf = (int)(job % p.nbuf);
-                const uint32_t tph = (uint32_t)((job / p.nbuf) & 1);
-                ptx::mbar_wait(&pb.t_full[buf], tph);
+                ptx::mbar_wait(&pb.t_full, job & 1);
                 ptx::tc_fence_after();
-                const uint32_t ta = lane_base + buf * p.buf_cols;
-                if (c == 0) {
-                    uint32_t r4[4];
-                    ptx::tmem_ld4(ta + (p.buf_cols - 16), r4);
-                    ptx::tmem_ld_wait();
-                    sq = __uint_as_float(r4[0]) + __uint_as_float(r4[1]) + __uint_as_float(r4[2]);
-                }
-                const int col0 = c * p.chunk_cols;
-                int valid = p.n_bg - col0;
+                int valid = p.n_bg - c * p.chunk_cols;
                 if (valid > p.chunk_cols) valid = p.chunk_cols;
-                for (int cc = 0; cc < valid; cc += 16) {
-                    uint32_t r[16];
-                    ptx::tmem_ld16(ta + cc, r);
+                // double-buffered TMEM reads: the load of group g+1 is in flight while group g is evaluated; the
+                // accumulator columns are handed back to the MMA warp as soon as the last one has been read
+                const int ngroups = (valid + 15) >> 4;
+                uint32_t ra[16], rb[16];
+                ptx::tmem_ld16(ta, ra);
+                for (int gi = 0; gi < ngroups; gi += 2) {
                     ptx::tmem_ld_wait();
-                    if (cc + 16 <= valid) {
-#pragma unroll
-                        for (int i = 0; i < 16; ++i)
-                            acc += ptx::rcp_approx(1.0f + ptx::ex2_approx(__uint_as_float(r[i]) + sq));
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 16; ++i)
-                            if (cc + i < valid) acc += ptx::rcp_approx(1.0f + ptx::ex2_approx(__uint_as_float(r[i]) + sq));
+                    if (gi + 1 < ngroups) ptx::tmem_ld16(ta + (gi + 1) * 16, rb);
+                    else release_tmem(&pb.t_empty, lane);
+                    acc += p.wide ? sigmoid_group<true>(ra, valid - gi * 16) : sigmoid_group<false>(ra, valid - gi * 16);
+                    if (gi + 1 < ngroups) {
+                        ptx::tmem_ld_wait();
+                        if (gi + 2 < ngroups) ptx::tmem_ld16(ta + (gi + 2) * 16, ra);
+                        else release_tmem(&pb.t_empty, lane);
+                        acc += p.wide ? sigmoid_group<true>(rb, valid - (gi + 1) * 16) : sigmoid_group<false>(rb, valid - (gi + 1) * 16);
                     }
                 }
-                ptx::tc_fence_before();
-                __syncwarp();
-                if (lane == 0) ptx::mbar_arrive(&pb.t_empty[buf]);
             }
             p.ey[(size_t)row * p.m_pad + tile * 128 + qd * 32 + lane] = acc * p.inv_bg;
         }
@@ -259,7 +322,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcPa
 
     ptx::tc_fence_before();
     __syncthreads();
-    if (warp == 2) {
+    if (warp == kPipes) {
         ptx::tc_fence_after();
         ptx::tmem_dealloc(tmem_base, 512);
     }
@@ -273,11 +336,11 @@ int fdb_kshap_launch_eval_tc(fdb_kshap_plan* pl, cudaStream_t st, const float* x
     p.x = x; p.set_idx = set_idx; p.aimg = pl->d_aimg; p.bimg = pl->d_bimg; p.wq = pl->d_wq; p.ey = ey;
     p.row_offset = row_offset; p.n_rows = n_rows; p.n_sets = pl->n_sets; p.tiles = pl->m_pad / 128; p.m_pad = pl->m_pad;
     p.n_bg = pl->n_bg; p.nb_pad = pl->nb_pad; p.nsplit = pl->nsplit; p.fmt = pl->fmt;
-    p.n_chunks = (pl->nb_pad + 239) / 240;
+    p.n_chunks = (pl->nb_pad + kPipeCols - 1) / kPipeCols;
     p.chunk_cols = (((pl->nb_pad + p.n_chunks - 1) / p.n_chunks) + 15) & ~15;
-    if (p.chunk_cols + 16 <= 128) { p.buf_cols = 128; p.nbuf = 2; } else { p.buf_cols = 256; p.nbuf = 1; }
     p.inv_bg = 1.0f / (float)pl->n_bg;
-    const size_t smem = (size_t)pl->nsplit * pl->nb_pad * 64 + 2 * kAStages * (kATileBytes + kBqBytes) + sizeof(TcBars) + 64;
+    p.wide = pl->link == 1;
+    const size_t smem = (size_t)pl->nsplit * pl->nb_pad * 64 + kPipes * kAStages * (kATileBytes + kBqBytes) + sizeof(TcBars) + 64;
     FDB_REQUIRE(smem <= 227 * 1024, FDB_ERR_ARG, "background of %d rows with %d operand splits needs %zu bytes of shared memory",
                 pl->n_bg, pl->nsplit, smem);
     static size_t configured = 0;
@@ -286,7 +349,7 @@ int fdb_kshap_launch_eval_tc(fdb_kshap_plan* pl, cudaStream_t st, const float* x
         configured = smem;
     }
     const int64_t n_items = (int64_t)n_rows * p.tiles;
-    int64_t grid = (n_items + 1) / 2;
+    int64_t grid = (n_items + kPipes - 1) / kPipes;
     if (grid > pl->ctx->sm_count) grid = pl->ctx->sm_count;
     if (grid < 1) grid = 1;
     kshap_eval_tc_kernel<<<(int)grid, kThreadsTc, smem, st>>>(p);
