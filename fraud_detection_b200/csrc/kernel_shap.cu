@@ -172,21 +172,33 @@ __global__ void __launch_bounds__(128) kshap_wls_solve(
         const uint32_t* sb = bits + (size_t)s * m_pad;
         const float* sk = kw + (size_t)s * m_pad;
         const float* er = ey + (size_t)r * m_pad;
-        float g = 0.f;
+        // X'W y: every lane owns one coalition per step and keeps all 29 partial sums in registers
+        // (x_mj * v = zp_j ? vp : 0 after folding the sign of the eliminated feature into vp / zp) ...
+        float gj[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) gj[j] = 0.f;
         for (int m0 = 0; m0 < m_pad; m0 += 32) {
             const uint32_t b = sb[m0 + lane];
             const float kwv = sk[m0 + lane];
-            float v = kwv != 0.f ? kwv * (link_apply(er[m0 + lane], link) - lnull) : 0.f;
+            const float v = kwv != 0.f ? kwv * (link_apply(er[m0 + lane], link) - lnull) : 0.f;
             const bool z29 = (b >> 29) & 1u;
-            const float vp = z29 ? -v : v;          // x_mj * v = zp_j ? vp : 0
+            const float vp = z29 ? -v : v;
             const uint32_t bp = z29 ? ~b : b;
 #pragma unroll
-            for (int t = 0; t < 32; ++t) {
-                const float vt = __shfl_sync(0xffffffffu, vp, t);
-                const uint32_t bt = __shfl_sync(0xffffffffu, bp, t);
-                g += ((bt >> lane) & 1u) ? vt : 0.f;
+            for (int j = 0; j < kNV; ++j) gj[j] += ((bp >> j) & 1u) ? vp : 0.f;
+        }
+        // ... then a butterfly transpose-reduce leaves the total of column j in lane j (31 shuffles)
+#pragma unroll
+        for (int half = 16; half >= 1; half >>= 1) {
+            const bool up = (lane & half) != 0;
+#pragma unroll
+            for (int i = 0; i < half; ++i) {
+                const float send = up ? gj[i] : gj[i + half];
+                const float keep = up ? gj[i + half] : gj[i];
+                gj[i] = keep + __shfl_xor_sync(0xffffffffu, send, half);
             }
         }
+        const float g = gj[0];
         const float rhs = lane < kNV ? g - d * c2[(size_t)s * 32 + lane] : 0.f;
         const float* ai = ainv + (size_t)s * kNV * 32;
         float w = 0.f;

@@ -1,0 +1,87 @@
+#!/usr/bin/env python
+"""Config 5 - serving micro-batch latency through the drop-in classes (H2D/D2H included).
+
+Times exactly the brackets the reference instruments with Prometheus histograms:
+  * ``api_inference_duration_seconds``  api/app.py:208-240: MODEL.predict(X) + MODEL.predict_proba(X)
+    on a pandas DataFrame of scaled features (after SCALER.transform at :194);
+  * ``xai_task_duration_seconds``       api/worker.py:74-75: EXPL.shap_values(X) on a DataFrame;
+for batch sizes 1..4096, p50/p99 over N calls, next to live sklearn (+ the numpy LinearExplainer
+restatement) in the same loop on the same host.  HTTP, Redis and Postgres are not part of the
+bracket (and not installable here).
+
+    python tools/serving_bench.py [--calls 10000] [--out profiles/r01/serving_latency.json]
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+import warnings
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def _percentiles(fn, calls, warm=50):
+    for _ in range(warm):
+        fn()
+    ts = np.empty(calls)
+    for i in range(calls):
+        t0 = time.perf_counter()
+        fn()
+        ts[i] = time.perf_counter() - t0
+    return {"p50_ms": float(np.percentile(ts, 50) * 1e3), "p99_ms": float(np.percentile(ts, 99) * 1e3),
+            "mean_ms": float(ts.mean() * 1e3)}
+
+
+def run(batches=(1, 2, 4, 8, 16, 32, 64, 128, 256, 512, 1024, 2048, 4096), calls=10000, device=None):
+    import pandas as pd
+    from fraud_detection_b200 import B200LinearExplainer, wrap
+    from oracle import linear_shap, scoring, synth
+
+    warnings.filterwarnings("ignore")
+    scaler_sk, model_sk, origin = scoring.live_estimators()
+    scaler, model = wrap(scaler_sk, device=device), wrap(model_sk, device=device)
+    names = list(getattr(scaler_sk, "feature_names_in_", synth.FEATURE_NAMES))
+    zero_bg = pd.DataFrame([[0] * 30], columns=names)
+    expl = B200LinearExplainer(model, zero_bg, device=device)            # api/worker.py:52-53
+    coef = model_sk.coef_[0]
+    out = {"estimators": origin, "calls": calls, "host_cpus": os.cpu_count(), "rows": []}
+    for bsz in batches:
+        raw = pd.DataFrame(synth.rows(bsz, seed=bsz))
+        Xs = pd.DataFrame(scaler_sk.transform(raw), columns=names)        # api/app.py:194-197
+        Xw = pd.DataFrame(raw.values, columns=[f"feature_{i}" for i in range(30)])   # api/worker.py:70
+        n = max(200, calls // max(1, bsz // 64)) if bsz > 64 else calls
+        row = {"batch": bsz, "calls": n}
+        row["b200_predict_bracket"] = _percentiles(lambda: (model.predict(Xs), model.predict_proba(Xs)), n)
+        row["b200_score_rows"] = _percentiles(lambda: model.score_rows(Xs), n)
+        row["sklearn_predict_bracket"] = _percentiles(lambda: (model_sk.predict(Xs), model_sk.predict_proba(Xs)), n)
+        row["b200_shap_bracket"] = _percentiles(lambda: expl.shap_values(Xw), n)
+        row["cpu_shap_bracket"] = _percentiles(lambda: linear_shap.shap_values(coef, np.zeros(30), Xw), n)
+        row["b200_transform"] = _percentiles(lambda: scaler.transform(raw), n)
+        row["sklearn_transform"] = _percentiles(lambda: scaler_sk.transform(raw), n)
+        out["rows"].append(row)
+    return out
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--calls", type=int, default=10000)
+    ap.add_argument("--out", default="")
+    a = ap.parse_args()
+    res = run(calls=a.calls)
+    txt = json.dumps(res, indent=1)
+    if a.out:
+        os.makedirs(os.path.dirname(a.out), exist_ok=True)
+        with open(a.out, "w") as fh:
+            fh.write(txt)
+    for r in res["rows"]:
+        print(f"batch {r['batch']:5d}: predict+proba  b200 p50 {r['b200_predict_bracket']['p50_ms']:.3f} p99 {r['b200_predict_bracket']['p99_ms']:.3f} ms"
+              f" | one-pass {r['b200_score_rows']['p50_ms']:.3f} | sklearn p50 {r['sklearn_predict_bracket']['p50_ms']:.3f} p99 {r['sklearn_predict_bracket']['p99_ms']:.3f}"
+              f" || shap b200 p50 {r['b200_shap_bracket']['p50_ms']:.3f} p99 {r['b200_shap_bracket']['p99_ms']:.3f} | cpu p50 {r['cpu_shap_bracket']['p50_ms']:.3f}")
