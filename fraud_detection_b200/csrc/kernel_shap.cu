@@ -248,7 +248,7 @@ void free_plan(fdb_kshap_plan* p) {
     if (!p) return;
     cudaFree(p->d_bits); cudaFree(p->d_kw); cudaFree(p->d_P); cudaFree(p->d_wq); cudaFree(p->d_bimg); cudaFree(p->d_aimg);
     cudaFree(p->d_ainv); cudaFree(p->d_c2); cudaFree(p->d_status); cudaFree(p->d_ey); cudaFree(p->d_x); cudaFree(p->d_phi);
-    cudaFree(p->d_set); cudaFree(p->d_abs);
+    cudaFree(p->d_set); cudaFree(p->d_abs); cudaFree(p->d_E); cudaFree(p->d_eoff);
     delete p;
 }
 
@@ -372,6 +372,7 @@ extern "C" int fdb_kshap_plan_create(fdb_ctx* ctx, const double* coef, double in
         fdb_set_error("kernel-SHAP plan creation failed: %s", cudaGetErrorString(e));
         rc = e == cudaErrorMemoryAllocation ? FDB_ERR_NOMEM : FDB_ERR_CUDA;
     }
+    if (rc == FDB_OK && n_sets == 1) rc = fdb_kshap_build_factored(p, bg);
     if (rc != FDB_OK) { free_plan(p); return rc; }
     *out = p;
     return FDB_OK;
@@ -403,7 +404,10 @@ extern "C" int fdb_kshap_explain_dev(fdb_kshap_plan* p, void* stream, int64_t n_
     FDB_REQUIRE(p != nullptr, FDB_ERR_ARG, "plan is NULL");
     FDB_REQUIRE(n_rows >= 0, FDB_ERR_ARG, "n_rows is negative");
     FDB_REQUIRE(n_rows == 0 || (x && phi), FDB_ERR_ARG, "x / phi is NULL");
-    FDB_REQUIRE(evaluator == FDB_KSHAP_EVAL_TC || evaluator == FDB_KSHAP_EVAL_SIMT, FDB_ERR_ARG, "unknown evaluator %d", evaluator);
+    FDB_REQUIRE(evaluator >= FDB_KSHAP_EVAL_AUTO && evaluator <= FDB_KSHAP_EVAL_FACTORED, FDB_ERR_ARG, "unknown evaluator %d", evaluator);
+    if (evaluator == FDB_KSHAP_EVAL_AUTO) evaluator = p->n_sets == 1 ? FDB_KSHAP_EVAL_FACTORED : FDB_KSHAP_EVAL_TC;
+    FDB_REQUIRE(evaluator != FDB_KSHAP_EVAL_FACTORED || p->n_sets == 1, FDB_ERR_ARG,
+                "the factored evaluator needs a plan with exactly one coalition set (this plan has %d)", p->n_sets);
     cudaStream_t st = (cudaStream_t)stream;
     if (n_rows == 0) {
         if (abs_sum) FDB_CUDA(cudaMemsetAsync(abs_sum, 0, 32 * sizeof(double), st));
@@ -416,6 +420,9 @@ extern "C" int fdb_kshap_explain_dev(fdb_kshap_plan* p, void* stream, int64_t n_
         const int32_t* sb = set_idx ? set_idx + r0 : nullptr;
         if (evaluator == FDB_KSHAP_EVAL_TC) {
             int rc = fdb_kshap_launch_eval_tc(p, st, xb, r0, nb, sb, p->d_ey);
+            if (rc != FDB_OK) return rc;
+        } else if (evaluator == FDB_KSHAP_EVAL_FACTORED) {
+            int rc = fdb_kshap_launch_eval_fx(p, st, xb, nb, p->d_ey);
             if (rc != FDB_OK) return rc;
         } else {
             dim3 grid(p->m_pad / 128, nb);

@@ -1,0 +1,375 @@
+// K2f - factored Kernel SHAP evaluator for a SHARED coalition set (sm_100a, tcgen05 + TMEM + TMA).
+//
+// With one coalition set for every explained row, the background part of the logit does not depend on the
+// row:  logit[r][m][b] = G[m][b] + c + s[r][m],  G = ((1-Z) diag(w)) bg^T,  s[r][m] = sum_k z_mk w_k x_rk.
+// So  2^(-log2e logit) = E[m][b] * u[r][m]  with  E = 2^(-log2e (G + c) - o_m)  built ONCE per plan and
+// u = 2^(-log2e s + o_m)  one exponential per (row, coalition) instead of one per (row, coalition, background):
+//     ey[r][m] = mean_b 1 / (1 + E[m][b] u[r][m])
+// (o_m centres the exponents of coalition m so E and u stay inside fp32 range.)
+//
+// The per-row term is a GEMM and runs on the tensor cores:  D[r][m] = Q[r][:] . Abar[m][:]  with
+//   Q    (128 rows x 32, smem, A operand) = 3-term f16/bf16 split of [log2e w_k x_rk | -log2e sum_k w_k x_rk | 0]
+//   Abar (128 coalitions x 32, smem, B operand) = [1 - z_mk | 1 | 0]   (the same tile image K2 uses as A)
+//   D    (TMEM, fp32, lane = explained row, column = coalition) = -log2e s[r][m]
+// Each compute thread owns one explained row (TMEM lane) and 32 coalitions; E[m][b] is the same for the
+// whole warp, so it is read from shared memory as a broadcast LDS.128 and the inner loop is
+//   d = min(fma(E, u, 1), 2^30);  four d share one reciprocal       (4.5 issue slots, 0.25 SFU ops per sigmoid)
+// against 6.25 issue slots and 1.25 SFU ops in the general evaluator.  E streams through a double-buffered
+// TMA ring in background chunks of <= 128 columns; partial sums stay in registers across chunks.
+//
+// CTA = 20 warps, persistent, one per SM; work unit = (block of 128 rows, tile of 128 coalitions):
+//   warp 0 (one lane)  TMA: coalition tile image per unit, E chunks
+//   warp 1 (one lane)  tcgen05.mma issue (6 per unit) + commits
+//   warps 2-3          build the Q block (x rows -> scaled, split, canonical K-major layout)
+//   warps 4-19         compute: TMEM lane quarter = warp % 4, coalition group = (warp - 4) / 4
+
+#include <new>
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include "kshap_internal.cuh"
+#include "ptx_sm100.cuh"
+
+namespace {
+
+constexpr int kFxThreads = 640;
+constexpr int kFxComputeWarps = 16;
+constexpr int kTileBytes = 128 * 32 * 2;        // 8192: one 128 x 32 operand image
+constexpr int kQBytes = 3 * kTileBytes;          // three split terms
+constexpr int kEStageBytes = 128 * 128 * 4;      // 65536: 128 coalitions x <= 128 background columns
+constexpr uint32_t kLbo = 128, kSbo = 512;
+
+struct FxParams {
+    const float* x;
+    const uint16_t* zimg;      // coalition tile images (plan->d_aimg, set 0)
+    const float* E;            // [tile][chunk][128][cbs]
+    const float* eoff;         // [m_pad] exponent centre o_m
+    const float* wq;
+    float* ey;
+    int n_rows, tiles, m_pad, n_bg, fmt;
+    int n_chunks;              // background chunks of 128 columns (last one narrower)
+    int wide;
+    float inv_bg;
+};
+
+struct FxBars {
+    uint64_t zq_full[2], zq_empty[2], t_full[2], t_empty[2], e_full[2], e_empty[2];
+    uint32_t tmem_base;
+};
+
+__device__ __forceinline__ uint16_t fx_to_h16(float v, int fmt) {
+    return fmt == 0 ? __half_as_ushort(__float2half_rn(v)) : __bfloat16_as_ushort(__float2bfloat16_rn(v));
+}
+__device__ __forceinline__ float fx_from_h16(uint16_t h, int fmt) {
+    return fmt == 0 ? __half2float(__ushort_as_half(h)) : __bfloat162float(__ushort_as_bfloat16(h));
+}
+
+// sum over one background chunk for one (row, coalition): erow points at E[m][chunk columns] in smem (same
+// address in every lane -> broadcast loads).  WIDE: logit link, two sigmoids per reciprocal, clamp 2^62.
+template <bool WIDE>
+__device__ __forceinline__ float chunk_sum(const float* __restrict__ erow, int nquads, int ntail, float u) {
+    constexpr float kClamp = WIDE ? 4.611686018427388e18f : 1073741824.f;
+    float s = 0.f;
+#pragma unroll 4
+    for (int q = 0; q < nquads; ++q) {
+        const float4 e = *reinterpret_cast<const float4*>(erow + 4 * q);
+        const float d0 = fminf(fmaf(e.x, u, 1.0f), kClamp), d1 = fminf(fmaf(e.y, u, 1.0f), kClamp);
+        const float d2 = fminf(fmaf(e.z, u, 1.0f), kClamp), d3 = fminf(fmaf(e.w, u, 1.0f), kClamp);
+        const float n01 = d0 + d1, p01 = d0 * d1, n23 = d2 + d3, p23 = d2 * d3;
+        if (WIDE) {
+            s = fmaf(n01, ptx::rcp_approx(p01), s);
+            s = fmaf(n23, ptx::rcp_approx(p23), s);
+        } else {
+            s = fmaf(fmaf(n01, p23, n23 * p01), ptx::rcp_approx(p01 * p23), s);
+        }
+    }
+    for (int i = 0; i < ntail; ++i) s += ptx::rcp_approx(fminf(fmaf(erow[4 * nquads + i], u, 1.0f), kClamp));
+    return s;
+}
+
+
+__device__ __forceinline__ int fx_cbw(int n_bg, int c) { const int r = n_bg - 128 * c; return r < 128 ? r : 128; }
+
+__global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxParams p) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    unsigned char* sE = smem;                                   // [2][65536]
+    unsigned char* sZ = sE + 2 * kEStageBytes;                  // [2][8192]
+    unsigned char* sQ = sZ + 2 * kTileBytes;                    // [2][24576]
+    FxBars* bars = reinterpret_cast<FxBars*>(sQ + 2 * kQBytes);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int row_blocks = (p.n_rows + 127) >> 7;
+    const int64_t n_units = (int64_t)row_blocks * p.tiles;
+    const int cbs_last = (fx_cbw(p.n_bg, p.n_chunks - 1) + 3) & ~3;
+    const size_t tile_floats = (size_t)128 * (128 * (p.n_chunks - 1) + cbs_last);
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 2; ++i) {
+            ptx::mbar_init(&bars->zq_full[i], 3);
+            ptx::mbar_init(&bars->zq_empty[i], 1);
+            ptx::mbar_init(&bars->t_full[i], 1);
+            ptx::mbar_init(&bars->t_empty[i], kFxComputeWarps);
+            ptx::mbar_init(&bars->e_full[i], 1);
+            ptx::mbar_init(&bars->e_empty[i], kFxComputeWarps);
+        }
+        ptx::mbar_fence_init();
+    }
+    if (warp == 1) ptx::tmem_alloc(&bars->tmem_base, 256);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    if (warp == 0) {
+        // ================================================================ TMA: coalition tiles + E chunks
+        if (lane == 0) {
+            auto issue_z = [&](int kk, int64_t unit) {
+                const int s = kk & 1;
+                ptx::mbar_wait(&bars->zq_empty[s], ((kk >> 1) & 1) ^ 1);
+                ptx::mbar_arrive_expect_tx(&bars->zq_full[s], kTileBytes);
+                ptx::bulk_g2s(sZ + s * kTileBytes, reinterpret_cast<const unsigned char*>(p.zimg) + (size_t)(unit % p.tiles) * kTileBytes,
+                              kTileBytes, &bars->zq_full[s]);
+            };
+            int k = 0;
+            uint32_t j = 0;
+            if ((int64_t)blockIdx.x < n_units) issue_z(0, blockIdx.x);
+            for (int64_t u = blockIdx.x; u < n_units; u += gridDim.x, ++k) {
+                if (u + gridDim.x < n_units) issue_z(k + 1, u + gridDim.x);
+                const float* et = p.E + (size_t)(u % p.tiles) * tile_floats;
+                for (int c = 0; c < p.n_chunks; ++c, ++j) {
+                    const int es = j & 1;
+                    const uint32_t bytes = 128u * (uint32_t)((fx_cbw(p.n_bg, c) + 3) & ~3) * 4u;
+                    ptx::mbar_wait(&bars->e_empty[es], ((j >> 1) & 1) ^ 1);
+                    ptx::mbar_arrive_expect_tx(&bars->e_full[es], bytes);
+                    ptx::bulk_g2s(sE + es * kEStageBytes, et + (size_t)c * 128 * 128, bytes, &bars->e_full[es]);
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ================================================================ MMA issue
+        if (lane == 0) {
+            const uint32_t idesc = ptx::make_idesc_f16(p.fmt, 128, 128);
+            int k = 0;
+            for (int64_t u = blockIdx.x; u < n_units; u += gridDim.x, ++k) {
+                const int s = k & 1;
+                const uint32_t ph = (k >> 1) & 1;
+                ptx::mbar_wait(&bars->zq_full[s], ph);
+                ptx::mbar_wait(&bars->t_empty[s], ph ^ 1);
+                ptx::tc_fence_after();
+                const uint32_t d = tmem_base + s * 128;
+                const uint32_t qa = ptx::smem_u32(sQ + s * kQBytes), za = ptx::smem_u32(sZ + s * kTileBytes);
+#pragma unroll
+                for (int sp = 0; sp < 3; ++sp)
+#pragma unroll
+                    for (int ks = 0; ks < 2; ++ks)
+                        ptx::mma_f16(d, ptx::make_desc_kmajor_noswizzle(qa + sp * kTileBytes + ks * 256, kLbo, kSbo),
+                                     ptx::make_desc_kmajor_noswizzle(za + ks * 256, kLbo, kSbo), idesc, (sp | ks) != 0);
+                ptx::mma_commit(&bars->t_full[s]);
+                ptx::mma_commit(&bars->zq_empty[s]);
+            }
+        }
+        __syncwarp();
+    } else if (warp < 4) {
+        // ================================================================ Q block builders (64 rows each)
+        const int w = warp - 2;
+        const float wk = lane < FDB_F ? 1.4426950408889634f * p.wq[lane] : 0.f;
+        int k = 0;
+        for (int64_t u = blockIdx.x; u < n_units; u += gridDim.x, ++k) {
+            const int s = k & 1;
+            const int64_t row0 = (u / p.tiles) * 128 + w * 64;
+            ptx::mbar_wait(&bars->zq_empty[s], ((k >> 1) & 1) ^ 1);
+            unsigned char* qb = sQ + s * kQBytes + (lane >> 3) * 128 + (lane & 7) * 2;
+#pragma unroll 4
+            for (int i = 0; i < 64; ++i) {
+                const int64_t gr = row0 + i;
+                float v = (lane < FDB_F && gr < p.n_rows) ? wk * p.x[(size_t)gr * FDB_F + lane] : 0.f;
+                v = fminf(fmaxf(v, -30000.f), 30000.f);
+                float tot = v;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+                if (lane == 30) v = fminf(fmaxf(-tot, -60000.f), 60000.f);
+                const int r = w * 64 + i;
+                unsigned char* dst = qb + (r >> 3) * 512 + (r & 7) * 16;
+                float rem = v;
+#pragma unroll
+                for (int jj = 0; jj < 3; ++jj) {
+                    const uint16_t h = fx_to_h16(rem, p.fmt);
+                    *reinterpret_cast<uint16_t*>(dst + jj * kTileBytes) = h;
+                    rem -= fx_from_h16(h, p.fmt);
+                }
+            }
+            ptx::fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&bars->zq_full[s]);
+        }
+    } else {
+        // ================================================================ compute: lane = explained row
+        const int qd = warp & 3;
+        const int cg = (warp - 4) >> 2;
+        int k = 0;
+        uint32_t j = 0;
+        for (int64_t u = blockIdx.x; u < n_units; u += gridDim.x, ++k) {
+            const int s = k & 1;
+            const int tile = (int)(u % p.tiles);
+            const int64_t row = (u / p.tiles) * 128 + qd * 32 + lane;
+            ptx::mbar_wait(&bars->t_full[s], (k >> 1) & 1);
+            ptx::tc_fence_after();
+            const uint32_t ta = tmem_base + ((uint32_t)(qd * 32) << 16) + s * 128 + cg * 32;
+            uint32_t r0[16], r1[16];
+            ptx::tmem_ld16(ta, r0);
+            ptx::tmem_ld16(ta + 16, r1);
+            ptx::tmem_ld_wait();
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&bars->t_empty[s]);
+            float uu[32], part[32];
+            const float4* op = reinterpret_cast<const float4*>(p.eoff + tile * 128 + cg * 32);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float4 o = __ldg(op + i);
+                const float oo[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int mi = i * 4 + q;
+                    const float sq = __uint_as_float(mi < 16 ? r0[mi] : r1[mi - 16]) + oo[q];
+                    uu[mi] = ptx::ex2_approx(fminf(fmaxf(sq, -126.f), 126.f));
+                    part[mi] = 0.f;
+                }
+            }
+            for (int c = 0; c < p.n_chunks; ++c, ++j) {
+                const int es = j & 1;
+                const int cbw = fx_cbw(p.n_bg, c);
+                const int cbs = (cbw + 3) & ~3;
+                ptx::mbar_wait(&bars->e_full[es], (j >> 1) & 1);
+                const float* eb = reinterpret_cast<const float*>(sE + es * kEStageBytes) + (size_t)cg * 32 * cbs;
+                if (p.wide) {
+#pragma unroll
+                    for (int mi = 0; mi < 32; ++mi) part[mi] += chunk_sum<true>(eb + mi * cbs, cbw >> 2, cbw & 3, uu[mi]);
+                } else {
+#pragma unroll
+                    for (int mi = 0; mi < 32; ++mi) part[mi] += chunk_sum<false>(eb + mi * cbs, cbw >> 2, cbw & 3, uu[mi]);
+                }
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(&bars->e_empty[es]);
+            }
+            if (row < p.n_rows) {
+                float4* dst = reinterpret_cast<float4*>(p.ey + (size_t)row * p.m_pad + tile * 128 + cg * 32);
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    dst[i] = make_float4(part[4 * i] * p.inv_bg, part[4 * i + 1] * p.inv_bg, part[4 * i + 2] * p.inv_bg,
+                                         part[4 * i + 3] * p.inv_bg);
+            }
+        }
+    }
+
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc(tmem_base, 256);
+    }
+}
+
+// One block per coalition: exponents e_b = -log2e (c + sum_k (1 - z_mk) w_k bg_bk) in f64, centred per
+// coalition, stored as E = 2^(e_b - o_m) in the [tile][chunk][128][cbs] layout the evaluator streams.
+__global__ void __launch_bounds__(128) kshap_build_E(const uint32_t* __restrict__ bits, const double* __restrict__ Pd,
+                                                     int n_bg, int n_chunks, float* __restrict__ E,
+                                                     float* __restrict__ eoff) {
+    __shared__ double s_min[128], s_max[128];
+    const int m = blockIdx.x, tid = threadIdx.x;
+    const uint32_t b = bits[m];
+    double ev[8];
+    double mn = 1e300, mx = -1e300;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int col = tid + i * 128;
+        ev[i] = 0.0;
+        if (col < n_bg) {
+            const double* pr = Pd + (size_t)col * 32;
+            double g = pr[30];
+            for (int k = 0; k < FDB_F; ++k) g += ((b >> k) & 1u) ? 0.0 : pr[k];
+            ev[i] = -1.4426950408889634074 * g;
+            mn = fmin(mn, ev[i]);
+            mx = fmax(mx, ev[i]);
+        }
+    }
+    s_min[tid] = mn;
+    s_max[tid] = mx;
+    __syncthreads();
+    for (int o = 64; o > 0; o >>= 1) {
+        if (tid < o) { s_min[tid] = fmin(s_min[tid], s_min[tid + o]); s_max[tid] = fmax(s_max[tid], s_max[tid + o]); }
+        __syncthreads();
+    }
+    const double centre = 0.5 * (s_min[0] + s_max[0]);
+    if (tid == 0) eoff[m] = (float)centre;
+    const int cbs_last = (fx_cbw(n_bg, n_chunks - 1) + 3) & ~3;
+    const size_t tile_floats = (size_t)128 * (128 * (n_chunks - 1) + cbs_last);
+    float* et = E + (size_t)(m >> 7) * tile_floats;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int col = tid + i * 128;
+        if (col < n_bg) {
+            const int c = col >> 7;
+            const int cbs = (fx_cbw(n_bg, c) + 3) & ~3;
+            const double ex = fmin(fmax(ev[i] - centre, -120.0), 120.0);
+            et[(size_t)c * 128 * 128 + (size_t)(m & 127) * cbs + (col & 127)] = (float)exp2(ex);
+        }
+    }
+}
+
+}  // namespace
+
+// Build the factored operands of a single-set plan (called from fdb_kshap_plan_create).
+int fdb_kshap_build_factored(fdb_kshap_plan* pl, const double* bg_host) {
+    const int n_chunks = (pl->n_bg + 127) / 128;
+    const int cbs_last = ((pl->n_bg - 128 * (n_chunks - 1)) + 3) & ~3;
+    const size_t tile_floats = (size_t)128 * (128 * (n_chunks - 1) + cbs_last);
+    const size_t total = tile_floats * (pl->m_pad / 128);
+    double* h = new (std::nothrow) double[(size_t)pl->n_bg * 32];
+    FDB_REQUIRE(h != nullptr, FDB_ERR_NOMEM, "out of host memory");
+    for (int b = 0; b < pl->n_bg; ++b) {
+        for (int k = 0; k < 32; ++k) h[(size_t)b * 32 + k] = 0.0;
+        for (int k = 0; k < FDB_F; ++k) h[(size_t)b * 32 + k] = pl->coef[k] * bg_host[(size_t)b * FDB_F + k];
+        h[(size_t)b * 32 + 30] = pl->intercept;
+    }
+    double* dP = nullptr;
+    cudaError_t e = cudaMalloc((void**)&dP, (size_t)pl->n_bg * 32 * 8);
+    if (e == cudaSuccess) e = cudaMemcpy(dP, h, (size_t)pl->n_bg * 32 * 8, cudaMemcpyHostToDevice);
+    delete[] h;
+    if (e == cudaSuccess) e = cudaMalloc((void**)&pl->d_E, total * 4);
+    if (e == cudaSuccess) e = cudaMemset(pl->d_E, 0, total * 4);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&pl->d_eoff, (size_t)pl->m_pad * 4);
+    if (e == cudaSuccess) {
+        kshap_build_E<<<pl->m_pad, 128>>>(pl->d_bits, dP, pl->n_bg, n_chunks, pl->d_E, pl->d_eoff);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    cudaFree(dP);
+    FDB_CUDA(e);
+    return FDB_OK;
+}
+
+int fdb_kshap_launch_eval_fx(fdb_kshap_plan* pl, cudaStream_t st, const float* x, int n_rows, float* ey) {
+    FDB_REQUIRE(pl->d_E != nullptr, FDB_ERR_STATE, "the factored evaluator needs a plan with exactly one coalition set");
+    FxParams p;
+    p.x = x; p.zimg = pl->d_aimg; p.E = pl->d_E; p.eoff = pl->d_eoff; p.wq = pl->d_wq; p.ey = ey;
+    p.n_rows = n_rows; p.tiles = pl->m_pad / 128; p.m_pad = pl->m_pad; p.n_bg = pl->n_bg; p.fmt = pl->fmt;
+    p.n_chunks = (pl->n_bg + 127) / 128;
+    p.wide = pl->link == 1;
+    p.inv_bg = 1.0f / (float)pl->n_bg;
+    const size_t smem = 2 * kEStageBytes + 2 * kTileBytes + 2 * kQBytes + sizeof(FxBars) + 64;
+    static bool configured = false;
+    if (!configured) {
+        FDB_CUDA(cudaFuncSetAttribute(kshap_eval_fx_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    const int64_t n_units = (int64_t)((n_rows + 127) / 128) * p.tiles;
+    int64_t grid = n_units < pl->ctx->sm_count ? n_units : pl->ctx->sm_count;
+    if (grid < 1) grid = 1;
+    kshap_eval_fx_kernel<<<(int)grid, kFxThreads, smem, st>>>(p);
+    FDB_CUDA(cudaGetLastError());
+    return FDB_OK;
+}

@@ -32,6 +32,8 @@ struct fdb_kshap_plan {
     float* d_phi = nullptr;
     int32_t* d_set = nullptr;
     double* d_abs = nullptr;
+    float* d_E = nullptr;              // factored evaluator (single set): [tile][chunk][128][cbs] 2^(e - o_m)
+    float* d_eoff = nullptr;           // [m_pad] exponent centres o_m
 };
 
 void fdb_kshap_split(double v, int fmt, int n, uint16_t* out);
@@ -39,3 +41,7 @@ void fdb_kshap_split(double v, int fmt, int n, uint16_t* out);
 // K2: tcgen05 evaluator (kshap_eval_tc.cu).  ey[r][m] for rows [0, n_rows) of x.
 int fdb_kshap_launch_eval_tc(fdb_kshap_plan* p, cudaStream_t st, const float* x, int64_t row_offset, int n_rows,
                              const int32_t* set_idx, float* ey);
+
+// K2f: factored evaluator for single-set plans (kshap_eval_fx.cu).
+int fdb_kshap_build_factored(fdb_kshap_plan* pl, const double* bg_host);
+int fdb_kshap_launch_eval_fx(fdb_kshap_plan* pl, cudaStream_t st, const float* x, int n_rows, float* ey);

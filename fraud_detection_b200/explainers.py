@@ -113,7 +113,7 @@ class B200LinearExplainer:
 # =========================================================================================
 # Kernel SHAP
 # =========================================================================================
-EVAL_TC, EVAL_SIMT = 0, 1
+EVAL_AUTO, EVAL_TC, EVAL_SIMT, EVAL_FACTORED = -1, 0, 1, 2
 _LINKS = {"identity": 0, "logit": 1}
 
 
@@ -157,7 +157,7 @@ class KernelShapPlan:
         keys = ("n_bg", "nb_pad", "n_masks", "m_pad", "n_sets", "fmt", "nsplit", "batch_rows")
         return dict(zip(keys, list(arr)))
 
-    def explain_host(self, X32: np.ndarray, set_idx=None, evaluator=EVAL_TC, abs_sum=None) -> np.ndarray:
+    def explain_host(self, X32: np.ndarray, set_idx=None, evaluator=EVAL_AUTO, abs_sum=None) -> np.ndarray:
         X32 = np.ascontiguousarray(X32, dtype=np.float32)
         phi = np.empty_like(X32)
         sidx = None if set_idx is None else np.ascontiguousarray(set_idx, dtype=np.int32)
@@ -165,7 +165,7 @@ class KernelShapPlan:
                                                    int(evaluator), _lib.np_ptr(phi), _lib.np_ptr(abs_sum)))
         return phi
 
-    def explain_dev(self, x, set_idx=None, evaluator=EVAL_TC, phi=None, ey=None, abs_sum=None, stream=None):
+    def explain_dev(self, x, set_idx=None, evaluator=EVAL_AUTO, phi=None, ey=None, abs_sum=None, stream=None):
         """torch CUDA tensors in/out (float32 rows); enqueues on torch's current stream."""
         import torch
         if not (x.is_cuda and x.dtype == torch.float32 and x.is_contiguous() and x.dim() == 2 and x.shape[1] == N_FEATURES):
@@ -197,7 +197,8 @@ class B200KernelExplainer:
     ``np.random`` state (``mask_mode="per_row"``, what shap does), the coalition expectations
     are evaluated by the tcgen05 kernel (K2) and the additivity-constrained weighted least
     squares is solved per row (K3).  ``mask_mode="shared"`` draws ONE coalition set for all rows
-    - a different sampler from the reference, meant for throughput runs.
+    - a different sampler from the reference, meant for throughput runs (SURVEY.md section 7);
+    single-set plans use the factored evaluator (K2f: one exponential per (row, coalition)).
     ``masks=(Z, kw)`` or a list of per-row pairs feeds exported reference masks instead.
     Only ``l1_reg=False`` (plain WLS over all features) runs on the GPU.
     """
@@ -240,7 +241,7 @@ class B200KernelExplainer:
             kw[i, :len(w)] = w
         return bits, kw
 
-    def shap_values(self, X, nsamples="auto", l1_reg=False, mask_mode="per_row", masks=None, evaluator=EVAL_TC,
+    def shap_values(self, X, nsamples="auto", l1_reg=False, mask_mode="per_row", masks=None, evaluator=EVAL_AUTO,
                     random=None, silent=True, **kwargs):
         from . import sampler
         if l1_reg not in (False, 0):

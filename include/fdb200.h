@@ -114,15 +114,17 @@ int fdb_linear_pass_host(fdb_ctx* ctx, int dtype, int64_t n_rows, const void* x,
  * is the Shapley-kernel weight (maskMatrix / kernelWeights of the reference run).  With
  * n_sets == 1 all rows share the set; otherwise row r uses set set_idx[r] (or r mod n_sets
  * when set_idx is NULL), which reproduces the reference's per-row sampling.
- * link: 0 identity, 1 logit.  evaluator: FDB_KSHAP_EVAL_TC (tcgen05 tensor cores) or
- * FDB_KSHAP_EVAL_SIMT (plain fp32 CUDA cores; the cross-check).
+ * link: 0 identity, 1 logit.  evaluator: FDB_KSHAP_EVAL_TC (tcgen05 tensor cores, any plan),
+ * FDB_KSHAP_EVAL_FACTORED (single-set plans only: background part of every coalition is
+ * precomputed, one exponential per (row, coalition)), FDB_KSHAP_EVAL_SIMT (plain fp32 CUDA
+ * cores; the cross-check) or FDB_KSHAP_EVAL_AUTO (FACTORED for single-set plans, else TC).
  * explain: x is n_rows x 30 float32; phi is n_rows x 30 float32 with
  * sum_k phi[r][k] = link(f(x_r)) - expected_value exactly by construction; ey_out
  * (optional, n_rows x n_masks) returns the coalition expectations; abs_sum as in K1b.
  * A singular X'WX (too few coalitions) makes plan creation fail with FDB_ERR_ARG.
  * ------------------------------------------------------------------------------- */
 typedef struct fdb_kshap_plan fdb_kshap_plan;
-enum { FDB_KSHAP_EVAL_TC = 0, FDB_KSHAP_EVAL_SIMT = 1 };
+enum { FDB_KSHAP_EVAL_AUTO = -1, FDB_KSHAP_EVAL_TC = 0, FDB_KSHAP_EVAL_SIMT = 1, FDB_KSHAP_EVAL_FACTORED = 2 };
 int fdb_kshap_plan_create(fdb_ctx* ctx, const double* coef, double intercept, int n_bg, const double* bg,
                           int n_sets, int n_masks, const uint32_t* bits, const double* kw, int link,
                           fdb_kshap_plan** out);

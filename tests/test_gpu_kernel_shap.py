@@ -17,7 +17,7 @@ torch = pytest.importorskip("torch")
 from oracle import kernel_shap as ks  # noqa: E402
 from oracle import scoring, synth  # noqa: E402
 
-TC, SIMT = 0, 1
+TC, SIMT, FX = 0, 1, 2
 
 
 def _setup(params, n_bg, n_rows, seed=0):
@@ -64,8 +64,8 @@ def _check_phi(phi, phi_ref, f, X, expected, rel=1e-4, link=lambda v: v):
     np.testing.assert_allclose(phi.sum(1) + expected, link(f(X)), rtol=0, atol=1e-5)
 
 
-@pytest.mark.parametrize("evaluator", [SIMT, TC])
-@pytest.mark.parametrize("nsamples,n_bg", [(2048, 100), (256, 100), (100, 37), (2048, 1)])
+@pytest.mark.parametrize("evaluator", [SIMT, TC, FX])
+@pytest.mark.parametrize("nsamples,n_bg", [(2048, 100), (256, 100), (100, 37), (2048, 1), (300, 130)])
 def test_shared_masks_vs_oracle(params, evaluator, nsamples, n_bg):
     bg, X, f = _setup(params, n_bg, 12)
     Z, kw, _ = ks.sample_coalitions(30, nsamples, np.random.RandomState(0))
@@ -86,8 +86,11 @@ def test_tc_and_simt_evaluators_agree(params):
     plan = _plan(params, bg, [(Z, kw)])
     phi_a, ey_a, _ = _run(plan, X, TC)
     phi_b, ey_b, _ = _run(plan, X, SIMT)
+    phi_c, ey_c, _ = _run(plan, X, FX)
     np.testing.assert_allclose(ey_a, ey_b, rtol=0, atol=1e-6)
     np.testing.assert_allclose(phi_a, phi_b, rtol=0, atol=2e-6)
+    np.testing.assert_allclose(ey_c, ey_b, rtol=0, atol=2e-6)      # E * u carries one more rounding than ex2(t)
+    np.testing.assert_allclose(phi_c, phi_b, rtol=0, atol=3e-6)
     info = plan.info()
     assert info["m_pad"] == 2048 and info["nb_pad"] == 112 and info["nsplit"] in (2, 3)
     plan.close()
@@ -113,9 +116,10 @@ def test_config4_shapes_wide_background(params):
     Z, kw, _ = ks.sample_coalitions(30, 4096, np.random.RandomState(3))
     phi_ref, ey_ref, fnull = _oracle_rows(f, X, bg, [(Z, kw)])
     plan = _plan(params, bg, [(Z, kw)])
-    phi, ey, _ = _run(plan, X, TC)
-    np.testing.assert_allclose(ey, ey_ref, rtol=0, atol=2e-6)
-    _check_phi(phi, phi_ref, f, X, fnull)
+    for ev in (TC, FX):
+        phi, ey, _ = _run(plan, X, ev)
+        np.testing.assert_allclose(ey, ey_ref, rtol=0, atol=2e-6)
+        _check_phi(phi, phi_ref, f, X, fnull)
     plan.close()
 
 
@@ -126,10 +130,11 @@ def test_logit_link(params):
     plan = _plan(params, bg, [(Z, kw)], link="logit")
     lg = lambda v: np.log(v / (1 - v))  # noqa: E731
     assert abs(plan.expected_value - lg(fnull)) < 1e-10
-    phi, _, _ = _run(plan, X, TC, want_ey=False)
-    scale = np.abs(phi_ref).max(1, keepdims=True)
-    assert np.all(np.abs(phi - phi_ref) <= 2e-3 * scale)          # float32 logit() of ey amplifies rounding
-    np.testing.assert_allclose(phi.sum(1) + lg(fnull), lg(f(X)), rtol=0, atol=2e-4)
+    for ev in (TC, FX):
+        phi, _, _ = _run(plan, X, ev, want_ey=False)
+        scale = np.abs(phi_ref).max(1, keepdims=True)
+        assert np.all(np.abs(phi - phi_ref) <= 2e-3 * scale)          # float32 logit() of ey amplifies rounding
+        np.testing.assert_allclose(phi.sum(1) + lg(fnull), lg(f(X)), rtol=0, atol=2e-4)
     plan.close()
 
 
@@ -138,14 +143,26 @@ def test_many_rows_batches_and_determinism(params):
     bg, X, f = _setup(params, 20, 9000, seed=5)
     Z, kw, _ = ks.sample_coalitions(30, 128, np.random.RandomState(5))
     plan = _plan(params, bg, [(Z, kw)])
-    phi, _, abs_sum = _run(plan, X, TC, want_ey=False)
-    phi2, _, abs_sum2 = _run(plan, X, TC, want_ey=False)
+    phi_tc, _, _ = _run(plan, X, TC, want_ey=False)
+    phi, _, abs_sum = _run(plan, X, FX, want_ey=False)
+    phi2, _, abs_sum2 = _run(plan, X, FX, want_ey=False)
     assert np.array_equal(phi, phi2) and np.array_equal(abs_sum, abs_sum2)
+    np.testing.assert_allclose(phi, phi_tc, rtol=0, atol=2e-6)
     idx = np.array([0, 1, 4095, 8191, 8192, 8999])
     phi_ref, _, fnull = _oracle_rows(f, X[idx], bg, [(Z, kw)])
     _check_phi(phi[idx], phi_ref, f, X[idx], fnull)
     np.testing.assert_allclose(phi.sum(1) + fnull, f(X), rtol=0, atol=1e-5)
     np.testing.assert_allclose(abs_sum[:30], np.abs(phi).sum(0), rtol=1e-6)
+    plan.close()
+
+
+def test_factored_evaluator_needs_a_single_set(params):
+    bg, X, f = _setup(params, 10, 4, seed=9)
+    rs = np.random.RandomState(9)
+    sets = [ks.sample_coalitions(30, 128, rs)[:2] for _ in range(2)]
+    plan = _plan(params, bg, sets)
+    with pytest.raises(ValueError, match="exactly one coalition set"):
+        _run(plan, X, FX, want_ey=False)
     plan.close()
 
 
@@ -160,7 +177,7 @@ def test_explainer_class_matches_oracle_with_same_seed(params):
     _check_phi(phi, phi_ref, f, X, expl.expected_value)
     one = expl.shap_values(X[0], nsamples=2048, random=np.random.RandomState(7))
     assert one.shape == (30,)
-    np.testing.assert_allclose(one, phi[0], atol=1e-12)
+    np.testing.assert_allclose(one, phi[0], atol=1e-6)      # one set -> factored evaluator, five sets -> general one
     shared = expl.shap_values(X, nsamples=2048, mask_mode="shared", random=np.random.RandomState(8))
     np.testing.assert_allclose(shared.sum(1) + expl.expected_value, f(X), atol=1e-5)
     with pytest.raises(NotImplementedError):

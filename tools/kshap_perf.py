@@ -24,7 +24,7 @@ plan = KernelShapPlan(prm.coef, prm.intercept, bg, bits, kw)
 x = torch.from_numpy(X).cuda()
 phi = torch.empty_like(x)
 abs_sum = torch.empty(32, dtype=torch.float64, device="cuda")
-for ev, name in ((0, "tcgen05"), (1, "simt")):
+for ev, name in ((2, "factored"), (0, "tcgen05"), (1, "simt")):
     if ev == 1 and rows > 4096:
         xx, pp = x[:4096], phi[:4096]
     else:
