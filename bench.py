@@ -267,7 +267,7 @@ def bench_kernel_shap(args, torch, dist, device, rank, world, prm, sm_max_mhz):
         "value": rows * world / (ms * 1e-3), "unit": "explained rows/s", "ms_per_step": ms, "steps": steps,
         "sigmoids_per_s": sig * world / (ms * 1e-3),
         "evaluator": "K2f factored (single coalition set: one exponential per (row, coalition), E[m][b] precomputed) + K3",
-        "gpu_launches_per_step": 2 * -(-rows // 8192),
+        "gpu_launches_per_step": 2 * -(-rows // 32768),
         "general_evaluator": {"evaluator": "K2 tcgen05 per-element sigmoid (any plan, the per-row-mask path) + K3",
                               "value": rows * world / (ms_tc * 1e-3), "unit": "explained rows/s", "ms_per_step": ms_tc,
                               "sigmoids_per_s": sig * world / (ms_tc * 1e-3)},

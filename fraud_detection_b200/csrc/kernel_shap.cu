@@ -119,6 +119,17 @@ __global__ void __launch_bounds__(32) kshap_wls_prepare(const uint32_t* __restri
     if (lane == 0) status[s] = singular ? 1 : 0;
 }
 
+// xw[m][j] = kw_m * x_mj (x = z_j - z_29) for the single set of a factored plan: the row-independent factor of X'W y
+__global__ void kshap_build_xw(const uint32_t* __restrict__ bits, const float* __restrict__ kw, int m_pad,
+                               float* __restrict__ xw) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= m_pad * 32) return;
+    const int m = idx >> 5, j = idx & 31;
+    const uint32_t b = bits[m];
+    const float x = j < kNV ? (float)((b >> j) & 1u) - (float)((b >> 29) & 1u) : 0.f;
+    xw[idx] = kw[m] * x;
+}
+
 // ---------------------------------------------------------------------------------------
 // SIMT evaluator: one thread per (row, mask), plain fp32 FMAs and full-precision expf.
 // The GPU-side cross-check of K2 and the evaluator for shapes K2 does not take.
@@ -155,7 +166,8 @@ __global__ void __launch_bounds__(128) kshap_wls_solve(
     const uint32_t* __restrict__ bits, const float* __restrict__ kw, int m_pad, const float* __restrict__ ey,
     const float* __restrict__ ainv, const float* __restrict__ c2, const float* __restrict__ wcoef, float intercept,
     float fnull, int link, float* __restrict__ phi, double* __restrict__ abs_sum, int accumulate,
-    int64_t total_rows, double* __restrict__ partials, unsigned int* __restrict__ ticket) {
+    int64_t total_rows, double* __restrict__ partials, unsigned int* __restrict__ ticket,
+    const float* __restrict__ gpart, int nparts) {
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const float lnull = link_apply(fnull, link);
@@ -172,33 +184,41 @@ __global__ void __launch_bounds__(128) kshap_wls_solve(
         const uint32_t* sb = bits + (size_t)s * m_pad;
         const float* sk = kw + (size_t)s * m_pad;
         const float* er = ey + (size_t)r * m_pad;
-        // X'W y: every lane owns one coalition per step and keeps all 29 partial sums in registers
-        // (x_mj * v = zp_j ? vp : 0 after folding the sign of the eliminated feature into vp / zp) ...
-        float gj[32];
+        float g;
+        if (gpart != nullptr) {
+            // X'W y already accumulated by the factored evaluator: fold its per-(tile, warp) partials in a fixed order
+            const float* gp = gpart + (size_t)r * nparts * 32 + lane;
+            g = 0.f;
+            for (int q = 0; q < nparts; ++q) g += gp[(size_t)q * 32];
+        } else {
+            // X'W y: every lane owns one coalition per step and keeps all 29 partial sums in registers
+            // (x_mj * v = zp_j ? vp : 0 after folding the sign of the eliminated feature into vp / zp) ...
+            float gj[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) gj[j] = 0.f;
-        for (int m0 = 0; m0 < m_pad; m0 += 32) {
-            const uint32_t b = sb[m0 + lane];
-            const float kwv = sk[m0 + lane];
-            const float v = kwv != 0.f ? kwv * (link_apply(er[m0 + lane], link) - lnull) : 0.f;
-            const bool z29 = (b >> 29) & 1u;
-            const float vp = z29 ? -v : v;
-            const uint32_t bp = z29 ? ~b : b;
+            for (int j = 0; j < 32; ++j) gj[j] = 0.f;
+            for (int m0 = 0; m0 < m_pad; m0 += 32) {
+                const uint32_t b = sb[m0 + lane];
+                const float kwv = sk[m0 + lane];
+                const float v = kwv != 0.f ? kwv * (link_apply(er[m0 + lane], link) - lnull) : 0.f;
+                const bool z29 = (b >> 29) & 1u;
+                const float vp = z29 ? -v : v;
+                const uint32_t bp = z29 ? ~b : b;
 #pragma unroll
-            for (int j = 0; j < kNV; ++j) gj[j] += ((bp >> j) & 1u) ? vp : 0.f;
-        }
-        // ... then a butterfly transpose-reduce leaves the total of column j in lane j (31 shuffles)
-#pragma unroll
-        for (int half = 16; half >= 1; half >>= 1) {
-            const bool up = (lane & half) != 0;
-#pragma unroll
-            for (int i = 0; i < half; ++i) {
-                const float send = up ? gj[i] : gj[i + half];
-                const float keep = up ? gj[i + half] : gj[i];
-                gj[i] = keep + __shfl_xor_sync(0xffffffffu, send, half);
+                for (int j = 0; j < kNV; ++j) gj[j] += ((bp >> j) & 1u) ? vp : 0.f;
             }
+            // ... then a butterfly transpose-reduce leaves the total of column j in lane j (31 shuffles)
+#pragma unroll
+            for (int half = 16; half >= 1; half >>= 1) {
+                const bool up = (lane & half) != 0;
+#pragma unroll
+                for (int i = 0; i < half; ++i) {
+                    const float send = up ? gj[i] : gj[i + half];
+                    const float keep = up ? gj[i + half] : gj[i];
+                    gj[i] = keep + __shfl_xor_sync(0xffffffffu, send, half);
+                }
+            }
+            g = gj[0];
         }
-        const float g = gj[0];
         const float rhs = lane < kNV ? g - d * c2[(size_t)s * 32 + lane] : 0.f;
         const float* ai = ainv + (size_t)s * kNV * 32;
         float w = 0.f;
@@ -248,7 +268,7 @@ void free_plan(fdb_kshap_plan* p) {
     if (!p) return;
     cudaFree(p->d_bits); cudaFree(p->d_kw); cudaFree(p->d_P); cudaFree(p->d_wq); cudaFree(p->d_bimg); cudaFree(p->d_aimg);
     cudaFree(p->d_ainv); cudaFree(p->d_c2); cudaFree(p->d_status); cudaFree(p->d_ey); cudaFree(p->d_x); cudaFree(p->d_phi);
-    cudaFree(p->d_set); cudaFree(p->d_abs); cudaFree(p->d_E); cudaFree(p->d_eoff);
+    cudaFree(p->d_set); cudaFree(p->d_abs); cudaFree(p->d_E); cudaFree(p->d_eoff); cudaFree(p->d_xw); cudaFree(p->d_gpart);
     delete p;
 }
 
@@ -372,7 +392,20 @@ extern "C" int fdb_kshap_plan_create(fdb_ctx* ctx, const double* coef, double in
         fdb_set_error("kernel-SHAP plan creation failed: %s", cudaGetErrorString(e));
         rc = e == cudaErrorMemoryAllocation ? FDB_ERR_NOMEM : FDB_ERR_CUDA;
     }
-    if (rc == FDB_OK && n_sets == 1) rc = fdb_kshap_build_factored(p, bg);
+    if (rc == FDB_OK && n_sets == 1) {
+        cudaError_t e2 = cudaMalloc((void**)&p->d_xw, (size_t)p->m_pad * 32 * 4);
+        if (e2 == cudaSuccess) e2 = cudaMalloc((void**)&p->d_gpart, (size_t)p->batch_rows * (p->m_pad / 32) * 32 * 4);
+        if (e2 == cudaSuccess) {
+            kshap_build_xw<<<(p->m_pad * 32 + 255) / 256, 256>>>(p->d_bits, p->d_kw, p->m_pad, p->d_xw);
+            e2 = cudaGetLastError();
+        }
+        if (e2 != cudaSuccess) {
+            fdb_set_error("kernel-SHAP plan creation failed: %s", cudaGetErrorString(e2));
+            rc = e2 == cudaErrorMemoryAllocation ? FDB_ERR_NOMEM : FDB_ERR_CUDA;
+        } else {
+            rc = fdb_kshap_build_factored(p, bg);
+        }
+    }
     if (rc != FDB_OK) { free_plan(p); return rc; }
     *out = p;
     return FDB_OK;
@@ -422,7 +455,7 @@ extern "C" int fdb_kshap_explain_dev(fdb_kshap_plan* p, void* stream, int64_t n_
             int rc = fdb_kshap_launch_eval_tc(p, st, xb, r0, nb, sb, p->d_ey);
             if (rc != FDB_OK) return rc;
         } else if (evaluator == FDB_KSHAP_EVAL_FACTORED) {
-            int rc = fdb_kshap_launch_eval_fx(p, st, xb, nb, p->d_ey);
+            int rc = fdb_kshap_launch_eval_fx(p, st, xb, nb, ey_out ? p->d_ey : nullptr);
             if (rc != FDB_OK) return rc;
         } else {
             dim3 grid(p->m_pad / 128, nb);
@@ -438,7 +471,8 @@ extern "C" int fdb_kshap_explain_dev(fdb_kshap_plan* p, void* stream, int64_t n_
         kshap_wls_solve<<<grid, 128, 0, st>>>(xb, r0, nb, sb, p->n_sets, p->d_bits, p->d_kw, p->m_pad, p->d_ey, p->d_ainv,
                                              p->d_c2, p->d_wq, (float)p->intercept, (float)p->fnull, p->link,
                                              phi + r0 * FDB_F, abs_sum, r0 > 0 ? 1 : 0, n_rows, ctx->d_partials,
-                                             ctx->d_ticket);
+                                             ctx->d_ticket, evaluator == FDB_KSHAP_EVAL_FACTORED ? p->d_gpart : nullptr,
+                                             p->m_pad / 32);
         FDB_CUDA(cudaGetLastError());
     }
     return FDB_OK;

@@ -23,6 +23,8 @@
 //   warps 2-3          build the Q block (x rows -> scaled, split, canonical K-major layout)
 //   warps 4-19         compute: TMEM lane quarter = warp % 4, coalition group = (warp - 4) / 4
 
+#include <math.h>
+
 #include <new>
 
 #include <cuda_bf16.h>
@@ -46,11 +48,13 @@ struct FxParams {
     const float* E;            // [tile][chunk][128][cbs]
     const float* eoff;         // [m_pad] exponent centre o_m
     const float* wq;
-    float* ey;
+    const float* xw;           // [m_pad][32] kw_m * x_mj
+    float* ey;                 // optional [n_rows][m_pad]
+    float* gpart;              // [n_rows][m_pad/32][32] partial X'W y
     int n_rows, tiles, m_pad, n_bg, fmt;
     int n_chunks;              // background chunks of 128 columns (last one narrower)
-    int wide;
-    float inv_bg;
+    int link;
+    float inv_bg, lnull;
 };
 
 struct FxBars {
@@ -65,32 +69,44 @@ __device__ __forceinline__ float fx_from_h16(uint16_t h, int fmt) {
     return fmt == 0 ? __half2float(__ushort_as_half(h)) : __bfloat162float(__ushort_as_bfloat16(h));
 }
 
-// sum over one background chunk for one (row, coalition): erow points at E[m][chunk columns] in smem (same
-// address in every lane -> broadcast loads).  WIDE: logit link, two sigmoids per reciprocal, clamp 2^62.
+// Sums over one background chunk for one row and FOUR coalitions at once (independent chains hide the LDS and
+// SFU latency and share the loop overhead).  e0 points at E[m0][chunk columns] in smem, rows are cbs floats
+// apart; every lane reads the same addresses -> broadcast LDS.128.  WIDE: logit link, two sigmoids per
+// reciprocal and clamp 2^62 so that tiny sigmoids keep their relative accuracy.
 template <bool WIDE>
-__device__ __forceinline__ float chunk_sum(const float* __restrict__ erow, int nquads, int ntail, float u) {
+__device__ __forceinline__ void chunk_sum4(const float* __restrict__ e0, int cbs, int nquads, int ntail,
+                                           const float* __restrict__ u, float* __restrict__ acc) {
     constexpr float kClamp = WIDE ? 4.611686018427388e18f : 1073741824.f;
-    float s = 0.f;
-#pragma unroll 4
+#pragma unroll 2
     for (int q = 0; q < nquads; ++q) {
-        const float4 e = *reinterpret_cast<const float4*>(erow + 4 * q);
-        const float d0 = fminf(fmaf(e.x, u, 1.0f), kClamp), d1 = fminf(fmaf(e.y, u, 1.0f), kClamp);
-        const float d2 = fminf(fmaf(e.z, u, 1.0f), kClamp), d3 = fminf(fmaf(e.w, u, 1.0f), kClamp);
-        const float n01 = d0 + d1, p01 = d0 * d1, n23 = d2 + d3, p23 = d2 * d3;
-        if (WIDE) {
-            s = fmaf(n01, ptx::rcp_approx(p01), s);
-            s = fmaf(n23, ptx::rcp_approx(p23), s);
-        } else {
-            s = fmaf(fmaf(n01, p23, n23 * p01), ptx::rcp_approx(p01 * p23), s);
+#pragma unroll
+        for (int mm = 0; mm < 4; ++mm) {
+            const float4 e = *reinterpret_cast<const float4*>(e0 + mm * cbs + 4 * q);
+            const float d0 = fminf(fmaf(e.x, u[mm], 1.0f), kClamp), d1 = fminf(fmaf(e.y, u[mm], 1.0f), kClamp);
+            const float d2 = fminf(fmaf(e.z, u[mm], 1.0f), kClamp), d3 = fminf(fmaf(e.w, u[mm], 1.0f), kClamp);
+            const float n01 = d0 + d1, p01 = d0 * d1, n23 = d2 + d3, p23 = d2 * d3;
+            if (WIDE) {
+                acc[mm] = fmaf(n01, ptx::rcp_approx(p01), acc[mm]);
+                acc[mm] = fmaf(n23, ptx::rcp_approx(p23), acc[mm]);
+            } else {
+                acc[mm] = fmaf(fmaf(n01, p23, n23 * p01), ptx::rcp_approx(p01 * p23), acc[mm]);
+            }
         }
     }
-    for (int i = 0; i < ntail; ++i) s += ptx::rcp_approx(fminf(fmaf(erow[4 * nquads + i], u, 1.0f), kClamp));
-    return s;
+    for (int i = 0; i < ntail; ++i)
+#pragma unroll
+        for (int mm = 0; mm < 4; ++mm)
+            acc[mm] += ptx::rcp_approx(fminf(fmaf(e0[mm * cbs + 4 * nquads + i], u[mm], 1.0f), kClamp));
 }
 
+// waits of the single-lane service warps back off so their polling does not take issue slots from the compute warps
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
+    while (!ptx::mbar_try_wait(bar, parity)) __nanosleep(64);
+}
 
 __device__ __forceinline__ int fx_cbw(int n_bg, int c) { const int r = n_bg - 128 * c; return r < 128 ? r : 128; }
 
+template <bool WIDE>
 __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     unsigned char* sE = smem;                                   // [2][65536]
@@ -127,7 +143,7 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
         if (lane == 0) {
             auto issue_z = [&](int kk, int64_t unit) {
                 const int s = kk & 1;
-                ptx::mbar_wait(&bars->zq_empty[s], ((kk >> 1) & 1) ^ 1);
+                mbar_wait_relaxed(&bars->zq_empty[s], ((kk >> 1) & 1) ^ 1);
                 ptx::mbar_arrive_expect_tx(&bars->zq_full[s], kTileBytes);
                 ptx::bulk_g2s(sZ + s * kTileBytes, reinterpret_cast<const unsigned char*>(p.zimg) + (size_t)(unit % p.tiles) * kTileBytes,
                               kTileBytes, &bars->zq_full[s]);
@@ -141,7 +157,7 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
                 for (int c = 0; c < p.n_chunks; ++c, ++j) {
                     const int es = j & 1;
                     const uint32_t bytes = 128u * (uint32_t)((fx_cbw(p.n_bg, c) + 3) & ~3) * 4u;
-                    ptx::mbar_wait(&bars->e_empty[es], ((j >> 1) & 1) ^ 1);
+                    mbar_wait_relaxed(&bars->e_empty[es], ((j >> 1) & 1) ^ 1);
                     ptx::mbar_arrive_expect_tx(&bars->e_full[es], bytes);
                     ptx::bulk_g2s(sE + es * kEStageBytes, et + (size_t)c * 128 * 128, bytes, &bars->e_full[es]);
                 }
@@ -156,8 +172,8 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
             for (int64_t u = blockIdx.x; u < n_units; u += gridDim.x, ++k) {
                 const int s = k & 1;
                 const uint32_t ph = (k >> 1) & 1;
-                ptx::mbar_wait(&bars->zq_full[s], ph);
-                ptx::mbar_wait(&bars->t_empty[s], ph ^ 1);
+                mbar_wait_relaxed(&bars->zq_full[s], ph);
+                mbar_wait_relaxed(&bars->t_empty[s], ph ^ 1);
                 ptx::tc_fence_after();
                 const uint32_t d = tmem_base + s * 128;
                 const uint32_t qa = ptx::smem_u32(sQ + s * kQBytes), za = ptx::smem_u32(sZ + s * kTileBytes);
@@ -180,7 +196,7 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
         for (int64_t u = blockIdx.x; u < n_units; u += gridDim.x, ++k) {
             const int s = k & 1;
             const int64_t row0 = (u / p.tiles) * 128 + w * 64;
-            ptx::mbar_wait(&bars->zq_empty[s], ((k >> 1) & 1) ^ 1);
+            mbar_wait_relaxed(&bars->zq_empty[s], ((k >> 1) & 1) ^ 1);
             unsigned char* qb = sQ + s * kQBytes + (lane >> 3) * 128 + (lane & 7) * 2;
 #pragma unroll 4
             for (int i = 0; i < 64; ++i) {
@@ -245,22 +261,40 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
                 const int cbs = (cbw + 3) & ~3;
                 ptx::mbar_wait(&bars->e_full[es], (j >> 1) & 1);
                 const float* eb = reinterpret_cast<const float*>(sE + es * kEStageBytes) + (size_t)cg * 32 * cbs;
-                if (p.wide) {
 #pragma unroll
-                    for (int mi = 0; mi < 32; ++mi) part[mi] += chunk_sum<true>(eb + mi * cbs, cbw >> 2, cbw & 3, uu[mi]);
-                } else {
-#pragma unroll
-                    for (int mi = 0; mi < 32; ++mi) part[mi] += chunk_sum<false>(eb + mi * cbs, cbw >> 2, cbw & 3, uu[mi]);
-                }
+                for (int g4 = 0; g4 < 8; ++g4)
+                    chunk_sum4<WIDE>(eb + (size_t)g4 * 4 * cbs, cbs, cbw >> 2, cbw & 3, uu + 4 * g4, part + 4 * g4);
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(&bars->e_empty[es]);
             }
             if (row < p.n_rows) {
-                float4* dst = reinterpret_cast<float4*>(p.ey + (size_t)row * p.m_pad + tile * 128 + cg * 32);
+                // fused first half of the least-squares solve: this thread's share of X'W y,
+                //   g[j] += (kw_m x_mj) * (link(ey[r][m]) - link(fnull))   over its 32 coalitions
+                float gq[32];
 #pragma unroll
-                for (int i = 0; i < 8; ++i)
-                    dst[i] = make_float4(part[4 * i] * p.inv_bg, part[4 * i + 1] * p.inv_bg, part[4 * i + 2] * p.inv_bg,
-                                         part[4 * i + 3] * p.inv_bg);
+                for (int jj = 0; jj < 32; ++jj) gq[jj] = 0.f;
+                const float4* xwp = reinterpret_cast<const float4*>(p.xw + (size_t)(tile * 128 + cg * 32) * 32);
+#pragma unroll
+                for (int mi = 0; mi < 32; ++mi) {
+                    part[mi] *= p.inv_bg;
+                    const float yv = (p.link == 1 ? __logf(part[mi] / (1.0f - part[mi])) : part[mi]) - p.lnull;
+#pragma unroll
+                    for (int v4 = 0; v4 < 8; ++v4) {
+                        const float4 xv = __ldg(xwp + mi * 8 + v4);          // same address in every lane
+                        gq[4 * v4] = fmaf(xv.x, yv, gq[4 * v4]);
+                        gq[4 * v4 + 1] = fmaf(xv.y, yv, gq[4 * v4 + 1]);
+                        gq[4 * v4 + 2] = fmaf(xv.z, yv, gq[4 * v4 + 2]);
+                        gq[4 * v4 + 3] = fmaf(xv.w, yv, gq[4 * v4 + 3]);
+                    }
+                }
+                float4* gdst = reinterpret_cast<float4*>(p.gpart + ((size_t)row * (p.m_pad / 32) + tile * 4 + cg) * 32);
+#pragma unroll
+                for (int v4 = 0; v4 < 8; ++v4) gdst[v4] = make_float4(gq[4 * v4], gq[4 * v4 + 1], gq[4 * v4 + 2], gq[4 * v4 + 3]);
+                if (p.ey != nullptr) {
+                    float4* dst = reinterpret_cast<float4*>(p.ey + (size_t)row * p.m_pad + tile * 128 + cg * 32);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) dst[i] = make_float4(part[4 * i], part[4 * i + 1], part[4 * i + 2], part[4 * i + 3]);
+                }
             }
         }
     }
@@ -356,20 +390,24 @@ int fdb_kshap_launch_eval_fx(fdb_kshap_plan* pl, cudaStream_t st, const float* x
     FDB_REQUIRE(pl->d_E != nullptr, FDB_ERR_STATE, "the factored evaluator needs a plan with exactly one coalition set");
     FxParams p;
     p.x = x; p.zimg = pl->d_aimg; p.E = pl->d_E; p.eoff = pl->d_eoff; p.wq = pl->d_wq; p.ey = ey;
+    p.xw = pl->d_xw; p.gpart = pl->d_gpart;
     p.n_rows = n_rows; p.tiles = pl->m_pad / 128; p.m_pad = pl->m_pad; p.n_bg = pl->n_bg; p.fmt = pl->fmt;
     p.n_chunks = (pl->n_bg + 127) / 128;
-    p.wide = pl->link == 1;
+    p.link = pl->link;
     p.inv_bg = 1.0f / (float)pl->n_bg;
+    p.lnull = pl->link == 1 ? (float)log(pl->fnull / (1.0 - pl->fnull)) : (float)pl->fnull;
     const size_t smem = 2 * kEStageBytes + 2 * kTileBytes + 2 * kQBytes + sizeof(FxBars) + 64;
     static bool configured = false;
     if (!configured) {
-        FDB_CUDA(cudaFuncSetAttribute(kshap_eval_fx_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        FDB_CUDA(cudaFuncSetAttribute(kshap_eval_fx_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        FDB_CUDA(cudaFuncSetAttribute(kshap_eval_fx_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = true;
     }
     const int64_t n_units = (int64_t)((n_rows + 127) / 128) * p.tiles;
     int64_t grid = n_units < pl->ctx->sm_count ? n_units : pl->ctx->sm_count;
     if (grid < 1) grid = 1;
-    kshap_eval_fx_kernel<<<(int)grid, kFxThreads, smem, st>>>(p);
+    if (pl->link == 1) kshap_eval_fx_kernel<true><<<(int)grid, kFxThreads, smem, st>>>(p);
+    else kshap_eval_fx_kernel<false><<<(int)grid, kFxThreads, smem, st>>>(p);
     FDB_CUDA(cudaGetLastError());
     return FDB_OK;
 }

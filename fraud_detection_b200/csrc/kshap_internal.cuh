@@ -4,7 +4,7 @@
 #include "fdb_internal.cuh"
 
 #define FDB_KSHAP_MAX_BG 1024          // background rows the tensor-core evaluator keeps resident in smem
-#define FDB_KSHAP_BATCH_ROWS 8192      // explained rows per evaluate->solve round (bounds the ey scratch)
+#define FDB_KSHAP_BATCH_ROWS 32768     // explained rows per evaluate->solve round (bounds the ey / partial-sum scratch)
 
 struct fdb_kshap_plan {
     fdb_ctx* ctx = nullptr;
@@ -34,6 +34,8 @@ struct fdb_kshap_plan {
     double* d_abs = nullptr;
     float* d_E = nullptr;              // factored evaluator (single set): [tile][chunk][128][cbs] 2^(e - o_m)
     float* d_eoff = nullptr;           // [m_pad] exponent centres o_m
+    float* d_xw = nullptr;             // [m_pad][32] kw_m * x_mj
+    float* d_gpart = nullptr;          // [batch_rows][m_pad/32][32] partial X'W y written by K2f, folded by K3
 };
 
 void fdb_kshap_split(double v, int fmt, int n, uint16_t* out);
