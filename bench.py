@@ -37,6 +37,9 @@ METRIC = "scored_rows_per_sec"
 UNIT = "rows/s"
 BYTES_PER_ROW = 244           # 120 B x in + 4 B proba + 120 B phi
 FALLBACK_HBM_GBS = 6650.0     # B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
+# dram__bytes_read.sum + dram__bytes_write.sum of linear_pass_tma_kernel<float,0,1>, one `ncu --set full` capture at
+# 2e7 rows (profiles/r01/ncu_k1_tma.txt: 2.400650 GB + 2.436800 GB), per row; scaled to the launch's row count
+NCU_TRAFFIC_BYTES_PER_ROW = (2.400650e9 + 2.436800e9) / 2.0e7
 
 
 def parse_args():
@@ -258,7 +261,13 @@ def bench_kernel_shap(args, torch, dist, device, rank, world, prm, sm_max_mhz):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    ms = timed(lambda: plan.explain_dev(x, phi=phi, abs_sum=abs_sum), steps)            # AUTO -> factored (K2f) + K3
+    from fraud_detection_b200.distributed import allreduce_abs_sum
+
+    def step_auto():
+        plan.explain_dev(x, phi=phi, abs_sum=abs_sum)            # AUTO -> factored (K2f) + K3
+        allreduce_abs_sum(abs_sum)                                # global mean|SHAP| summary (no-op at world 1)
+
+    ms = timed(step_auto, steps)
     ms_tc = timed(lambda: plan.explain_dev(x, evaluator=0, phi=phi, abs_sum=abs_sum), steps)   # general tcgen05 evaluator (K2) + K3
     sig = rows * len(bits) * n_bg
     out = {
@@ -440,7 +449,7 @@ def run_b200(args):
                     "api": "fdb_linear_pass_host (pinned host in/out, 3-stream chunked pipeline)"},
             "gpu_launches": args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": "linear_pass_tma_kernel<float,false,true>", "kernel_ms": kernel_ms,
+                         "traffic": NCU_TRAFFIC_BYTES_PER_ROW * n, "kernel": "linear_pass_tma_kernel<float,false,true>", "kernel_ms": kernel_ms,
                          "algorithmic_bytes_per_launch": n * BYTES_PER_ROW, "peak_source": peak_src},
             "clocks": clocks.summary(),
         }

@@ -4,9 +4,9 @@ set -u
 TAG=${1:-r01}
 OUT=gpurun_out
 mkdir -p $OUT
-CMD="python bench.py --steps 2 --warmup 3 --rows 20000000 --e2e-rows 1000000 --cpu-rows 200000"
+CMD="python bench.py --steps 2 --warmup 3 --rows 20000000 --e2e-rows 1000000 --cpu-rows 200000 --no-kshap"
 $CMD > $OUT/${TAG}_plain.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -k regex:linear_pass -c 20 --csv \
+ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv \
     --log-file $OUT/${TAG}_launches.csv $CMD > $OUT/${TAG}_ncu_launches.log 2>&1
 echo "launch list rc=$?"
 $CMD > $OUT/${TAG}_plain2.log 2>&1 &&
