@@ -268,7 +268,7 @@ void free_plan(fdb_kshap_plan* p) {
     if (!p) return;
     cudaFree(p->d_bits); cudaFree(p->d_kw); cudaFree(p->d_P); cudaFree(p->d_wq); cudaFree(p->d_bimg); cudaFree(p->d_aimg);
     cudaFree(p->d_ainv); cudaFree(p->d_c2); cudaFree(p->d_status); cudaFree(p->d_ey); cudaFree(p->d_x); cudaFree(p->d_phi);
-    cudaFree(p->d_set); cudaFree(p->d_abs); cudaFree(p->d_E); cudaFree(p->d_eoff); cudaFree(p->d_xw); cudaFree(p->d_gpart);
+    cudaFree(p->d_set); cudaFree(p->d_abs); cudaFree(p->d_E); cudaFree(p->d_eoff); cudaFree(p->d_xw); cudaFree(p->d_gpart); cudaFree(p->d_gz); cudaFree(p->d_bv); cudaFree(p->d_s0);
     delete p;
 }
 
@@ -432,6 +432,18 @@ extern "C" int fdb_kshap_plan_info(const fdb_kshap_plan* p, int* info8) {
     return FDB_OK;
 }
 
+extern "C" int fdb_kshap_plan_set_num_features(fdb_kshap_plan* p, int k) {
+    FDB_REQUIRE(p != nullptr, FDB_ERR_ARG, "plan is NULL");
+    FDB_REQUIRE(k >= 0 && k <= 16, FDB_ERR_ARG, "num_features must be in [0, 16] (0 = no feature selection), got %d", k);
+    if (k > 0) {
+        FDB_CUDA(cudaSetDevice(p->ctx->device));
+        int rc = fdb_kshap_prepare_lars(p);
+        if (rc != FDB_OK) return rc;
+    }
+    p->num_features = k;
+    return FDB_OK;
+}
+
 extern "C" int fdb_kshap_explain_dev(fdb_kshap_plan* p, void* stream, int64_t n_rows, const float* x,
                                      const int32_t* set_idx, int evaluator, float* phi, float* ey_out, double* abs_sum) {
     FDB_REQUIRE(p != nullptr, FDB_ERR_ARG, "plan is NULL");
@@ -455,7 +467,7 @@ extern "C" int fdb_kshap_explain_dev(fdb_kshap_plan* p, void* stream, int64_t n_
             int rc = fdb_kshap_launch_eval_tc(p, st, xb, r0, nb, sb, p->d_ey);
             if (rc != FDB_OK) return rc;
         } else if (evaluator == FDB_KSHAP_EVAL_FACTORED) {
-            int rc = fdb_kshap_launch_eval_fx(p, st, xb, nb, ey_out ? p->d_ey : nullptr);
+            int rc = fdb_kshap_launch_eval_fx(p, st, xb, nb, (ey_out || p->num_features > 0) ? p->d_ey : nullptr);
             if (rc != FDB_OK) return rc;
         } else {
             dim3 grid(p->m_pad / 128, nb);
@@ -465,6 +477,11 @@ extern "C" int fdb_kshap_explain_dev(fdb_kshap_plan* p, void* stream, int64_t n_
         if (ey_out)
             FDB_CUDA(cudaMemcpy2DAsync(ey_out + r0 * p->n_masks, (size_t)p->n_masks * 4, p->d_ey, (size_t)p->m_pad * 4,
                                        (size_t)p->n_masks * 4, nb, cudaMemcpyDeviceToDevice, st));
+        if (p->num_features > 0) {
+            int rc = fdb_kshap_launch_lars_solve(p, st, xb, r0, nb, sb, phi + r0 * FDB_F, abs_sum, r0 > 0 ? 1 : 0, n_rows);
+            if (rc != FDB_OK) return rc;
+            continue;
+        }
         int grid = (nb + 3) / 4;
         const int cap = ctx->sm_count * 8;
         if (grid > cap) grid = cap;

@@ -35,6 +35,10 @@ struct fdb_kshap_plan {
     float* d_E = nullptr;              // factored evaluator (single set): [tile][chunk][128][cbs] 2^(e - o_m)
     float* d_eoff = nullptr;           // [m_pad] exponent centres o_m
     float* d_xw = nullptr;             // [m_pad][32] kw_m * x_mj
+    double* d_gz = nullptr;            // [S][30][32] Z'WZ, built on demand for l1_reg = num_features(k)
+    double* d_bv = nullptr;            // [S][32]
+    double* d_s0 = nullptr;            // [S]
+    int num_features = 0;              // 0 = plain WLS over all features; k = LARS selection of k features first
     float* d_gpart = nullptr;          // [batch_rows][m_pad/32][32] partial X'W y written by K2f, folded by K3
 };
 
@@ -47,3 +51,8 @@ int fdb_kshap_launch_eval_tc(fdb_kshap_plan* p, cudaStream_t st, const float* x,
 // K2f: factored evaluator for single-set plans (kshap_eval_fx.cu).
 int fdb_kshap_build_factored(fdb_kshap_plan* pl, const double* bg_host);
 int fdb_kshap_launch_eval_fx(fdb_kshap_plan* pl, cudaStream_t st, const float* x, int n_rows, float* ey);
+
+// l1_reg = "num_features(k)": LARS selection + reduced WLS (kshap_lars.cu)
+int fdb_kshap_prepare_lars(fdb_kshap_plan* p);
+int fdb_kshap_launch_lars_solve(fdb_kshap_plan* p, cudaStream_t st, const float* x, int64_t row_offset, int n_rows,
+                                const int32_t* set_idx, float* phi, double* abs_sum, int accumulate, int64_t total_rows);

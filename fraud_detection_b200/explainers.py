@@ -150,6 +150,10 @@ class KernelShapPlan:
         self._h = h.value
         self.expected_value = float(_lib.lib.fdb_kshap_expected_value(self._h))
 
+    def set_num_features(self, k: int) -> None:
+        """``l1_reg="num_features(k)"``: LARS-select k features per row before the constrained WLS (0 = off)."""
+        _lib.check(_lib.lib.fdb_kshap_plan_set_num_features(self._h, int(k)))
+
     def info(self) -> dict:
         import ctypes as C
         arr = (C.c_int * 8)()
@@ -200,7 +204,8 @@ class B200KernelExplainer:
     - a different sampler from the reference, meant for throughput runs (SURVEY.md section 7);
     single-set plans use the factored evaluator (K2f: one exponential per (row, coalition)).
     ``masks=(Z, kw)`` or a list of per-row pairs feeds exported reference masks instead.
-    Only ``l1_reg=False`` (plain WLS over all features) runs on the GPU.
+    ``l1_reg=False`` (plain WLS over all features) and ``l1_reg="num_features(k)"`` (shap's recalled default
+    is k = 10: LARS feature selection on the augmented system, then WLS over the selected features) run on the GPU.
     """
 
     def __init__(self, model, data, link="identity", device=None, keep_index=False, **kwargs):
@@ -244,9 +249,14 @@ class B200KernelExplainer:
     def shap_values(self, X, nsamples="auto", l1_reg=False, mask_mode="per_row", masks=None, evaluator=EVAL_AUTO,
                     random=None, silent=True, **kwargs):
         from . import sampler
-        if l1_reg not in (False, 0):
-            raise NotImplementedError("only l1_reg=False (plain constrained WLS) runs on the B200 path; "
-                                      "feature-selecting l1_reg modes are listed as next in SURVEY.md 8(f)")
+        num_features = 0
+        if isinstance(l1_reg, str) and l1_reg.startswith("num_features("):
+            num_features = int(l1_reg[len("num_features("):-1])
+            if not 1 <= num_features <= 16:
+                raise ValueError("num_features(k) is supported for 1 <= k <= 16")
+        elif l1_reg not in (False, 0):
+            raise NotImplementedError("l1_reg must be False/0 (plain constrained WLS) or 'num_features(k)'; "
+                                      "'auto'/'aic'/'bic'/a Lasso alpha are not available on the B200 path")
         A, single = _plain_rows(X)
         A64 = A.astype(np.float64, copy=False)
         varying = self._varying(A64)
@@ -287,6 +297,8 @@ class B200KernelExplainer:
         bits, kw = self._pad_sets(sets)
         plan = KernelShapPlan(self.coef, self.intercept, self.data, bits, kw, self.link, self.device)
         try:
+            if num_features:
+                plan.set_num_features(num_features)
             phi = plan.explain_host(Xr, None, evaluator)
         finally:
             plan.close()

@@ -131,6 +131,10 @@ int fdb_kshap_plan_create(fdb_ctx* ctx, const double* coef, double intercept, in
 int fdb_kshap_plan_destroy(fdb_kshap_plan* plan);
 double fdb_kshap_expected_value(const fdb_kshap_plan* plan);
 int fdb_kshap_plan_info(const fdb_kshap_plan* plan, int* info8);
+/* l1_reg = "num_features(k)" of KernelExplainer.shap_values: k > 0 selects k features per row with LARS on the
+ * augmented system (sklearn lars_path semantics, float64) and solves the constrained WLS over them only;
+ * k = 0 (default) is l1_reg=False.  k <= 16. */
+int fdb_kshap_plan_set_num_features(fdb_kshap_plan* plan, int k);
 int fdb_kshap_explain_dev(fdb_kshap_plan* plan, void* stream, int64_t n_rows, const float* x,
                           const int32_t* set_idx, int evaluator, float* phi, float* ey_out, double* abs_sum);
 int fdb_kshap_explain_host(fdb_kshap_plan* plan, int64_t n_rows, const float* x, const int32_t* set_idx,

@@ -181,7 +181,50 @@ def test_explainer_class_matches_oracle_with_same_seed(params):
     shared = expl.shap_values(X, nsamples=2048, mask_mode="shared", random=np.random.RandomState(8))
     np.testing.assert_allclose(shared.sum(1) + expl.expected_value, f(X), atol=1e-5)
     with pytest.raises(NotImplementedError):
-        expl.shap_values(X, l1_reg="num_features(10)")
+        expl.shap_values(X, l1_reg="aic")
+
+
+@pytest.mark.parametrize("k", [10, 3, 1, 16])
+@pytest.mark.parametrize("evaluator", [TC, FX])
+def test_num_features_selection_matches_sklearn_lars(params, k, evaluator):
+    """l1_reg="num_features(k)": LARS selection + reduced WLS on the GPU against the oracle (sklearn lars_path).
+    The oracle is fed the GPU's own coalition expectations, so both sides select from identical inputs."""
+    bg, X, f = _setup(params, 100, 48, seed=12)
+    Z, kw, _ = ks.sample_coalitions(30, 2048, np.random.RandomState(12))
+    plan = _plan(params, bg, [(Z, kw)])
+    plan.set_num_features(k)
+    phi, ey, abs_sum = _run(plan, X, evaluator)
+    fnull = float(f(bg).mean())
+    same = 0
+    for i, x in enumerate(X):
+        ref = ks.solve(Z, kw, ey[i].astype(np.float64), float(f(x[None])[0]), fnull, l1_reg=f"num_features({k})")
+        assert np.count_nonzero(phi[i]) <= k
+        np.testing.assert_allclose(phi[i].sum() + fnull, f(x[None])[0], atol=1e-5)
+        if np.array_equal(ref != 0, phi[i] != 0):
+            same += 1
+            scale = np.abs(ref).max()
+            assert np.all(np.abs(phi[i] - ref) <= 1e-4 * scale + 1e-9)
+    assert same >= len(X) - 1, f"selected feature sets differ on {len(X) - same} of {len(X)} rows"
+    np.testing.assert_allclose(abs_sum[:30], np.abs(phi).sum(0), rtol=1e-6, atol=1e-12)
+    plan.set_num_features(0)
+    phi0, _, _ = _run(plan, X, evaluator, want_ey=False)
+    assert np.count_nonzero(phi0[0]) == 30
+    plan.close()
+
+
+def test_num_features_end_to_end_vs_oracle(params):
+    """Whole explainer call with the reference's default-style l1_reg, same seed on both sides."""
+    from fraud_detection_b200 import B200KernelExplainer
+    bg, X, f = _setup(params, 100, 16, seed=13)
+    expl = B200KernelExplainer((params.coef, params.intercept), bg)
+    phi = expl.shap_values(X, nsamples=2048, l1_reg="num_features(10)", random=np.random.RandomState(3))
+    ref = ks.shap_values(f, X, bg, nsamples=2048, l1_reg="num_features(10)", random=np.random.RandomState(3))
+    agree = [np.array_equal(a != 0, b != 0) for a, b in zip(phi, ref)]
+    assert sum(agree) >= len(X) - 1
+    for a, b, ok in zip(phi, ref, agree):
+        if ok:
+            assert np.all(np.abs(a - b) <= 1e-4 * np.abs(b).max() + 1e-9)
+    np.testing.assert_allclose(phi.sum(1) + expl.expected_value, f(X), atol=1e-5)
 
 
 def test_degenerate_rows_and_errors(params):
