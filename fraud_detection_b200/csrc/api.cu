@@ -104,6 +104,7 @@ int check_common(const fdb_ctx* ctx, int dtype, int64_t n_rows, const void* x) {
 // fast path for serving-size batches.
 int run_host(fdb_ctx* ctx, int dtype, int64_t n, const void* x, const LinearParams& prm, bool divide,
              void* proba, int proba_cols, void* logit, void* phi, uint8_t* cls, double* abs_sum) {
+    std::lock_guard<std::mutex> lock(ctx->host_mu);
     DeviceGuard guard(ctx->device);
     FDB_REQUIRE(guard.ok, FDB_ERR_CUDA, "cannot select device %d", ctx->device);
     const size_t es = elem_size(dtype);
@@ -218,7 +219,7 @@ extern "C" int fdb_ctx_create(int device, fdb_ctx** out) {
     cudaError_t e = cudaGetDeviceCount(&count);
     FDB_REQUIRE(e == cudaSuccess && count > 0, FDB_ERR_CUDA, "no CUDA device available (%s); libfdb200 has no CPU fallback",
                 e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
-    FDB_REQUIRE(device >= 0 && device < count, FDB_ERR_ARG, "device %d out of range (0..%d)", device, count - 1);
+    FDB_REQUIRE(device >= 0 && device < count && device < FDB_MAX_DEVICES, FDB_ERR_ARG, "device %d out of range (0..%d)", device, count - 1);
     DeviceGuard guard(device);
     FDB_REQUIRE(guard.ok, FDB_ERR_CUDA, "cannot select device %d", device);
     fdb_ctx* ctx = new (std::nothrow) fdb_ctx();

@@ -3,6 +3,8 @@
 
 #include <cuda_runtime.h>
 #include <stdint.h>
+
+#include <mutex>
 #include <stdio.h>
 
 #include "../../include/fdb200.h"
@@ -34,6 +36,7 @@ void fdb_set_error(const char* fmt, ...);
 static inline bool fdb_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 // ---- context --------------------------------------------------------------------------
+constexpr int FDB_MAX_DEVICES = 64;        // device indices a process may use
 constexpr int FDB_PIPE_SLOTS = 3;          // host pipeline depth (H2D / kernel / D2H overlap)
 constexpr int FDB_MAX_GRID = 148 * 16;     // upper bound on CTAs of any grid-stride kernel
 
@@ -47,6 +50,7 @@ struct fdb_pipe_slot {
 };
 
 struct fdb_ctx {
+    std::mutex host_mu;                    // serialises the *_host entry points (they share streams and staging)
     int device = 0;
     int sm_count = 0;
     // scratch of the |phi| column-sum reduction: per-CTA partials + arrival ticket

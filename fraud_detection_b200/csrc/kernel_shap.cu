@@ -503,6 +503,7 @@ extern "C" int fdb_kshap_explain_host(fdb_kshap_plan* p, int64_t n_rows, const f
     if (abs_sum) memset(abs_sum, 0, 32 * sizeof(double));
     if (n_rows == 0) return FDB_OK;
     fdb_ctx* ctx = p->ctx;
+    std::lock_guard<std::mutex> lock(ctx->host_mu);
     FDB_CUDA(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->slot[0].stream;
     for (int64_t r0 = 0; r0 < n_rows; r0 += p->batch_rows) {

@@ -397,11 +397,11 @@ int fdb_kshap_launch_eval_fx(fdb_kshap_plan* pl, cudaStream_t st, const float* x
     p.inv_bg = 1.0f / (float)pl->n_bg;
     p.lnull = pl->link == 1 ? (float)log(pl->fnull / (1.0 - pl->fnull)) : (float)pl->fnull;
     const size_t smem = 2 * kEStageBytes + 2 * kTileBytes + 2 * kQBytes + sizeof(FxBars) + 64;
-    static bool configured = false;
-    if (!configured) {
+    static bool configured[FDB_MAX_DEVICES] = {};          // function attributes are per device
+    if (!configured[pl->ctx->device]) {
         FDB_CUDA(cudaFuncSetAttribute(kshap_eval_fx_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         FDB_CUDA(cudaFuncSetAttribute(kshap_eval_fx_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
+        configured[pl->ctx->device] = true;
     }
     const int64_t n_units = (int64_t)((n_rows + 127) / 128) * p.tiles;
     int64_t grid = n_units < pl->ctx->sm_count ? n_units : pl->ctx->sm_count;

@@ -343,10 +343,10 @@ int fdb_kshap_launch_eval_tc(fdb_kshap_plan* pl, cudaStream_t st, const float* x
     const size_t smem = (size_t)pl->nsplit * pl->nb_pad * 64 + kPipes * kAStages * (kATileBytes + kBqBytes) + sizeof(TcBars) + 64;
     FDB_REQUIRE(smem <= 227 * 1024, FDB_ERR_ARG, "background of %d rows with %d operand splits needs %zu bytes of shared memory",
                 pl->n_bg, pl->nsplit, smem);
-    static size_t configured = 0;
-    if (smem > configured) {
+    static size_t configured[FDB_MAX_DEVICES] = {};        // function attributes are per device
+    if (smem > configured[pl->ctx->device]) {
         FDB_CUDA(cudaFuncSetAttribute(kshap_eval_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
+        configured[pl->ctx->device] = smem;
     }
     const int64_t n_items = (int64_t)n_rows * p.tiles;
     int64_t grid = (n_items + kPipes - 1) / kPipes;

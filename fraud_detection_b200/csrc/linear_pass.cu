@@ -210,8 +210,8 @@ int launch_typed(fdb_ctx* ctx, cudaStream_t st, int64_t n_rows, const void* x, c
     int64_t want = (n_groups + 2 * kWarps - 1) / (2 * kWarps);   // 2 groups per warp minimum
     if (want < 1) want = 1;
     // persistent grid-stride launch: exactly the resident CTA count (multiple of the SM count)
-    static int per_sm[2] = {0, 0};
-    int& occ = per_sm[divide ? 1 : 0];
+    static int per_sm[FDB_MAX_DEVICES][2] = {};
+    int& occ = per_sm[ctx->device][divide ? 1 : 0];
     if (occ == 0) {
         int v = 0;
         cudaError_t e = divide

@@ -258,11 +258,11 @@ template <typename T, bool DIVIDE, bool WRITE_PHI>
 int launch_inst(fdb_ctx* ctx, cudaStream_t st, int64_t n_rows, const void* x, const KParams<T>& kp, void* proba,
                 int proba_cols, void* logit, void* phi, uint8_t* cls, double* abs_sum, double* partials,
                 unsigned int* ticket) {
-    static bool configured = false;
+    static bool configured[FDB_MAX_DEVICES] = {};          // function attributes are per device
     auto kern = linear_pass_tma_kernel<T, DIVIDE, WRITE_PHI>;
-    if (!configured) {
+    if (!configured[ctx->device]) {
         FDB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TmaSmem)));
-        configured = true;
+        configured[ctx->device] = true;
     }
     constexpr int TR = kTileBytes / (FDB_F * (int)sizeof(T));
     const int64_t n_tiles = n_rows / TR;

@@ -1,0 +1,61 @@
+"""GPU: the micro-batcher and the XAI-task helper return what the one-row reference calls return."""
+
+import threading
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+from oracle import linear_shap, scoring, synth  # noqa: E402
+
+
+def test_microbatcher_equals_one_row_calls(params):
+    import warnings
+    from fraud_detection_b200 import B200LinearExplainer, wrap
+    from fraud_detection_b200.serving import MicroBatcher
+    warnings.filterwarnings("ignore")
+    scaler_sk, model_sk, _ = scoring.live_estimators(params)
+    scaler, model = wrap(scaler_sk), wrap(model_sk)
+    expl = B200LinearExplainer(model, np.zeros((1, 30)))
+    X = synth.rows(512, seed=4)
+    Xs = scaler_sk.transform(X)
+    want_p, want_c = model_sk.predict_proba(Xs), model_sk.predict(Xs)
+    want_phi = linear_shap.shap_values(model_sk.coef_[0], np.zeros(30), Xs)
+    res = [None] * len(X)
+    with MicroBatcher(scaler, model, explainer=expl, max_batch=256, max_wait_us=5000) as mb:
+        def client(lo, hi):
+            for i in range(lo, hi):
+                res[i] = mb.submit(X[i]).result(30)
+        ts = [threading.Thread(target=client, args=(k * 64, (k + 1) * 64)) for k in range(8)]
+        [t.start() for t in ts]
+        [t.join() for t in ts]
+        assert mb.batches < len(X)
+    for i, r in enumerate(res):
+        assert r.prediction == want_c[i]
+        np.testing.assert_allclose(r.proba, want_p[i], atol=1e-12)
+        np.testing.assert_allclose(r.shap_values, want_phi[i], atol=1e-10)
+
+
+def test_xai_task_helper_keeps_the_reference_quirks(params):
+    from fraud_detection_b200 import wrap
+    from fraud_detection_b200.serving import attributions_for_task
+    scaler_sk, model_sk, _ = scoring.live_estimators(params)
+    scaler, model = wrap(scaler_sk), wrap(model_sk)
+    names = params.feature_names
+    row = synth.rows(1, seed=5)[0]
+    # keys the task actually receives from api/app.py:243 -> every lookup misses -> all-zero row (quirk Q2)
+    p0, attr0 = attributions_for_task(model, names, {f"feature_{i}": float(v) for i, v in enumerate(row)})
+    assert abs(p0 - 1.0 / (1.0 + np.exp(-params.intercept))) < 1e-12 and all(v == 0.0 for v in attr0.values())
+    # matching keys: score of the UNSCALED row and coef * x, as xai_tasks.py:97,106-107 compute them
+    data = dict(zip(names, row.tolist()))
+    p1, attr1 = attributions_for_task(model, names, data)
+    assert abs(p1 - model_sk.predict_proba(row[None])[0, 1]) < 1e-12
+    np.testing.assert_allclose([attr1[n] for n in names], linear_shap.coef_times_x(model_sk.coef_, row), rtol=1e-12)
+    # opt-in fix: apply the scaler first
+    p2, attr2 = attributions_for_task(model, names, data, scaler=scaler, apply_scaler=True)
+    xs = scaler_sk.transform(row[None])
+    assert abs(p2 - model_sk.predict_proba(xs)[0, 1]) < 1e-12
+    np.testing.assert_allclose([attr2[n] for n in names], model_sk.coef_[0] * xs[0], rtol=1e-10, atol=1e-12)

@@ -1,0 +1,85 @@
+"""Micro-batcher host logic on CPU with stand-in estimators (the oracle math), no GPU needed."""
+
+import threading
+import time
+
+import numpy as np
+import pytest
+
+from fraud_detection_b200.serving import MicroBatcher
+from oracle import scoring, synth
+
+
+class _Scaler:
+    def __init__(self, p):
+        self.p, self.calls = p, 0
+
+    def transform(self, X):
+        self.calls += 1
+        return scoring.transform(self.p, X)
+
+
+class _Model:
+    n_features_in_ = 30
+
+    def __init__(self, p):
+        self.p, self.batch_sizes = p, []
+
+    def score_rows(self, Xs):
+        if not np.all(np.isfinite(Xs)):
+            raise ValueError("Input X contains NaN.")
+        self.batch_sizes.append(len(Xs))
+        return scoring.predict(self.p, Xs), scoring.predict_proba(self.p, Xs)
+
+
+def test_concurrent_requests_share_calls_and_get_their_own_rows(params):
+    scaler, model = _Scaler(params), _Model(params)
+    X = synth.rows(400, seed=1)
+    want_pred = scoring.predict(params, scoring.transform(params, X))
+    want_proba = scoring.predict_proba(params, scoring.transform(params, X))
+    with MicroBatcher(scaler, model, max_batch=64, max_wait_us=20000) as mb:
+        out = [None] * len(X)
+
+        def client(i0, i1):
+            for i in range(i0, i1):
+                out[i] = mb.score(X[i], timeout=30)
+        threads = [threading.Thread(target=client, args=(k * 50, (k + 1) * 50)) for k in range(8)]
+        [t.start() for t in threads]
+        [t.join() for t in threads]
+        assert mb.rows == 400 and mb.batches < 400            # requests were coalesced
+    assert max(model.batch_sizes) <= 64
+    for i, (pred, proba) in enumerate(out):
+        assert pred == want_pred[i]
+        np.testing.assert_array_equal(proba, want_proba[i])
+
+
+def test_bad_request_fails_alone(params):
+    with MicroBatcher(_Scaler(params), _Model(params), max_batch=8, max_wait_us=50000) as mb:
+        good = [mb.submit(r) for r in synth.rows(3, seed=2)]
+        bad_nan = mb.submit(np.full(30, np.nan))
+        bad_len = mb.submit(np.zeros(29))
+        with pytest.raises(ValueError, match="must have 30 features"):
+            bad_len.result(10)
+        with pytest.raises(ValueError, match="NaN"):
+            bad_nan.result(10)
+        for f in good:
+            assert f.result(10).proba.shape == (2,)
+
+
+def test_single_request_latency_is_bounded_by_max_wait(params):
+    with MicroBatcher(_Scaler(params), _Model(params), max_batch=4096, max_wait_us=2000) as mb:
+        mb.score(np.zeros(30))
+        t0 = time.perf_counter()
+        mb.score(np.ones(30))
+        assert time.perf_counter() - t0 < 0.2
+
+
+def test_asyncio_entry_point(params):
+    import asyncio
+
+    async def go():
+        with MicroBatcher(_Scaler(params), _Model(params), max_wait_us=1000) as mb:
+            res = await asyncio.gather(*[mb.score_async(r) for r in synth.rows(20, seed=3)])
+            return res
+    res = asyncio.run(go())
+    assert len(res) == 20 and all(r.proba.shape == (2,) for r in res)

@@ -70,12 +70,61 @@ def run(batches=(1, 2, 4, 8, 16, 32, 64, 128, 256, 512, 1024, 2048, 4096), calls
     return out
 
 
+def run_microbatch(n_requests=20000, clients=(1, 8, 64), device=None):
+    """Requests/s for one-row requests: the reference pattern (one sklearn call chain per request), the drop-in
+    called once per request, and the drop-in behind MicroBatcher with concurrent client threads."""
+    import threading
+    from fraud_detection_b200 import wrap
+    from fraud_detection_b200.serving import MicroBatcher
+    from oracle import scoring, synth
+
+    warnings.filterwarnings("ignore")
+    scaler_sk, model_sk, origin = scoring.live_estimators()
+    scaler, model = wrap(scaler_sk, device=device), wrap(model_sk, device=device)
+    X = synth.rows(n_requests, seed=7)
+    out = {"requests": n_requests, "estimators": origin}
+    n_seq = min(n_requests, 3000)
+    t0 = time.perf_counter()
+    for i in range(n_seq):
+        xs = scaler_sk.transform(X[i:i + 1]); model_sk.predict(xs); model_sk.predict_proba(xs)
+    out["sklearn_one_row_rps"] = n_seq / (time.perf_counter() - t0)
+    t0 = time.perf_counter()
+    for i in range(n_seq):
+        model.score_rows(scaler.transform(X[i:i + 1]))
+    out["b200_one_row_rps"] = n_seq / (time.perf_counter() - t0)
+    out["microbatcher"] = []
+    for nc in clients:
+        with MicroBatcher(scaler, model, max_batch=4096, max_wait_us=200) as mb:
+            mb.score(X[0])
+            per = n_requests // nc
+            lat = [None] * nc
+
+            def client(c):
+                ts = np.empty(per)
+                for k in range(per):
+                    t1 = time.perf_counter()
+                    mb.score(X[c * per + k])
+                    ts[k] = time.perf_counter() - t1
+                lat[c] = ts
+            th = [threading.Thread(target=client, args=(c,)) for c in range(nc)]
+            t0 = time.perf_counter()
+            [t.start() for t in th]
+            [t.join() for t in th]
+            dt = time.perf_counter() - t0
+            allv = np.concatenate(lat)
+            out["microbatcher"].append({"clients": nc, "rps": per * nc / dt, "p50_ms": float(np.percentile(allv, 50) * 1e3),
+                                        "p99_ms": float(np.percentile(allv, 99) * 1e3), "mean_batch": mb.rows / max(mb.batches, 1)})
+    return out
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--calls", type=int, default=10000)
     ap.add_argument("--out", default="")
     a = ap.parse_args()
     res = run(calls=a.calls)
+    res["microbatch"] = run_microbatch()
+    print(json.dumps(res["microbatch"]))
     txt = json.dumps(res, indent=1)
     if a.out:
         os.makedirs(os.path.dirname(a.out), exist_ok=True)
