@@ -59,3 +59,22 @@ def test_xai_task_helper_keeps_the_reference_quirks(params):
     xs = scaler_sk.transform(row[None])
     assert abs(p2 - model_sk.predict_proba(xs)[0, 1]) < 1e-12
     np.testing.assert_allclose([attr2[n] for n in names], model_sk.coef_[0] * xs[0], rtol=1e-10, atol=1e-12)
+
+
+def test_score_file_end_to_end(params, tmp_path):
+    """CSV -> pinned rows -> fused raw-row pass, against pandas + sklearn + numpy linear SHAP."""
+    import pandas as pd
+    from fraud_detection_b200 import io as fio
+    from fraud_detection_b200.device import FraudScorer
+    X = synth.reference_rows(50000)
+    path = tmp_path / "creditcard.csv"
+    pd.DataFrame(np.column_stack([X, np.zeros(len(X))]), columns=synth.FEATURE_NAMES + ["Class"]).to_csv(path, index=False)
+    scorer = FraudScorer(params.coef, params.intercept, params.mean, params.scale)
+    out = fio.score_file(str(path), scorer, dtype=np.float64)
+    Xs = scoring.transform(params, X)                      # the CSV round-trips exactly (correctly rounded parser)
+    np.testing.assert_allclose(out["proba"], scoring.predict_proba(params, Xs)[:, 1], atol=1e-12)
+    phi_ref = linear_shap.shap_values(params.coef, np.zeros(30), Xs)
+    np.testing.assert_allclose(out["phi"], phi_ref, atol=1e-9)
+    ref_abs, ref_top3 = linear_shap.global_summary(phi_ref)
+    np.testing.assert_allclose(out["mean_abs_shap"], ref_abs, rtol=1e-10)
+    assert list(out["top3"]) == list(ref_top3) and out["rows"] == 50000
