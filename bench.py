@@ -52,7 +52,7 @@ def parse_args():
                     help="rows per GPU resident in HBM (config 2: 1e8)")
     ap.add_argument("--e2e-rows", type=int, default=int(os.environ.get("FDB_BENCH_E2E_ROWS", 8_000_000)))
     ap.add_argument("--kshap-rows", type=int, default=int(os.environ.get("FDB_BENCH_KSHAP_ROWS", 100_000)))
-    ap.add_argument("--kshap-per-row", type=int, default=1024)
+    ap.add_argument("--kshap-per-row", type=int, default=32768)
     ap.add_argument("--kshap-cpu-rows", type=int, default=256)
     ap.add_argument("--no-kshap", action="store_true")
     ap.add_argument("--cpu-rows", type=int, default=int(os.environ.get("FDB_BENCH_CPU_ROWS", 4_000_000)))
@@ -304,21 +304,23 @@ def bench_kernel_shap(args, torch, dist, device, rank, world, prm, sm_max_mhz):
                   "d2h_bytes_per_step": rows * 120 + 256, "api": "fdb_kshap_explain_host (pinned host rows in, phi out)"}
     plan.close()
 
-    # the reference's sampler: a different coalition set for every explained row
+    # the reference's behaviour: a different coalition set for every explained row, drawn on the device
     pr = args.kshap_per_row
-    rs = np.random.RandomState(1)
-    sets = [sampler.sample_coalitions(30, nsamples, rs) for _ in range(pr)]
-    plan2 = KernelShapPlan(prm.coef, prm.intercept, bg, np.stack([b for b, _ in sets]), np.stack([w for _, w in sets]),
-                           device=device.index)
     x2, phi2 = x[:pr].contiguous(), torch.empty((pr, 30), dtype=torch.float32, device=device)
+    KernelShapPlan.sampled(prm.coef, prm.intercept, bg, 64, nsamples, seed=0, device=device.index).close()   # warm the module
+    sync()
+    t0 = time.perf_counter()
+    plan2 = KernelShapPlan.sampled(prm.coef, prm.intercept, bg, pr, nsamples, seed=1 + rank, device=device.index)
+    torch.cuda.synchronize()
+    t_plan = time.perf_counter() - t0
     ms2 = timed(lambda: plan2.explain_dev(x2, phi=phi2), steps)
-    out["per_row_masks"] = {"rows": pr, "value": pr * world / (ms2 * 1e-3), "unit": "explained rows/s", "ms_per_step": ms2}
+    out["per_row_masks"] = {"rows": pr, "sets": pr, "sampler": "device (Philox, reference schedule)",
+                            "value": pr * world / (ms2 * 1e-3), "unit": "explained rows/s", "ms_per_step": ms2,
+                            "plan_ms": t_plan * 1e3,
+                            "value_including_sampling": pr * world / (ms2 * 1e-3 + t_plan),
+                            "note": "plan_ms = drawing the sets + operand images + per-set (X'WX)^-1, paid once per batch of rows"}
     plan2.close()
 
-    # SFU roofline: sigmoid = ex2 + rcp = 2 MUFU ops; 16 MUFU lanes per SM per clock
-    sms = torch.cuda.get_device_properties(device).multi_processor_count
-    clock_hz = (sm_max_mhz or 1965) * 1e6
-    peak = 16.0 * sms * clock_hz
     # SFU roofline (north-star form: one exp per sigmoid against SFU exp throughput).  K2 issues 1.25 MUFU ops per
     # sigmoid (ex2 + a reciprocal shared by four); K2f issues 0.26 (reciprocal shared by four + one ex2 per 100), so it
     # is bound by issue slots (4.5 per sigmoid), not by the SFU, and may exceed the one-exp-per-sigmoid line.

@@ -52,6 +52,8 @@ _SIGS = {
     "fdb_linear_pass_host": (_i, [_vp, _i, _i64, _vp, _dp, _dp, C.c_double, _vp, _i, _vp, _vp, _vp, _vp]),
     "fdb_linear_pass_noalloc": (_i, [_vp, _i, _i64, _vp, _dp, _dp, C.c_double, _vp, _i, _vp, _vp, _vp, _vp]),
     "fdb_kshap_plan_create": (_i, [_vp, _dp, C.c_double, _i, _vp, _i, _i, _vp, _vp, _i, C.POINTER(_vp)]),
+    "fdb_kshap_plan_create_sampled": (_i, [_vp, _dp, C.c_double, _i, _vp, _i, _i, C.c_uint64, _i, C.POINTER(_vp)]),
+    "fdb_kshap_plan_get_masks": (_i, [_vp, _i, _vp, _vp]),
     "fdb_kshap_plan_destroy": (_i, [_vp]),
     "fdb_kshap_expected_value": (C.c_double, [_vp]),
     "fdb_kshap_plan_info": (_i, [_vp, C.POINTER(C.c_int)]),

@@ -284,10 +284,11 @@ void fdb_kshap_split(double v, int fmt, int n, uint16_t* out) {
     }
 }
 
-extern "C" int fdb_kshap_plan_create(fdb_ctx* ctx, const double* coef, double intercept, int n_bg, const double* bg,
-                                     int n_sets, int n_masks, const uint32_t* bits, const double* kw, int link,
-                                     fdb_kshap_plan** out) {
-    FDB_REQUIRE(ctx && coef && bg && bits && kw && out, FDB_ERR_ARG, "NULL argument");
+// bits == nullptr: draw the coalition sets on the device (n_masks = resolved nsamples, seed)
+static int plan_create_impl(fdb_ctx* ctx, const double* coef, double intercept, int n_bg, const double* bg,
+                            int n_sets, int n_masks, const uint32_t* bits, const double* kw, int link,
+                            unsigned long long seed, fdb_kshap_plan** out) {
+    FDB_REQUIRE(ctx && coef && bg && out, FDB_ERR_ARG, "NULL argument");
     *out = nullptr;
     FDB_REQUIRE(n_bg >= 1 && n_bg <= FDB_KSHAP_MAX_BG, FDB_ERR_ARG, "background rows must be in [1, %d], got %d", FDB_KSHAP_MAX_BG, n_bg);
     FDB_REQUIRE(n_sets >= 1 && n_masks >= 1, FDB_ERR_ARG, "need at least one mask set and one mask");
@@ -337,9 +338,9 @@ extern "C" int fdb_kshap_plan_create(fdb_ctx* ctx, const double* coef, double in
             for (int sidx = 0; sidx < p->nsplit; ++sidx)
                 bimg[(size_t)sidx * p->nb_pad * 32 + (size_t)(b >> 3) * 256 + (k >> 3) * 64 + (b & 7) * 8 + (k & 7)] = parts[sidx];
         }
-    std::vector<uint32_t> hbits(SM, 0u);
-    std::vector<float> hkw(SM, 0.f);
-    for (int s = 0; s < n_sets; ++s)
+    std::vector<uint32_t> hbits(bits ? SM : 0, 0u);
+    std::vector<float> hkw(bits ? SM : 0, 0.f);
+    for (int s = 0; bits && s < n_sets; ++s)
         for (int m = 0; m < n_masks; ++m) {
             hbits[(size_t)s * p->m_pad + m] = bits[(size_t)s * n_masks + m] & 0x3FFFFFFFu;
             hkw[(size_t)s * p->m_pad + m] = (float)kw[(size_t)s * n_masks + m];
@@ -366,8 +367,13 @@ extern "C" int fdb_kshap_plan_create(fdb_ctx* ctx, const double* coef, double in
         TRY(cudaMalloc((void**)&p->d_phi, (size_t)p->batch_rows * FDB_F * 4));
         TRY(cudaMalloc((void**)&p->d_set, (size_t)p->batch_rows * 4));
         TRY(cudaMalloc((void**)&p->d_abs, 32 * 8));
-        TRY(cudaMemcpy(p->d_bits, hbits.data(), SM * 4, cudaMemcpyHostToDevice));
-        TRY(cudaMemcpy(p->d_kw, hkw.data(), SM * 4, cudaMemcpyHostToDevice));
+        if (bits) {
+            TRY(cudaMemcpy(p->d_bits, hbits.data(), SM * 4, cudaMemcpyHostToDevice));
+            TRY(cudaMemcpy(p->d_kw, hkw.data(), SM * 4, cudaMemcpyHostToDevice));
+        } else {
+            rc = fdb_kshap_sample_on_device(p, n_masks, seed);
+            if (rc != FDB_OK) break;
+        }
         TRY(cudaMemcpy(p->d_P, P.data(), P.size() * 4, cudaMemcpyHostToDevice));
         TRY(cudaMemcpy(p->d_wq, wq, 32 * 4, cudaMemcpyHostToDevice));
         TRY(cudaMemcpy(p->d_bimg, bimg.data(), bimg.size() * 2, cudaMemcpyHostToDevice));
@@ -408,6 +414,29 @@ extern "C" int fdb_kshap_plan_create(fdb_ctx* ctx, const double* coef, double in
     }
     if (rc != FDB_OK) { free_plan(p); return rc; }
     *out = p;
+    return FDB_OK;
+}
+
+extern "C" int fdb_kshap_plan_create(fdb_ctx* ctx, const double* coef, double intercept, int n_bg, const double* bg,
+                                     int n_sets, int n_masks, const uint32_t* bits, const double* kw, int link,
+                                     fdb_kshap_plan** out) {
+    FDB_REQUIRE(bits && kw, FDB_ERR_ARG, "bits / kw is NULL");
+    return plan_create_impl(ctx, coef, intercept, n_bg, bg, n_sets, n_masks, bits, kw, link, 0ULL, out);
+}
+
+extern "C" int fdb_kshap_plan_create_sampled(fdb_ctx* ctx, const double* coef, double intercept, int n_bg,
+                                             const double* bg, int n_sets, int nsamples, uint64_t seed, int link,
+                                             fdb_kshap_plan** out) {
+    return plan_create_impl(ctx, coef, intercept, n_bg, bg, n_sets, fdb_kshap_resolve_nsamples(nsamples), nullptr, nullptr,
+                            link, (unsigned long long)seed, out);
+}
+
+extern "C" int fdb_kshap_plan_get_masks(const fdb_kshap_plan* p, int set, uint32_t* bits, float* kw) {
+    FDB_REQUIRE(p && bits && kw, FDB_ERR_ARG, "NULL argument");
+    FDB_REQUIRE(set >= 0 && set < p->n_sets, FDB_ERR_ARG, "set %d out of range", set);
+    FDB_CUDA(cudaSetDevice(p->ctx->device));
+    FDB_CUDA(cudaMemcpy(bits, p->d_bits + (size_t)set * p->m_pad, (size_t)p->n_masks * 4, cudaMemcpyDeviceToHost));
+    FDB_CUDA(cudaMemcpy(kw, p->d_kw + (size_t)set * p->m_pad, (size_t)p->n_masks * 4, cudaMemcpyDeviceToHost));
     return FDB_OK;
 }
 

@@ -56,3 +56,7 @@ int fdb_kshap_launch_eval_fx(fdb_kshap_plan* pl, cudaStream_t st, const float* x
 int fdb_kshap_prepare_lars(fdb_kshap_plan* p);
 int fdb_kshap_launch_lars_solve(fdb_kshap_plan* p, cudaStream_t st, const float* x, int64_t row_offset, int n_rows,
                                 const int32_t* set_idx, float* phi, double* abs_sum, int accumulate, int64_t total_rows);
+
+// on-device coalition sampler (kshap_sampler.cu)
+int fdb_kshap_resolve_nsamples(int nsamples);
+int fdb_kshap_sample_on_device(fdb_kshap_plan* pl, int nsamples, unsigned long long seed);

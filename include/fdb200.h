@@ -128,6 +128,13 @@ enum { FDB_KSHAP_EVAL_AUTO = -1, FDB_KSHAP_EVAL_TC = 0, FDB_KSHAP_EVAL_SIMT = 1,
 int fdb_kshap_plan_create(fdb_ctx* ctx, const double* coef, double intercept, int n_bg, const double* bg,
                           int n_sets, int n_masks, const uint32_t* bits, const double* kw, int link,
                           fdb_kshap_plan** out);
+/* Same plan, but the n_sets coalition sets are drawn ON THE DEVICE with the reference's schedule (enumerated
+ * sizes, paired random draws, duplicate merging, weight renormalisation; Philox stream keyed by (seed, set)):
+ * statistically, not bitwise, equivalent to shap's per-row sampling.  nsamples <= 0 means "auto" (2*30 + 2048);
+ * 64 <= nsamples <= 4096.  fdb_kshap_plan_get_masks copies one set back (n_masks entries each). */
+int fdb_kshap_plan_create_sampled(fdb_ctx* ctx, const double* coef, double intercept, int n_bg, const double* bg,
+                                  int n_sets, int nsamples, uint64_t seed, int link, fdb_kshap_plan** out);
+int fdb_kshap_plan_get_masks(const fdb_kshap_plan* plan, int set, uint32_t* bits, float* kw);
 int fdb_kshap_plan_destroy(fdb_kshap_plan* plan);
 double fdb_kshap_expected_value(const fdb_kshap_plan* plan);
 int fdb_kshap_plan_info(const fdb_kshap_plan* plan, int* info8);

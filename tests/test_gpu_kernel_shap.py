@@ -241,3 +241,86 @@ def test_degenerate_rows_and_errors(params):
         KernelShapPlan(params.coef, params.intercept, bg, np.array([1, 2, 3], dtype=np.uint32), np.ones(3))
     with pytest.raises(ValueError):
         KernelShapPlan(params.coef, params.intercept, np.zeros((2000, 30)), np.array([1], dtype=np.uint32), np.ones(1))
+
+
+# --------------------------------------------------------------------------- on-device sampler
+def test_device_sampler_follows_the_reference_schedule(params):
+    from fraud_detection_b200 import KernelShapPlan, sampler
+    bg, X, f = _setup(params, 20, 4, seed=20)
+    n_sets = 64
+    plan = KernelShapPlan.sampled(params.coef, params.intercept, bg, n_sets, 2048, seed=7)
+    assert plan.n_masks == 2048 and plan.n_sets == n_sets
+    host_bits, host_kw = sampler.sample_coalitions(30, 2048, np.random.RandomState(0))
+    wv, _, n_paired = sampler.size_weights(30)
+    seen_sets = set()
+    size_hist = np.zeros(31)
+    for s in range(n_sets):
+        bits, kw = plan.masks(s)
+        # enumerated block: identical to the host schedule (30 singletons + complements, weight 4.352e-3)
+        assert np.array_equal(bits[:60], host_bits[:60])
+        np.testing.assert_allclose(kw[:60], host_kw[:60], rtol=1e-6)
+        used = kw > 0
+        assert used.sum() > 1900 and np.all(used[:used.sum()]) and not np.any(used[used.sum():])   # contiguous, no holes
+        b = bits[used]
+        assert len(np.unique(b)) == len(b)                         # duplicates were merged, not stored twice
+        sizes = np.array([bin(int(v)).count("1") for v in b])
+        assert sizes.min() >= 1 and sizes.max() <= 29
+        np.testing.assert_allclose(kw.sum(), 1.0, rtol=1e-5)
+        np.testing.assert_allclose(kw[60:].sum(), 0.738876, rtol=1e-4)      # weight_left of SURVEY 8(a) step 4
+        # random block comes in (coalition, complement) pairs for the paired sizes
+        rb = b[60:]
+        k = 0
+        while k < len(rb) - 1:
+            if bin(int(rb[k])).count("1") <= n_paired:
+                assert rb[k + 1] == (0x3FFFFFFF ^ rb[k])
+                k += 2
+            else:
+                k += 1
+        seen_sets.add(bits[60:].tobytes())
+        np.add.at(size_hist, sizes[60:], kw[used][60:])        # weights count the draws (duplicates merged)
+    assert len(seen_sets) == n_sets                                # every row gets its own coalitions
+    # size distribution of the drawn coalitions (sizes 2..15; complements mirror them): Shapley-kernel weights
+    expect = wv[1:15].copy(); expect[:13] /= 2; expect /= expect.sum()
+    got = size_hist[2:16] / size_hist[2:16].sum()
+    assert np.abs(got - expect).max() < 0.01
+    # reproducible for a seed, different for another
+    plan2 = KernelShapPlan.sampled(params.coef, params.intercept, bg, 2, 2048, seed=7)
+    plan3 = KernelShapPlan.sampled(params.coef, params.intercept, bg, 2, 2048, seed=8)
+    assert np.array_equal(plan2.masks(1)[0], plan.masks(1)[0]) and not np.array_equal(plan3.masks(1)[0], plan.masks(1)[0])
+    for p_ in (plan, plan2, plan3):
+        p_.close()
+
+
+def test_device_sampled_sets_give_oracle_phi(params):
+    """Per-row sets drawn on the device, exported, and fed to the oracle: same phi (parity with identical masks)."""
+    from fraud_detection_b200 import KernelShapPlan, sampler
+    bg, X, f = _setup(params, 100, 8, seed=21)
+    plan = KernelShapPlan.sampled(params.coef, params.intercept, bg, len(X), 2048, seed=3)
+    phi, ey, _ = _run(plan, X, TC)
+    fnull = float(f(bg).mean())
+    for i, x in enumerate(X):
+        bits, kw = plan.masks(i)
+        Z = sampler.bits_to_masks(bits)
+        e_ref = ks.evaluate(f, x, bg, Z)
+        np.testing.assert_allclose(ey[i], e_ref, atol=2e-6)
+        ref = ks.solve(Z, kw.astype(np.float64), e_ref, float(f(x[None])[0]), fnull)
+        assert np.all(np.abs(phi[i] - ref) <= 1e-4 * np.abs(ref).max() + 1e-9)
+    np.testing.assert_allclose(phi.sum(1) + fnull, f(X), atol=1e-5)
+    plan.close()
+
+
+def test_explainer_with_device_sampler_is_statistically_the_same(params):
+    """Two samplers, same estimator: Kernel SHAP values agree within the Monte-Carlo spread of the host sampler itself."""
+    from fraud_detection_b200 import B200KernelExplainer
+    bg, X, f = _setup(params, 100, 6, seed=22)
+    expl = B200KernelExplainer((params.coef, params.intercept), bg)
+    dev = expl.shap_values(X, nsamples=2048, sampler="device", seed=11)
+    h1 = expl.shap_values(X, nsamples=2048, random=np.random.RandomState(1))
+    h2 = expl.shap_values(X, nsamples=2048, random=np.random.RandomState(2))
+    np.testing.assert_allclose(dev.sum(1) + expl.expected_value, f(X), atol=1e-5)
+    spread = np.abs(h1 - h2).max() + 1e-4
+    assert np.abs(dev - h1).max() < 4 * spread
+    shared = expl.shap_values(X, nsamples=2048, sampler="device", mask_mode="shared", seed=11)
+    np.testing.assert_allclose(shared.sum(1) + expl.expected_value, f(X), atol=1e-5)
+    with pytest.raises(ValueError, match="64 <= nsamples <= 4096"):
+        expl.shap_values(X, nsamples=100000, sampler="device")
