@@ -321,6 +321,9 @@ def bench_kernel_shap(args, torch, dist, device, rank, world, prm, sm_max_mhz):
                             "note": "plan_ms = drawing the sets + operand images + per-set (X'WX)^-1, paid once per batch of rows"}
     plan2.close()
 
+    sms = torch.cuda.get_device_properties(device).multi_processor_count
+    clock_hz = (sm_max_mhz or 1965) * 1e6
+    peak = 16.0 * sms * clock_hz
     # SFU roofline (north-star form: one exp per sigmoid against SFU exp throughput).  K2 issues 1.25 MUFU ops per
     # sigmoid (ex2 + a reciprocal shared by four); K2f issues 0.26 (reciprocal shared by four + one ex2 per 100), so it
     # is bound by issue slots (4.5 per sigmoid), not by the SFU, and may exceed the one-exp-per-sigmoid line.
