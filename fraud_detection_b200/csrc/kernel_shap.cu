@@ -479,7 +479,7 @@ extern "C" int fdb_kshap_explain_dev(fdb_kshap_plan* p, void* stream, int64_t n_
     FDB_REQUIRE(n_rows >= 0, FDB_ERR_ARG, "n_rows is negative");
     FDB_REQUIRE(n_rows == 0 || (x && phi), FDB_ERR_ARG, "x / phi is NULL");
     FDB_REQUIRE(evaluator >= FDB_KSHAP_EVAL_AUTO && evaluator <= FDB_KSHAP_EVAL_FACTORED, FDB_ERR_ARG, "unknown evaluator %d", evaluator);
-    if (evaluator == FDB_KSHAP_EVAL_AUTO) evaluator = p->n_sets == 1 ? FDB_KSHAP_EVAL_FACTORED : FDB_KSHAP_EVAL_TC;
+    if (evaluator == FDB_KSHAP_EVAL_AUTO) evaluator = (p->n_sets == 1 && p->d_E != nullptr) ? FDB_KSHAP_EVAL_FACTORED : FDB_KSHAP_EVAL_TC;
     FDB_REQUIRE(evaluator != FDB_KSHAP_EVAL_FACTORED || p->n_sets == 1, FDB_ERR_ARG,
                 "the factored evaluator needs a plan with exactly one coalition set (this plan has %d)", p->n_sets);
     cudaStream_t st = (cudaStream_t)stream;

@@ -311,7 +311,7 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
 // coalition, stored as E = 2^(e_b - o_m) in the [tile][chunk][128][cbs] layout the evaluator streams.
 __global__ void __launch_bounds__(128) kshap_build_E(const uint32_t* __restrict__ bits, const double* __restrict__ Pd,
                                                      int n_bg, int n_chunks, float* __restrict__ E,
-                                                     float* __restrict__ eoff) {
+                                                     float* __restrict__ eoff, float* __restrict__ half_spread) {
     __shared__ double s_min[128], s_max[128];
     const int m = blockIdx.x, tid = threadIdx.x;
     const uint32_t b = bits[m];
@@ -338,7 +338,10 @@ __global__ void __launch_bounds__(128) kshap_build_E(const uint32_t* __restrict_
         __syncthreads();
     }
     const double centre = 0.5 * (s_min[0] + s_max[0]);
-    if (tid == 0) eoff[m] = (float)centre;
+    if (tid == 0) {
+        eoff[m] = (float)centre;
+        half_spread[m] = (float)(0.5 * (s_max[0] - s_min[0]));
+    }
     const int cbs_last = (fx_cbw(n_bg, n_chunks - 1) + 3) & ~3;
     const size_t tile_floats = (size_t)128 * (128 * (n_chunks - 1) + cbs_last);
     float* et = E + (size_t)(m >> 7) * tile_floats;
@@ -376,18 +379,36 @@ int fdb_kshap_build_factored(fdb_kshap_plan* pl, const double* bg_host) {
     if (e == cudaSuccess) e = cudaMalloc((void**)&pl->d_E, total * 4);
     if (e == cudaSuccess) e = cudaMemset(pl->d_E, 0, total * 4);
     if (e == cudaSuccess) e = cudaMalloc((void**)&pl->d_eoff, (size_t)pl->m_pad * 4);
+    float* d_spread = nullptr;
+    if (e == cudaSuccess) e = cudaMalloc((void**)&d_spread, (size_t)pl->m_pad * 4);
     if (e == cudaSuccess) {
-        kshap_build_E<<<pl->m_pad, 128>>>(pl->d_bits, dP, pl->n_bg, n_chunks, pl->d_E, pl->d_eoff);
+        kshap_build_E<<<pl->m_pad, 128>>>(pl->d_bits, dP, pl->n_bg, n_chunks, pl->d_E, pl->d_eoff, d_spread);
         e = cudaGetLastError();
     }
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    // The factorisation needs every coalition's background exponents within +-100 of their centre (fp32 range of
+    // E and u).  Backgrounds that spread the logit further (outliers of ~+-140 in logit) keep the general evaluator.
+    float worst = 0.f;
+    if (e == cudaSuccess) {
+        float* hs = new (std::nothrow) float[pl->m_pad];
+        if (hs && (e = cudaMemcpy(hs, d_spread, (size_t)pl->m_pad * 4, cudaMemcpyDeviceToHost)) == cudaSuccess)
+            for (int m = 0; m < pl->m_pad; ++m) worst = fmaxf(worst, hs[m]);
+        delete[] hs;
+    }
+    cudaFree(d_spread);
     cudaFree(dP);
     FDB_CUDA(e);
+    if (worst > 100.f) {
+        cudaFree(pl->d_E);
+        pl->d_E = nullptr;
+    }
     return FDB_OK;
 }
 
 int fdb_kshap_launch_eval_fx(fdb_kshap_plan* pl, cudaStream_t st, const float* x, int n_rows, float* ey) {
-    FDB_REQUIRE(pl->d_E != nullptr, FDB_ERR_STATE, "the factored evaluator needs a plan with exactly one coalition set");
+    FDB_REQUIRE(pl->d_E != nullptr, FDB_ERR_STATE,
+                "the factored evaluator is not available for this plan (needs one coalition set whose background logits "
+                "stay within +-100 log2 units per coalition)");
     FxParams p;
     p.x = x; p.zimg = pl->d_aimg; p.E = pl->d_E; p.eoff = pl->d_eoff; p.wq = pl->d_wq; p.ey = ey;
     p.xw = pl->d_xw; p.gpart = pl->d_gpart;

@@ -26,7 +26,8 @@
 namespace {
 
 constexpr int kMaxSizes = 16;
-constexpr int kHashSlots = 8192;             // >= 2 x the largest random block (nsamples <= 4096)
+// hash-set slots: >= 4 x the number of random primary draws (nsamples / 2), so probes stay short; the smaller
+// table (24 KB) doubles the resident warps per SM for the common nsamples <= 2048
 
 struct SamplerParams {
     uint32_t* bits;          // [S][m_pad]
@@ -43,6 +44,7 @@ struct SamplerParams {
     unsigned long long seed;
 };
 
+template <int kHashSlots, int kHashShift>
 __global__ void __launch_bounds__(32) kshap_sample_sets(const SamplerParams p) {
     __shared__ uint32_t h_key[kHashSlots];
     __shared__ uint16_t h_idx[kHashSlots];
@@ -81,7 +83,7 @@ __global__ void __launch_bounds__(32) kshap_sample_sets(const SamplerParams p) {
             int slot = -1;
             bool is_new = false;
             if (lane == 0) {
-                uint32_t h = (m * 2654435761u) >> 19;                               // 13-bit hash
+                uint32_t h = (m * 2654435761u) >> kHashShift;
                 while (true) {
                     const uint32_t k = h_key[h];
                     if (k == 0u) { h_key[h] = m; h_idx[h] = (uint16_t)count; slot = count; is_new = true; break; }
@@ -222,7 +224,8 @@ int fdb_kshap_sample_on_device(fdb_kshap_plan* pl, int nsamples, unsigned long l
     if (e == cudaSuccess) {
         sp.fixed_bits = d_fb;
         sp.fixed_kw = d_fw;
-        kshap_sample_sets<<<pl->n_sets, 32>>>(sp);
+        if (nsamples <= 2048) kshap_sample_sets<4096, 20><<<pl->n_sets, 32>>>(sp);
+        else kshap_sample_sets<8192, 19><<<pl->n_sets, 32>>>(sp);
         e = cudaGetLastError();
     }
     if (e == cudaSuccess) e = cudaDeviceSynchronize();

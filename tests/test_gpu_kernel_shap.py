@@ -324,3 +324,40 @@ def test_explainer_with_device_sampler_is_statistically_the_same(params):
     np.testing.assert_allclose(shared.sum(1) + expl.expected_value, f(X), atol=1e-5)
     with pytest.raises(ValueError, match="64 <= nsamples <= 4096"):
         expl.shap_values(X, nsamples=100000, sampler="device")
+
+
+def test_bf16_three_term_operands(params, monkeypatch):
+    """Operand values >= 2^14 switch the MMA operands from 2 x f16 to 3 x bf16 terms; force that branch."""
+    monkeypatch.setenv("FDB_KSHAP_FMT", "1")
+    bg, X, f = _setup(params, 100, 10, seed=30)
+    Z, kw, _ = ks.sample_coalitions(30, 512, np.random.RandomState(30))
+    phi_ref, ey_ref, fnull = _oracle_rows(f, X, bg, [(Z, kw)])
+    plan = _plan(params, bg, [(Z, kw)])
+    assert plan.info()["fmt"] == 1 and plan.info()["nsplit"] == 3
+    for ev in (TC, FX):
+        phi, ey, _ = _run(plan, X, ev)
+        np.testing.assert_allclose(ey, ey_ref, rtol=0, atol=2e-6)
+        _check_phi(phi, phi_ref, f, X, fnull)
+    plan.close()
+
+
+def test_large_magnitude_rows_select_bf16_and_stay_finite(params):
+    """A background with huge feature values (|w x| >= 2^14) must not overflow the half-precision operands."""
+    from fraud_detection_b200 import KernelShapPlan, sampler
+    bg = scoring.transform(params, synth.rows(16, seed=43))
+    bg[:, 28] *= 4000.0                                   # w_28 = 2.23 -> |w x| well above 16384
+    bits, kw = sampler.sample_coalitions(30, 256, np.random.RandomState(1))
+    plan = KernelShapPlan(params.coef, params.intercept, bg, bits, kw)
+    assert plan.info()["fmt"] == 1
+    X = scoring.transform(params, synth.rows(8, seed=31))
+    f = lambda A: scoring.predict_proba(params, A)[:, 1]  # noqa: E731
+    Zm = sampler.bits_to_masks(bits)
+    phi_ref, ey_ref, fnull = _oracle_rows(f, X, bg, [(Zm, kw)])
+    for ev in (TC, -1):          # AUTO falls back to the general evaluator: the exponent spread is too wide to factor
+        phi, ey, _ = _run(plan, X, ev)
+        assert np.all(np.isfinite(phi)) and np.all(np.isfinite(ey))
+        np.testing.assert_allclose(ey, ey_ref, rtol=0, atol=5e-6)
+        np.testing.assert_allclose(phi.sum(1) + fnull, f(X), atol=1e-5)
+    with pytest.raises(Exception, match="factored evaluator is not available"):
+        _run(plan, X, FX)
+    plan.close()
