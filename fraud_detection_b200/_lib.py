@@ -54,6 +54,7 @@ _SIGS = {
     "fdb_kshap_plan_create": (_i, [_vp, _dp, C.c_double, _i, _vp, _i, _i, _vp, _vp, _i, C.POINTER(_vp)]),
     "fdb_kshap_plan_create_sampled": (_i, [_vp, _dp, C.c_double, _i, _vp, _i, _i, C.c_uint64, _i, C.POINTER(_vp)]),
     "fdb_kshap_plan_get_masks": (_i, [_vp, _i, _vp, _vp]),
+    "fdb_kshap_plan_resample": (_i, [_vp, C.c_uint64]),
     "fdb_kshap_plan_destroy": (_i, [_vp]),
     "fdb_kshap_expected_value": (C.c_double, [_vp]),
     "fdb_kshap_plan_info": (_i, [_vp, C.POINTER(C.c_int)]),

@@ -284,6 +284,40 @@ void fdb_kshap_split(double v, int fmt, int n, uint16_t* out) {
     }
 }
 
+// Everything derived from the coalition sets (d_bits / d_kw): operand tile images, per-set (X'WX)^-1 and, for a
+// single set, the factored evaluator's operands.  Run at plan creation and again after a resample.
+static int refresh_set_products(fdb_kshap_plan* p) {
+    const size_t SM = (size_t)p->n_sets * p->m_pad;
+    const uint16_t one = p->fmt == 0 ? 0x3C00 : 0x3F80;
+    kshap_expand_masks<<<(unsigned)((SM + 255) / 256), 256>>>(p->d_bits, p->d_aimg, (int64_t)SM, one);
+    FDB_CUDA(cudaGetLastError());
+    kshap_wls_prepare<<<p->n_sets, 32>>>(p->d_bits, p->d_kw, p->m_pad, p->d_ainv, p->d_c2, p->d_status);
+    FDB_CUDA(cudaGetLastError());
+    FDB_CUDA(cudaDeviceSynchronize());
+    std::vector<int> st(p->n_sets);
+    FDB_CUDA(cudaMemcpy(st.data(), p->d_status, (size_t)p->n_sets * 4, cudaMemcpyDeviceToHost));
+    for (int s = 0; s < p->n_sets; ++s)
+        FDB_REQUIRE(st[s] == 0, FDB_ERR_ARG, "mask set %d gives a singular weighted least-squares system (X'WX); "
+                    "use more samples or fewer features", s);
+    if (p->n_sets == 1) {
+        if (!p->d_xw) FDB_CUDA(cudaMalloc((void**)&p->d_xw, (size_t)p->m_pad * 32 * 4));
+        if (!p->d_gpart) FDB_CUDA(cudaMalloc((void**)&p->d_gpart, (size_t)p->batch_rows * (p->m_pad / 32) * 32 * 4));
+        kshap_build_xw<<<(p->m_pad * 32 + 255) / 256, 256>>>(p->d_bits, p->d_kw, p->m_pad, p->d_xw);
+        FDB_CUDA(cudaGetLastError());
+        cudaFree(p->d_E); cudaFree(p->d_eoff);
+        p->d_E = nullptr; p->d_eoff = nullptr;
+        int rc = fdb_kshap_build_factored(p, p->bg_host.data());
+        if (rc != FDB_OK) return rc;
+    }
+    if (p->d_gz) {
+        cudaFree(p->d_gz); cudaFree(p->d_bv); cudaFree(p->d_s0);
+        p->d_gz = nullptr; p->d_bv = nullptr; p->d_s0 = nullptr;
+        int rc = fdb_kshap_prepare_lars(p);
+        if (rc != FDB_OK) return rc;
+    }
+    return FDB_OK;
+}
+
 // bits == nullptr: draw the coalition sets on the device (n_masks = resolved nsamples, seed)
 static int plan_create_impl(fdb_ctx* ctx, const double* coef, double intercept, int n_bg, const double* bg,
                             int n_sets, int n_masks, const uint32_t* bits, const double* kw, int link,
@@ -377,40 +411,16 @@ static int plan_create_impl(fdb_ctx* ctx, const double* coef, double intercept, 
         TRY(cudaMemcpy(p->d_P, P.data(), P.size() * 4, cudaMemcpyHostToDevice));
         TRY(cudaMemcpy(p->d_wq, wq, 32 * 4, cudaMemcpyHostToDevice));
         TRY(cudaMemcpy(p->d_bimg, bimg.data(), bimg.size() * 2, cudaMemcpyHostToDevice));
-        const uint16_t one = p->fmt == 0 ? 0x3C00 : 0x3F80;
-        kshap_expand_masks<<<(unsigned)((SM + 255) / 256), 256>>>(p->d_bits, p->d_aimg, (int64_t)SM, one);
-        TRY(cudaGetLastError());
-        kshap_wls_prepare<<<n_sets, 32>>>(p->d_bits, p->d_kw, p->m_pad, p->d_ainv, p->d_c2, p->d_status);
-        TRY(cudaGetLastError());
-        TRY(cudaDeviceSynchronize());
-        std::vector<int> st(n_sets);
-        TRY(cudaMemcpy(st.data(), p->d_status, (size_t)n_sets * 4, cudaMemcpyDeviceToHost));
-        for (int s = 0; s < n_sets; ++s)
-            if (st[s]) {
-                fdb_set_error("mask set %d gives a singular weighted least-squares system (X'WX); "
-                              "use more samples or fewer features", s);
-                rc = FDB_ERR_ARG;
-                break;
-            }
 #undef TRY
     } while (0);
     if (e != cudaSuccess) {
         fdb_set_error("kernel-SHAP plan creation failed: %s", cudaGetErrorString(e));
         rc = e == cudaErrorMemoryAllocation ? FDB_ERR_NOMEM : FDB_ERR_CUDA;
     }
-    if (rc == FDB_OK && n_sets == 1) {
-        cudaError_t e2 = cudaMalloc((void**)&p->d_xw, (size_t)p->m_pad * 32 * 4);
-        if (e2 == cudaSuccess) e2 = cudaMalloc((void**)&p->d_gpart, (size_t)p->batch_rows * (p->m_pad / 32) * 32 * 4);
-        if (e2 == cudaSuccess) {
-            kshap_build_xw<<<(p->m_pad * 32 + 255) / 256, 256>>>(p->d_bits, p->d_kw, p->m_pad, p->d_xw);
-            e2 = cudaGetLastError();
-        }
-        if (e2 != cudaSuccess) {
-            fdb_set_error("kernel-SHAP plan creation failed: %s", cudaGetErrorString(e2));
-            rc = e2 == cudaErrorMemoryAllocation ? FDB_ERR_NOMEM : FDB_ERR_CUDA;
-        } else {
-            rc = fdb_kshap_build_factored(p, bg);
-        }
+    if (rc == FDB_OK) {
+        p->bg_host.assign(bg, bg + (size_t)n_bg * FDB_F);
+        p->sampled = bits == nullptr;
+        rc = refresh_set_products(p);
     }
     if (rc != FDB_OK) { free_plan(p); return rc; }
     *out = p;
@@ -429,6 +439,17 @@ extern "C" int fdb_kshap_plan_create_sampled(fdb_ctx* ctx, const double* coef, d
                                              fdb_kshap_plan** out) {
     return plan_create_impl(ctx, coef, intercept, n_bg, bg, n_sets, fdb_kshap_resolve_nsamples(nsamples), nullptr, nullptr,
                             link, (unsigned long long)seed, out);
+}
+
+extern "C" int fdb_kshap_plan_resample(fdb_kshap_plan* p, uint64_t seed) {
+    FDB_REQUIRE(p != nullptr, FDB_ERR_ARG, "plan is NULL");
+    FDB_REQUIRE(p->sampled, FDB_ERR_STATE, "only plans made by fdb_kshap_plan_create_sampled can be resampled");
+    std::lock_guard<std::mutex> lock(p->ctx->host_mu);
+    FDB_CUDA(cudaSetDevice(p->ctx->device));
+    FDB_CUDA(cudaDeviceSynchronize());
+    int rc = fdb_kshap_sample_on_device(p, p->n_masks, (unsigned long long)seed);
+    if (rc != FDB_OK) return rc;
+    return refresh_set_products(p);
 }
 
 extern "C" int fdb_kshap_plan_get_masks(const fdb_kshap_plan* p, int set, uint32_t* bits, float* kw) {

@@ -1,6 +1,8 @@
 // Internal declarations of the Kernel SHAP part of libfdb200.so.
 #pragma once
 
+#include <vector>
+
 #include "fdb_internal.cuh"
 
 #define FDB_KSHAP_MAX_BG 1024          // background rows the tensor-core evaluator keeps resident in smem
@@ -38,6 +40,8 @@ struct fdb_kshap_plan {
     double* d_gz = nullptr;            // [S][30][32] Z'WZ, built on demand for l1_reg = num_features(k)
     double* d_bv = nullptr;            // [S][32]
     double* d_s0 = nullptr;            // [S]
+    std::vector<double> bg_host;       // background rows (host copy, for rebuilding set-dependent operands)
+    bool sampled = false;              // sets were drawn on the device and may be redrawn (fdb_kshap_plan_resample)
     int num_features = 0;              // 0 = plain WLS over all features; k = LARS selection of k features first
     float* d_gpart = nullptr;          // [batch_rows][m_pad/32][32] partial X'W y written by K2f, folded by K3
 };

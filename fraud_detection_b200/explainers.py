@@ -170,6 +170,10 @@ class KernelShapPlan:
         self.n_sets, self.n_masks = info["n_sets"], info["n_masks"]
         return self
 
+    def resample(self, seed: int) -> None:
+        """Redraw all coalition sets of a device-sampled plan in place (fresh coalitions for the next rows)."""
+        _lib.check(_lib.lib.fdb_kshap_plan_resample(self._h, int(seed) & 0xFFFFFFFFFFFFFFFF))
+
     def masks(self, set_index: int = 0):
         """(bits uint32 (n_masks,), kernel weights float32 (n_masks,)) of one coalition set, copied from the device."""
         bits = np.empty(self.n_masks, dtype=np.uint32)
@@ -257,6 +261,8 @@ class B200KernelExplainer:
         self.fnull = float(np.mean(1.0 / (1.0 + np.exp(-z))))
         self.expected_value = float(np.log(self.fnull / (1 - self.fnull))) if link == "logit" else self.fnull
         self._shared_cache: dict = {}
+        self._device_plans: dict = {}
+        self._device_calls = 0
 
     # ------------------------------------------------------------------ helpers
     def _varying(self, X: np.ndarray) -> np.ndarray:
@@ -310,14 +316,22 @@ class B200KernelExplainer:
         Xr = np.ascontiguousarray(A[rows], dtype=np.float32)
         if masks is None and sampler == "device":
             # coalition sets drawn on the GPU: one per row (the reference's behaviour) or one shared set
+            # the plan is kept and its sets are redrawn in place on later calls (no re-allocation)
             n_sets = len(rows) if mask_mode == "per_row" else 1
-            plan = KernelShapPlan.sampled(self.coef, self.intercept, self.data, n_sets, nsamples, seed, self.link, self.device)
-            try:
-                if num_features:
-                    plan.set_num_features(num_features)
-                out[rows] = plan.explain_host(Xr, None, evaluator)
-            finally:
-                plan.close()
+            key = (n_sets, nsamples)
+            plan = self._device_plans.get(key)
+            call_seed = int(seed) + self._device_calls
+            self._device_calls += 1
+            if plan is None:
+                for old in self._device_plans.values():
+                    old.close()
+                self._device_plans.clear()
+                plan = KernelShapPlan.sampled(self.coef, self.intercept, self.data, n_sets, nsamples, call_seed, self.link, self.device)
+                self._device_plans[key] = plan
+            else:
+                plan.resample(call_seed)
+            plan.set_num_features(num_features)
+            out[rows] = plan.explain_host(Xr, None, evaluator)
             return out[0] if single else out
         if sampler not in ("host", "device"):
             raise ValueError("sampler must be 'host' or 'device'")

@@ -135,6 +135,9 @@ int fdb_kshap_plan_create(fdb_ctx* ctx, const double* coef, double intercept, in
 int fdb_kshap_plan_create_sampled(fdb_ctx* ctx, const double* coef, double intercept, int n_bg, const double* bg,
                                   int n_sets, int nsamples, uint64_t seed, int link, fdb_kshap_plan** out);
 int fdb_kshap_plan_get_masks(const fdb_kshap_plan* plan, int set, uint32_t* bits, float* kw);
+/* Redraw every coalition set of a sampled plan in place (no allocation of the large buffers): fresh coalitions for
+ * the next batch of rows, as the reference draws them per explain() call. */
+int fdb_kshap_plan_resample(fdb_kshap_plan* plan, uint64_t seed);
 int fdb_kshap_plan_destroy(fdb_kshap_plan* plan);
 double fdb_kshap_expected_value(const fdb_kshap_plan* plan);
 int fdb_kshap_plan_info(const fdb_kshap_plan* plan, int* info8);

@@ -361,3 +361,35 @@ def test_large_magnitude_rows_select_bf16_and_stay_finite(params):
     with pytest.raises(Exception, match="factored evaluator is not available"):
         _run(plan, X, FX)
     plan.close()
+
+
+def test_resample_in_place(params):
+    """A sampled plan redraws its sets without re-allocation; explanations stay exact for the new sets."""
+    import time
+    from fraud_detection_b200 import B200KernelExplainer, KernelShapPlan, sampler
+    bg, X, f = _setup(params, 100, 4, seed=40)
+    plan = KernelShapPlan.sampled(params.coef, params.intercept, bg, len(X), 2048, seed=1)
+    before = plan.masks(2)[0].copy()
+    t0 = time.perf_counter()
+    plan.resample(2)
+    dt = time.perf_counter() - t0
+    after, kw_after = plan.masks(2)
+    assert not np.array_equal(before, after) and dt < 0.5
+    phi, ey, _ = _run(plan, X, TC)
+    fnull = float(f(bg).mean())
+    Z = sampler.bits_to_masks(after)
+    ref = ks.solve(Z, kw_after.astype(np.float64), ks.evaluate(f, X[2], bg, Z), float(f(X[2][None])[0]), fnull)
+    assert np.all(np.abs(phi[2] - ref) <= 1e-4 * np.abs(ref).max() + 1e-9)
+    plan.close()
+    host_plan = _plan(params, bg, [ks.sample_coalitions(30, 256, np.random.RandomState(0))[:2]])
+    with pytest.raises(Exception, match="create_sampled"):
+        host_plan.resample(1)
+    host_plan.close()
+    # the explainer keeps its device plan across calls and draws new coalitions each time (like shap does per call)
+    expl = B200KernelExplainer((params.coef, params.intercept), bg)
+    a = expl.shap_values(X[0], nsamples=2048, sampler="device", seed=5)
+    b = expl.shap_values(X[0], nsamples=2048, sampler="device", seed=5)
+    assert len(expl._device_plans) == 1 and not np.array_equal(a, b)
+    np.testing.assert_allclose(a.sum() + expl.expected_value, f(X[:1])[0], atol=1e-5)
+    np.testing.assert_allclose(b.sum() + expl.expected_value, f(X[:1])[0], atol=1e-5)
+    assert np.abs(a - b).max() < 0.05
