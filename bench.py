@@ -53,6 +53,7 @@ def parse_args():
     ap.add_argument("--e2e-rows", type=int, default=int(os.environ.get("FDB_BENCH_E2E_ROWS", 8_000_000)))
     ap.add_argument("--kshap-rows", type=int, default=int(os.environ.get("FDB_BENCH_KSHAP_ROWS", 100_000)))
     ap.add_argument("--kshap-per-row", type=int, default=32768)
+    ap.add_argument("--kshap4-rows", type=int, default=125_000)
     ap.add_argument("--kshap-cpu-rows", type=int, default=256)
     ap.add_argument("--no-kshap", action="store_true")
     ap.add_argument("--cpu-rows", type=int, default=int(os.environ.get("FDB_BENCH_CPU_ROWS", 4_000_000)))
@@ -303,6 +304,33 @@ def bench_kernel_shap(args, torch, dist, device, rank, world, prm, sm_max_mhz):
     out["e2e"] = {"value": rows * world / float(t.item()), "unit": "explained rows/s", "h2d_bytes_per_step": rows * 120,
                   "d2h_bytes_per_step": rows * 120 + 256, "api": "fdb_kshap_explain_host (pinned host rows in, phi out)"}
     plan.close()
+
+    # config 4: nsamples=4096, 1000-row background, 125,000 explained rows per GPU (1M rows over 8 GPUs), one all-reduce
+    rows4, ns4, nb4 = args.kshap4_rows, 4096, 1000
+    if rows4 > 0:
+        bg4 = scoring.transform(prm, synth.rows(nb4, seed=44))
+        b4, w4 = sampler.sample_coalitions(30, ns4, np.random.RandomState(4))
+        import warnings
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            plan4 = KernelShapPlan(prm.coef, prm.intercept, bg4, b4, w4, device=device.index)
+        x4 = torch.from_numpy(scoring.transform(prm, synth.rows(rows4, seed=2000 + rank)).astype(np.float32)).to(device)
+        phi4 = torch.empty_like(x4)
+
+        def step4():
+            plan4.explain_dev(x4, phi=phi4, abs_sum=abs_sum)
+            allreduce_abs_sum(abs_sum)
+
+        ms4 = timed(step4, 3)
+        ms4_tc = timed(lambda: plan4.explain_dev(x4, evaluator=0, phi=phi4), 2)
+        sig4 = rows4 * len(b4) * nb4
+        out["config4"] = {"workload": f"config4: Kernel SHAP nsamples={ns4}, {nb4}-row background, {rows4} explained rows per GPU, "
+                                      "shared coalition set, all-reduce of the |SHAP| summary",
+                          "value": rows4 * world / (ms4 * 1e-3), "unit": "explained rows/s", "ms_per_step": ms4,
+                          "sigmoids_per_s": sig4 * world / (ms4 * 1e-3),
+                          "general_evaluator_value": rows4 * world / (ms4_tc * 1e-3)}
+        plan4.close()
+        del x4, phi4
 
     # the reference's behaviour: a different coalition set for every explained row, drawn on the device
     pr = args.kshap_per_row
