@@ -33,6 +33,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+_OUT = sys.stdout
 METRIC = "scored_rows_per_sec"
 UNIT = "rows/s"
 BYTES_PER_ROW = 244           # 120 B x in + 4 B proba + 120 B phi
@@ -142,7 +143,7 @@ def run_reference(args):
     value = rows * args.steps / dt
     sample = (f"{rows} float64 rows per step from the same generator; sklearn {origin} estimators "
               f"(transform+predict_proba+predict) + numpy linear SHAP; row-chunked over {threads} threads")
-    print(json.dumps({
+    _OUT.write(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -150,7 +151,8 @@ def run_reference(args):
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads,
                          "kind": "reference" if origin == "joblib" else "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    }) + "\n")
+    _OUT.flush()
 
 
 # ------------------------------------------------------------------------------- clocks
@@ -498,14 +500,26 @@ def run_b200(args):
                           f"transform+predict_proba+predict + numpy linear SHAP, row-chunked over {cpu_threads} threads",
                 "single_thread_value": v1,
             }
-        print(json.dumps(line))
+        _OUT.write(json.dumps(line) + "\n")
+        _OUT.flush()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+def _claim_stdout():
+    """Keep stdout for the ONE JSON line: everything else a library prints there (NCCL's version banner, warnings)
+    is sent to stderr at the file-descriptor level; returns a writer for the real stdout."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    return os.fdopen(real, "w")
+
+
 def main():
     args = parse_args()
+    global _OUT
+    _OUT = _claim_stdout()
     if args.impl == "reference":
         run_reference(args)
     else:
