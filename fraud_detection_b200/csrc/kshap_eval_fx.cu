@@ -99,9 +99,12 @@ __device__ __forceinline__ void chunk_sum4(const float* __restrict__ e0, int cbs
             acc[mm] += ptx::rcp_approx(fminf(fmaf(e0[mm * cbs + 4 * nquads + i], u[mm], 1.0f), kClamp));
 }
 
+#ifndef FDB_FX_SERVICE_SLEEP_NS
+#define FDB_FX_SERVICE_SLEEP_NS 800     // a unit lasts ~35 us and every hand-off is double-buffered
+#endif
 // waits of the single-lane service warps back off so their polling does not take issue slots from the compute warps
 __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
-    while (!ptx::mbar_try_wait(bar, parity)) __nanosleep(64);
+    while (!ptx::mbar_try_wait(bar, parity)) __nanosleep(FDB_FX_SERVICE_SLEEP_NS);
 }
 
 __device__ __forceinline__ int fx_cbw(int n_bg, int c) { const int r = n_bg - 128 * c; return r < 128 ? r : 128; }

@@ -107,6 +107,14 @@ __device__ __forceinline__ void release_tmem(uint64_t* bar, int lane) {
 #endif
 constexpr uint32_t kPolyMask8 = FDB_K2_POLY_MASK;
 
+#ifndef FDB_K2_SERVICE_SLEEP_NS
+#define FDB_K2_SERVICE_SLEEP_NS 48
+#endif
+// producer / MMA lanes poll with a short back-off so they do not take issue slots from the epilogue warps
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
+    while (!ptx::mbar_try_wait(bar, parity)) __nanosleep(FDB_K2_SERVICE_SLEEP_NS);
+}
+
 // sum_i sigmoid over 16 accumulator columns, t_i = D[m][b_i] = -log2e * logit.
 // Four sigmoids share ONE reciprocal: s0+s1+s2+s3 = (n01 p23 + n23 p01) / (p01 p23) with d_i = 1 + 2^t_i,
 // n_ab = d_a + d_b, p_ab = d_a d_b.  t is clamped to 30 so the product of four d stays below 2^121;
@@ -215,7 +223,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcPa
                 h[j] = to_h16(rem, p.fmt);
                 rem -= from_h16(h[j], p.fmt);
             }
-            ptx::mbar_wait(&pb.a_empty[s], ph ^ 1);
+            mbar_wait_relaxed(&pb.a_empty[s], ph ^ 1);
             unsigned char* bq = sBq + (size_t)(g * kAStages + s) * kBqBytes + (lane >> 3) * 128 + (lane & 7) * 2;
 #pragma unroll
             for (int j = 0; j < 3; ++j)
@@ -245,12 +253,12 @@ __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcPa
             for (int64_t it = (int64_t)blockIdx.x * kPipes + g; it < n_items; it += stride, ++k) {
                 const int s = k % kAStages;
                 const uint32_t ph = (k / kAStages) & 1;
-                ptx::mbar_wait(&pb.a_full[s], ph);
+                mbar_wait_relaxed(&pb.a_full[s], ph);
                 ptx::tc_fence_after();
                 const uint32_t a_addr = a0 + s * kATileBytes;
                 const uint32_t q_addr = q0 + s * kBqBytes;
                 for (int c = 0; c < p.n_chunks; ++c, ++job) {
-                    ptx::mbar_wait(&pb.t_empty, (job & 1) ^ 1);
+                    mbar_wait_relaxed(&pb.t_empty, (job & 1) ^ 1);
                     ptx::tc_fence_after();
                     const int col0 = c * p.chunk_cols;
                     const int nc = (p.nb_pad - col0) < p.chunk_cols ? (p.nb_pad - col0) : p.chunk_cols;
