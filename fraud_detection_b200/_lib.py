@@ -52,6 +52,7 @@ _SIGS = {
     "fdb_linear_pass_host": (_i, [_vp, _i, _i64, _vp, _dp, _dp, C.c_double, _vp, _i, _vp, _vp, _vp, _vp]),
     "fdb_linear_pass_noalloc": (_i, [_vp, _i, _i64, _vp, _dp, _dp, C.c_double, _vp, _i, _vp, _vp, _vp, _vp]),
     "fdb_kshap_plan_create": (_i, [_vp, _dp, C.c_double, _i, _vp, _i, _i, _vp, _vp, _i, C.POINTER(_vp)]),
+    "fdb_kshap_plan_create_varying": (_i, [_vp, _dp, C.c_double, _i, _vp, _i, _i, _vp, _vp, _i, C.c_uint32, C.POINTER(_vp)]),
     "fdb_kshap_plan_create_sampled": (_i, [_vp, _dp, C.c_double, _i, _vp, _i, _i, C.c_uint64, _i, C.POINTER(_vp)]),
     "fdb_kshap_plan_get_masks": (_i, [_vp, _i, _vp, _vp]),
     "fdb_kshap_plan_resample": (_i, [_vp, C.c_uint64]),

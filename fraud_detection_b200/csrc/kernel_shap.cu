@@ -26,7 +26,11 @@ namespace {
 
 constexpr int kNV = FDB_F - 1;   // 29 unknowns after eliminating the last feature
 
-__device__ __forceinline__ float link_apply(float v, int link) { return link == 1 ? logf(v / (1.0f - v)) : v; }
+__device__ __forceinline__ float link_apply(float v, int link) {
+    if (link != 1) return v;
+    v = fminf(fmaxf(v, 1e-30f), 0.99999994f);       // see fdb_kshap_link: saturate instead of inf / NaN
+    return logf(v / (1.0f - v));
+}
 
 // ---------------------------------------------------------------------------------------
 // bits -> A operand image (tcgen05 canonical K-major no-swizzle layout, 128 masks x 32 k per tile)
@@ -57,7 +61,7 @@ __global__ void kshap_expand_masks(const uint32_t* __restrict__ bits, uint16_t* 
 // One warp per set; lane i owns row i of A while accumulating.
 __global__ void __launch_bounds__(32) kshap_wls_prepare(const uint32_t* __restrict__ bits, const float* __restrict__ kw,
                                                         int m_pad, float* __restrict__ ainv, float* __restrict__ c2out,
-                                                        int* __restrict__ status) {
+                                                        int* __restrict__ status, uint32_t varying) {
     __shared__ double A[kNV][kNV + 1];
     __shared__ double I[kNV][kNV + 1];
     const int s = blockIdx.x;
@@ -87,6 +91,8 @@ __global__ void __launch_bounds__(32) kshap_wls_prepare(const uint32_t* __restri
             A[lane][j] = a[j];
             I[lane][j] = (j == lane) ? 1.0 : 0.0;
         }
+        // a feature outside `varying` has an all-zero column (its bits follow bit 29): pin its unknown at 0
+        if (!((varying >> lane) & 1u)) A[lane][lane] = 1.0;
         c2out[(size_t)s * 32 + lane] = (float)c2;
     } else {
         c2out[(size_t)s * 32 + lane] = 0.f;
@@ -291,7 +297,7 @@ static int refresh_set_products(fdb_kshap_plan* p) {
     const uint16_t one = p->fmt == 0 ? 0x3C00 : 0x3F80;
     kshap_expand_masks<<<(unsigned)((SM + 255) / 256), 256>>>(p->d_bits, p->d_aimg, (int64_t)SM, one);
     FDB_CUDA(cudaGetLastError());
-    kshap_wls_prepare<<<p->n_sets, 32>>>(p->d_bits, p->d_kw, p->m_pad, p->d_ainv, p->d_c2, p->d_status);
+    kshap_wls_prepare<<<p->n_sets, 32>>>(p->d_bits, p->d_kw, p->m_pad, p->d_ainv, p->d_c2, p->d_status, p->varying);
     FDB_CUDA(cudaGetLastError());
     FDB_CUDA(cudaDeviceSynchronize());
     std::vector<int> st(p->n_sets);
@@ -321,9 +327,11 @@ static int refresh_set_products(fdb_kshap_plan* p) {
 // bits == nullptr: draw the coalition sets on the device (n_masks = resolved nsamples, seed)
 static int plan_create_impl(fdb_ctx* ctx, const double* coef, double intercept, int n_bg, const double* bg,
                             int n_sets, int n_masks, const uint32_t* bits, const double* kw, int link,
-                            unsigned long long seed, fdb_kshap_plan** out) {
+                            unsigned long long seed, uint32_t varying, fdb_kshap_plan** out) {
     FDB_REQUIRE(ctx && coef && bg && out, FDB_ERR_ARG, "NULL argument");
     *out = nullptr;
+    FDB_REQUIRE((varying & ~0x3FFFFFFFu) == 0 && ((varying >> 29) & 1u) && __builtin_popcount(varying) >= 2, FDB_ERR_ARG,
+                "varying_mask 0x%x must name at least 2 of the 30 features and include feature 29", varying);
     FDB_REQUIRE(n_bg >= 1 && n_bg <= FDB_KSHAP_MAX_BG, FDB_ERR_ARG, "background rows must be in [1, %d], got %d", FDB_KSHAP_MAX_BG, n_bg);
     FDB_REQUIRE(n_sets >= 1 && n_masks >= 1, FDB_ERR_ARG, "need at least one mask set and one mask");
     FDB_REQUIRE(link == 0 || link == 1, FDB_ERR_ARG, "link must be 0 (identity) or 1 (logit)");
@@ -337,6 +345,7 @@ static int plan_create_impl(fdb_ctx* ctx, const double* coef, double intercept, 
     p->m_pad = (n_masks + 127) & ~127;
     p->n_sets = n_sets;
     p->link = link;
+    p->varying = varying;
     p->intercept = intercept;
     memcpy(p->coef, coef, sizeof(double) * FDB_F);
     const size_t SM = (size_t)n_sets * p->m_pad;
@@ -376,7 +385,9 @@ static int plan_create_impl(fdb_ctx* ctx, const double* coef, double intercept, 
     std::vector<float> hkw(bits ? SM : 0, 0.f);
     for (int s = 0; bits && s < n_sets; ++s)
         for (int m = 0; m < n_masks; ++m) {
-            hbits[(size_t)s * p->m_pad + m] = bits[(size_t)s * n_masks + m] & 0x3FFFFFFFu;
+            // features outside `varying` follow bit 29, so that their column z_k - z_29 of the WLS is identically 0
+            const uint32_t b = bits[(size_t)s * n_masks + m] & varying;
+            hbits[(size_t)s * p->m_pad + m] = ((b >> 29) & 1u) ? (b | (~varying & 0x3FFFFFFFu)) : b;
             hkw[(size_t)s * p->m_pad + m] = (float)kw[(size_t)s * n_masks + m];
         }
     float wq[32] = {0};
@@ -431,14 +442,21 @@ extern "C" int fdb_kshap_plan_create(fdb_ctx* ctx, const double* coef, double in
                                      int n_sets, int n_masks, const uint32_t* bits, const double* kw, int link,
                                      fdb_kshap_plan** out) {
     FDB_REQUIRE(bits && kw, FDB_ERR_ARG, "bits / kw is NULL");
-    return plan_create_impl(ctx, coef, intercept, n_bg, bg, n_sets, n_masks, bits, kw, link, 0ULL, out);
+    return plan_create_impl(ctx, coef, intercept, n_bg, bg, n_sets, n_masks, bits, kw, link, 0ULL, 0x3FFFFFFFu, out);
+}
+
+extern "C" int fdb_kshap_plan_create_varying(fdb_ctx* ctx, const double* coef, double intercept, int n_bg, const double* bg,
+                                             int n_sets, int n_masks, const uint32_t* bits, const double* kw, int link,
+                                             uint32_t varying_mask, fdb_kshap_plan** out) {
+    FDB_REQUIRE(bits && kw, FDB_ERR_ARG, "bits / kw is NULL");
+    return plan_create_impl(ctx, coef, intercept, n_bg, bg, n_sets, n_masks, bits, kw, link, 0ULL, varying_mask, out);
 }
 
 extern "C" int fdb_kshap_plan_create_sampled(fdb_ctx* ctx, const double* coef, double intercept, int n_bg,
                                              const double* bg, int n_sets, int nsamples, uint64_t seed, int link,
                                              fdb_kshap_plan** out) {
     return plan_create_impl(ctx, coef, intercept, n_bg, bg, n_sets, fdb_kshap_resolve_nsamples(nsamples), nullptr, nullptr,
-                            link, (unsigned long long)seed, out);
+                            link, (unsigned long long)seed, 0x3FFFFFFFu, out);
 }
 
 extern "C" int fdb_kshap_plan_resample(fdb_kshap_plan* p, uint64_t seed) {

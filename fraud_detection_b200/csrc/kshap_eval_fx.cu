@@ -280,7 +280,7 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
 #pragma unroll
                 for (int mi = 0; mi < 32; ++mi) {
                     part[mi] *= p.inv_bg;
-                    const float yv = (p.link == 1 ? __logf(part[mi] / (1.0f - part[mi])) : part[mi]) - p.lnull;
+                    const float yv = fdb_kshap_link(part[mi], p.link) - p.lnull;
 #pragma unroll
                     for (int v4 = 0; v4 < 8; ++v4) {
                         const float4 xv = __ldg(xwp + mi * 8 + v4);          // same address in every lane

@@ -43,6 +43,7 @@ struct fdb_kshap_plan {
     std::vector<double> bg_host;       // background rows (host copy, for rebuilding set-dependent operands)
     bool sampled = false;              // sets were drawn on the device and may be redrawn (fdb_kshap_plan_resample)
     int num_features = 0;              // 0 = plain WLS over all features; k = LARS selection of k features first
+    uint32_t varying = 0x3FFFFFFFu;    // features that differ from the background for the rows of this plan (bit 29 always set)
     float* d_gpart = nullptr;          // [batch_rows][m_pad/32][32] partial X'W y written by K2f, folded by K3
 };
 
@@ -55,6 +56,16 @@ int fdb_kshap_launch_eval_tc(fdb_kshap_plan* p, cudaStream_t st, const float* x,
 // K2f: factored evaluator for single-set plans (kshap_eval_fx.cu).
 int fdb_kshap_build_factored(fdb_kshap_plan* pl, const double* bg_host);
 int fdb_kshap_launch_eval_fx(fdb_kshap_plan* pl, cudaStream_t st, const float* x, int n_rows, float* ey);
+
+// Link applied to a float32 coalition expectation.  The logit keeps its argument inside [1e-30, 1 - 2^-24]: an
+// expectation that rounds to 1 in float32 (|logit| beyond ~16.6) saturates there instead of giving inf / NaN.
+#ifdef __CUDACC__
+__device__ __forceinline__ float fdb_kshap_link(float v, int link) {
+    if (link != 1) return v;
+    v = fminf(fmaxf(v, 1e-30f), 0.99999994f);
+    return __logf(v / (1.0f - v));
+}
+#endif
 
 // l1_reg = "num_features(k)": LARS selection + reduced WLS (kshap_lars.cu)
 int fdb_kshap_prepare_lars(fdb_kshap_plan* p);

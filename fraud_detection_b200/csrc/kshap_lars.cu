@@ -2,7 +2,7 @@
 // (what an unmodified KernelExplainer.shap_values(X) call runs [recalled default]).
 //
 // Reference (oracle/kernel_shap.py::solve, restating shap/explainers/_kernel.py::solve):
-//   w_aug   = [kw (M - s); kw s]                     s_m = number of present features of coalition m, M = 30
+//   w_aug   = [kw (M - s); kw s]                     s_m = number of present features of coalition m, M = number of varying features (30 unless the plan says otherwise)
 //   X_aug   = sqrt(w_aug) * [Z; Z - 1],  y_aug = sqrt(w_aug) * [e; e - d]          e = link(ey) - link(fnull)
 //   sel     = sklearn.linear_model.lars_path(X_aug, y_aug, max_iter=k)[1]          (method "lar", Gram form)
 //   l       = sel[-1];  X = Z[:, sel[:-1]] - Z[:, l];  y = e - Z[:, l] d
@@ -52,7 +52,7 @@ struct WarpScratch {
 // Per coalition set: Gz = Z'WZ (30 x 30, row stride 32), B_j = sum kw s z_j, S0 = sum kw s.  One warp per set.
 __global__ void __launch_bounds__(32) kshap_gram_prepare(const uint32_t* __restrict__ bits, const float* __restrict__ kw,
                                                          int m_pad, double* __restrict__ gz, double* __restrict__ bv,
-                                                         double* __restrict__ s0) {
+                                                         double* __restrict__ s0, uint32_t varying) {
     const int s = blockIdx.x, lane = threadIdx.x;
     const uint32_t* sb = bits + (size_t)s * m_pad;
     const float* sk = kw + (size_t)s * m_pad;
@@ -63,8 +63,8 @@ __global__ void __launch_bounds__(32) kshap_gram_prepare(const uint32_t* __restr
     for (int m = 0; m < m_pad; ++m) {
         const double w = (double)sk[m];
         if (w == 0.0) continue;
-        const uint32_t z = sb[m];
-        const double cnt = (double)__popc(z & 0x3FFFFFFFu);
+        const uint32_t z = sb[m] & varying;                       // columns exist for the varying features only
+        const double cnt = (double)__popc(z);
         tot += w * cnt;
         if ((z >> lane) & 1u) {
 #pragma unroll
@@ -92,8 +92,11 @@ __global__ void __launch_bounds__(128) kshap_lars_solve(
     const double* __restrict__ gz, const double* __restrict__ bv, const double* __restrict__ s0v,
     const float* __restrict__ wcoef, double intercept, double fnull, int link, int kfeat, double n_samples_aug,
     float* __restrict__ phi, double* __restrict__ abs_sum, int accumulate, int64_t total_rows,
-    double* __restrict__ partials, unsigned int* __restrict__ ticket) {
+    double* __restrict__ partials, unsigned int* __restrict__ ticket, uint32_t varying) {
     __shared__ WarpScratch scr[4];
+    const bool is_var = (varying >> (threadIdx.x & 31)) & 1u;   // lane j = feature j takes part in the regression
+    const int n_var = __popc(varying);
+    const double Mf = (double)n_var;                            // the reference's M (number of varying features)
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     WarpScratch& S = scr[warp];
@@ -118,7 +121,7 @@ __global__ void __launch_bounds__(128) kshap_lars_solve(
             const uint32_t b = sb[m0 + lane];
             const float kwv = sk[m0 + lane];
             const float ev = er[m0 + lane];
-            const float v = kwv != 0.f ? kwv * ((link == 1 ? logf(ev / (1.0f - ev)) : ev) - lnull_f) : 0.f;
+            const float v = kwv != 0.f ? kwv * ((link == 1 ? logf(fminf(fmaxf(ev, 1e-30f), 0.99999994f) / (1.0f - fminf(fmaxf(ev, 1e-30f), 0.99999994f))) : ev) - lnull_f) : 0.f;
 #pragma unroll
             for (int j = 0; j < FDB_F; ++j) gj[j] += ((b >> j) & 1u) ? v : 0.f;
         }
@@ -132,17 +135,17 @@ __global__ void __launch_bounds__(128) kshap_lars_solve(
                 gj[i] = keep + __shfl_xor_sync(0xffffffffu, send, half);
             }
         }
-        const double T = lane < FDB_F ? (double)gj[0] : 0.0;
+        const double T = is_var ? (double)gj[0] : 0.0;
         const double* G = gz + (size_t)s * FDB_F * 32;
         const double* Bs = bv + (size_t)s * 32;
         const double Bj = Bs[lane];
         const double S0 = s0v[s];
         const double Tsum = warp_sum(T);
-        auto gram = [&](int i, int j) { return 30.0 * G[i * 32 + j] - Bs[i] - Bs[j] + S0; };
+        auto gram = [&](int i, int j) { return Mf * G[i * 32 + j] - Bs[i] - Bs[j] + S0; };
 
         // ---- LARS (method "lar", Gram form) over the augmented system; lane j = feature j
-        double Cov = lane < FDB_F ? 30.0 * T - d * Bj - Tsum + d * S0 : 0.0;
-        bool inactive = lane < FDB_F;
+        double Cov = is_var ? Mf * T - d * Bj - Tsum + d * S0 : 0.0;
+        bool inactive = is_var;
         double coef = 0.0;
         int n_active = 0, n_iter = 0;
         bool drop = false;
@@ -157,7 +160,7 @@ __global__ void __launch_bounds__(128) kshap_lars_solve(
             }
             const double C = best >= 0.0 ? best : 0.0;
             if (C / n_samples_aug <= eq_tol) break;                      // alpha <= alpha_min + tol
-            if (n_iter >= kfeat || n_active >= FDB_F || n_active >= kMaxSel) break;
+            if (n_iter >= kfeat || n_active >= n_var || n_active >= kMaxSel) break;
             if (!drop) {
                 const double Csigned = shfl_d(Cov, bidx);
                 bool degenerate = false;
@@ -332,7 +335,7 @@ int fdb_kshap_prepare_lars(fdb_kshap_plan* p) {
     FDB_CUDA(cudaMalloc((void**)&p->d_gz, (size_t)p->n_sets * FDB_F * 32 * 8));
     FDB_CUDA(cudaMalloc((void**)&p->d_bv, (size_t)p->n_sets * 32 * 8));
     FDB_CUDA(cudaMalloc((void**)&p->d_s0, (size_t)p->n_sets * 8));
-    kshap_gram_prepare<<<p->n_sets, 32>>>(p->d_bits, p->d_kw, p->m_pad, p->d_gz, p->d_bv, p->d_s0);
+    kshap_gram_prepare<<<p->n_sets, 32>>>(p->d_bits, p->d_kw, p->m_pad, p->d_gz, p->d_bv, p->d_s0, p->varying);
     FDB_CUDA(cudaGetLastError());
     FDB_CUDA(cudaDeviceSynchronize());
     return FDB_OK;
@@ -346,7 +349,7 @@ int fdb_kshap_launch_lars_solve(fdb_kshap_plan* p, cudaStream_t st, const float*
     kshap_lars_solve<<<grid, 128, 0, st>>>(x, row_offset, n_rows, set_idx, p->n_sets, p->d_bits, p->d_kw, p->m_pad, p->d_ey,
                                           p->d_gz, p->d_bv, p->d_s0, p->d_wq, p->intercept, p->fnull, p->link,
                                           p->num_features, 2.0 * (double)p->n_masks, phi, abs_sum, accumulate, total_rows,
-                                          p->ctx->d_partials, p->ctx->d_ticket);
+                                          p->ctx->d_partials, p->ctx->d_ticket, p->varying);
     FDB_CUDA(cudaGetLastError());
     return FDB_OK;
 }

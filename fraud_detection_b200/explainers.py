@@ -130,7 +130,9 @@ def _linear_model_of(model):
 class KernelShapPlan:
     """Owner of one native ``fdb_kshap_plan`` (model + background + coalition sets on the GPU)."""
 
-    def __init__(self, coef, intercept, background, bits, weights, link="identity", device=None):
+    def __init__(self, coef, intercept, background, bits, weights, link="identity", device=None, varying_mask=None):
+        """``varying_mask`` (bit k = feature k differs from the background; must contain bit 29): plan for rows
+        where only some features vary (``fdb_kshap_plan_create_varying``); the others get phi = 0."""
         import ctypes as C
         bits = np.ascontiguousarray(bits, dtype=np.uint32)
         weights = np.ascontiguousarray(weights, dtype=np.float64)
@@ -144,9 +146,15 @@ class KernelShapPlan:
         self.n_sets, self.n_masks = int(bits.shape[0]), int(bits.shape[1])
         self.device = device
         h = C.c_void_p()
-        _lib.check(_lib.lib.fdb_kshap_plan_create(
-            _lib.get_ctx(device), _lib.dvec(coef), float(intercept), int(bg.shape[0]), _lib.np_ptr(bg),
-            self.n_sets, self.n_masks, _lib.np_ptr(bits), _lib.np_ptr(weights), _LINKS[link], C.byref(h)))
+        if varying_mask is None:
+            _lib.check(_lib.lib.fdb_kshap_plan_create(
+                _lib.get_ctx(device), _lib.dvec(coef), float(intercept), int(bg.shape[0]), _lib.np_ptr(bg),
+                self.n_sets, self.n_masks, _lib.np_ptr(bits), _lib.np_ptr(weights), _LINKS[link], C.byref(h)))
+        else:
+            _lib.check(_lib.lib.fdb_kshap_plan_create_varying(
+                _lib.get_ctx(device), _lib.dvec(coef), float(intercept), int(bg.shape[0]), _lib.np_ptr(bg),
+                self.n_sets, self.n_masks, _lib.np_ptr(bits), _lib.np_ptr(weights), _LINKS[link],
+                int(varying_mask), C.byref(h)))
         self._h = h.value
         self.expected_value = float(_lib.lib.fdb_kshap_expected_value(self._h))
 
@@ -295,22 +303,38 @@ class B200KernelExplainer:
         A, single = _plain_rows(X)
         A64 = A.astype(np.float64, copy=False)
         varying = self._varying(A64)
-        full = varying.all(1)
+        nvar = varying.sum(1)
         out = np.zeros(A.shape, dtype=np.float64)
+        if sampler not in ("host", "device"):
+            raise ValueError("sampler must be 'host' or 'device'")
+        if mask_mode not in ("per_row", "shared"):
+            raise ValueError("mask_mode must be 'per_row' or 'shared'")
         # degenerate rows (shap: M == 0 -> zeros, M == 1 -> the single varying feature takes f(x) - E[f])
-        if not full.all():
-            for r in np.nonzero(~full)[0]:
-                nv = int(varying[r].sum())
-                if nv == 0:
-                    continue
-                if nv == 1:
-                    fx = float(B200LogisticRegressionProxy(self.coef, self.intercept, self.device).proba(A64[r:r + 1])[0])
-                    lf = (lambda v: np.log(v / (1 - v))) if self.link == "logit" else (lambda v: v)
-                    out[r, np.nonzero(varying[r])[0][0]] = lf(fx) - lf(self.fnull)
-                    continue
-                raise NotImplementedError("rows where 2..29 features vary against the background are not supported "
-                                          "on the B200 path yet (all 30, one or none are)")
-        rows = np.nonzero(full)[0]
+        for r in np.nonzero(nvar == 1)[0]:
+            fx = float(B200LogisticRegressionProxy(self.coef, self.intercept, self.device).proba(A64[r:r + 1])[0])
+            lf = (lambda v: np.log(v / (1 - v))) if self.link == "logit" else (lambda v: v)
+            out[r, np.nonzero(varying[r])[0][0]] = lf(fx) - lf(self.fnull)
+        rows = np.nonzero(nvar == N_FEATURES)[0]
+        part = np.nonzero((nvar >= 2) & (nvar < N_FEATURES))[0]
+        if masks is not None and len(part):
+            raise NotImplementedError("exported masks are taken for rows where all 30 features vary; rows with fewer "
+                                      "varying features draw their coalitions with the library's sampler")
+        # Host-drawn coalition sets, taken in ROW order: the reference consumes one np.random stream row by row.
+        host_sets: dict = {}
+        if masks is None and mask_mode == "per_row":
+            draw = part if sampler == "device" else np.nonzero(nvar >= 2)[0]
+            for r in draw:
+                host_sets[int(r)] = _sampler.sample_coalitions(int(nvar[r]), nsamples, random)
+
+        def shared_set(m_feat):
+            key = (m_feat, nsamples, id(random))
+            if key not in self._shared_cache:
+                self._shared_cache[key] = _sampler.sample_coalitions(m_feat, nsamples, random)
+            return self._shared_cache[key]
+
+        if len(part):
+            self._explain_partial(A, varying, part, host_sets if mask_mode == "per_row" else None, shared_set,
+                                  num_features, evaluator, out)
         if len(rows) == 0:
             return out[0] if single else out
         Xr = np.ascontiguousarray(A[rows], dtype=np.float32)
@@ -333,8 +357,6 @@ class B200KernelExplainer:
             plan.set_num_features(num_features)
             out[rows] = plan.explain_host(Xr, None, evaluator)
             return out[0] if single else out
-        if sampler not in ("host", "device"):
-            raise ValueError("sampler must be 'host' or 'device'")
         if masks is not None:
             pairs = masks if isinstance(masks, list) else [masks]
             sets = [(_sampler.masks_to_bits(Z) if np.asarray(Z).ndim == 2 else np.asarray(Z, dtype=np.uint32), np.asarray(w))
@@ -342,14 +364,9 @@ class B200KernelExplainer:
             if len(sets) not in (1, len(rows)):
                 raise ValueError("masks must be one (Z, kw) pair or one pair per explained row")
         elif mask_mode == "shared":
-            key = (nsamples, id(random))
-            if key not in self._shared_cache:
-                self._shared_cache[key] = [_sampler.sample_coalitions(N_FEATURES, nsamples, random)]
-            sets = self._shared_cache[key]
-        elif mask_mode == "per_row":
-            sets = [_sampler.sample_coalitions(N_FEATURES, nsamples, random) for _ in range(len(rows))]
+            sets = [shared_set(N_FEATURES)]
         else:
-            raise ValueError("mask_mode must be 'per_row' or 'shared'")
+            sets = [host_sets[int(r)] for r in rows]
         bits, kw = self._pad_sets(sets)
         plan = KernelShapPlan(self.coef, self.intercept, self.data, bits, kw, self.link, self.device)
         try:
@@ -360,6 +377,39 @@ class B200KernelExplainer:
             plan.close()
         out[rows] = phi
         return out[0] if single else out
+
+    def _explain_partial(self, A, varying, part, host_sets, shared_set, num_features, evaluator, out):
+        """Rows where 2..29 features differ from the background (shap: M = len(varyingInds) < 30): coalitions are
+        drawn over the M varying features, the others get phi = 0.  Rows are grouped by their varying pattern;
+        per group the feature axis is permuted so that the last varying feature - the one the additivity
+        constraint eliminates in the reference - sits at index 29 (``fdb_kshap_plan_create_varying``)."""
+        packed = np.packbits(varying[part], axis=1, bitorder="little")
+        for pat in np.unique(packed, axis=0):
+            grp = part[(packed == pat).all(1)]
+            v = np.nonzero(varying[grp[0]])[0]
+            perm = np.arange(N_FEATURES)
+            perm[[v[-1], N_FEATURES - 1]] = perm[[N_FEATURES - 1, v[-1]]]
+            pos = v.copy()
+            pos[-1] = N_FEATURES - 1                     # j-th varying feature -> bit pos[j] of the 30-bit coalition word
+            vmask = int(np.bitwise_or.reduce(np.uint32(1) << pos.astype(np.uint32)))
+            sets = [shared_set(len(v))] if host_sets is None else [host_sets[int(r)] for r in grp]
+            spread = []
+            for b, w in sets:
+                b = np.asarray(b, dtype=np.uint32)
+                b30 = np.zeros_like(b)
+                for j, pz in enumerate(pos):
+                    b30 |= ((b >> np.uint32(j)) & np.uint32(1)) << np.uint32(pz)
+                spread.append((b30, np.asarray(w)))
+            bits, kw = self._pad_sets(spread)
+            plan = KernelShapPlan(self.coef[perm], self.intercept, self.data[:, perm], bits, kw, self.link, self.device,
+                                  varying_mask=vmask)
+            try:
+                if num_features:
+                    plan.set_num_features(num_features)
+                phi = plan.explain_host(np.ascontiguousarray(A[grp][:, perm], dtype=np.float32), None, evaluator)
+            finally:
+                plan.close()
+            out[grp[:, None], v[None, :]] = phi[:, pos]
 
 
 class B200LogisticRegressionProxy:

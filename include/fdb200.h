@@ -128,6 +128,15 @@ enum { FDB_KSHAP_EVAL_AUTO = -1, FDB_KSHAP_EVAL_TC = 0, FDB_KSHAP_EVAL_SIMT = 1,
 int fdb_kshap_plan_create(fdb_ctx* ctx, const double* coef, double intercept, int n_bg, const double* bg,
                           int n_sets, int n_masks, const uint32_t* bits, const double* kw, int link,
                           fdb_kshap_plan** out);
+/* Rows for which only some features differ from the background (shap's varyingInds / M < 30, SURVEY.md 8(a) a9
+ * step 1: a feature "varies" when the row's value differs from at least one background row).  varying_mask has
+ * bit k set for each varying feature; it must contain bit 29 (the caller permutes the feature axis of coef, bg and
+ * the rows so that the LAST varying feature sits at index 29 - the one the constraint eliminates, as the reference
+ * eliminates the last varying column) and at least 2 bits.  Coalition bits of the other features are ignored; those
+ * features get phi = 0, the schedule constants (M - s, num_features) use M = popcount(varying_mask). */
+int fdb_kshap_plan_create_varying(fdb_ctx* ctx, const double* coef, double intercept, int n_bg, const double* bg,
+                                  int n_sets, int n_masks, const uint32_t* bits, const double* kw, int link,
+                                  uint32_t varying_mask, fdb_kshap_plan** out);
 /* Same plan, but the n_sets coalition sets are drawn ON THE DEVICE with the reference's schedule (enumerated
  * sizes, paired random draws, duplicate merging, weight renormalisation; Philox stream keyed by (seed, set)):
  * statistically, not bitwise, equivalent to shap's per-row sampling.  nsamples <= 0 means "auto" (2*30 + 2048);

@@ -291,22 +291,27 @@ def expected_value(f, background, link="identity") -> float:
 
 
 # ------------------------------------------------------------------ brute force KAT
-def exact_shapley(f, x, background) -> np.ndarray:
-    """Exact interventional Shapley values by enumerating all 2^M coalitions (small M)."""
+def exact_shapley(f, x, background, players=None) -> np.ndarray:
+    """Exact interventional Shapley values by enumerating all coalitions of ``players`` (default: every feature;
+    pass ``varying_features(x, background)`` to leave out the null players, whose value is 0)."""
     x = np.asarray(x, dtype=np.float64).reshape(-1)
     background = np.asarray(background, dtype=np.float64)
-    M = x.shape[0]
+    players = list(range(x.shape[0])) if players is None else [int(j) for j in players]
+    M = len(players)
+    cache: dict = {}
 
     def v(S):
-        synth = background.copy()
-        idx = list(S)
-        synth[:, idx] = x[idx]
-        return float(np.mean(f(synth)))
+        key = frozenset(S)
+        if key not in cache:
+            synth = background.copy()
+            idx = list(S)
+            synth[:, idx] = x[idx]
+            cache[key] = float(np.mean(f(synth)))
+        return cache[key]
 
-    phi = np.zeros(M)
-    others = list(range(M))
-    for i in range(M):
-        rest = [j for j in others if j != i]
+    phi = np.zeros(x.shape[0])
+    for i in players:
+        rest = [j for j in players if j != i]
         for k in range(M):
             for S in itertools.combinations(rest, k):
                 wgt = math.factorial(k) * math.factorial(M - k - 1) / math.factorial(M)

@@ -243,6 +243,105 @@ def test_degenerate_rows_and_errors(params):
         KernelShapPlan(params.coef, params.intercept, np.zeros((2000, 30)), np.array([1], dtype=np.uint32), np.ones(1))
 
 
+def _partially_varying_case(params, n_bg, seed):
+    """Background whose columns are constant outside a few features, rows that copy the background on a
+    per-row choice of features: shap's varyingInds has 2..29 entries (M < 30)."""
+    rs = np.random.RandomState(seed)
+    bg, X, f = _setup(params, n_bg, 12, seed=seed)
+    bg = bg.copy(); X = X.copy()
+    const_cols = np.array([c for c in range(30) if c not in (1, 4, 29)])
+    bg[:, const_cols] = bg[0, const_cols]                     # columns 1, 4, 29 always vary (when n_bg > 1)
+    counts = [2, 3, 5, 9, 12, 29, 30, 7, 7, 2, 20, 1]          # varying features wanted per row
+    for r, c in enumerate(counts):
+        keep = set(rs.choice(30, size=c, replace=False).tolist())
+        if n_bg > 1:
+            keep |= {1, 4, 29}
+        if r in (7, 8):
+            keep = {0, 2, 3, 5, 6, 7, 8} | ({1, 4, 29} if n_bg > 1 else set())   # two rows, one pattern, last varying != 29
+        for c_ in const_cols:
+            if c_ not in keep:
+                X[r, c_] = bg[0, c_]
+        if n_bg == 1:
+            for c_ in (1, 4, 29):
+                if c_ not in keep:
+                    X[r, c_] = bg[0, c_]
+    X = X.astype(np.float32).astype(np.float64)               # what the device sees
+    bg[:, :] = bg.astype(np.float32).astype(np.float64)
+    for r in range(len(X)):                                   # keep exact equality after the float32 rounding
+        same = np.isclose(X[r], bg[0]) & np.isclose(bg.min(0), bg.max(0))
+        X[r, same] = bg[0, same]
+    return bg, X, f
+
+
+@pytest.mark.parametrize("n_bg", [1, 6])
+@pytest.mark.parametrize("link", ["identity", "logit"])
+def test_rows_where_only_some_features_vary(params, n_bg, link):
+    """shap step 1 (varyingInds): coalitions over the M varying features only, phi = 0 elsewhere; same seed as the oracle."""
+    from fraud_detection_b200 import B200KernelExplainer
+    bg, X, f = _partially_varying_case(params, n_bg, seed=31)
+    counts = [len(ks.varying_features(x, bg)) for x in X]
+    assert min(counts) <= 5 and any(5 < c < 30 for c in counts)
+    expl = B200KernelExplainer((params.coef, params.intercept), bg, link=link)
+    phi = expl.shap_values(X, nsamples=1024, random=np.random.RandomState(5))
+    rs = np.random.RandomState(5)
+    ref, ey_max = [], []
+    for x in X:
+        ph, parts = ks.explain_row(f, x, bg, 1024, False, link, random=rs, return_parts=True)
+        ref.append(ph)
+        ey_max.append(float(np.max(parts["ey"])) if "ey" in parts else 0.0)
+    ref = np.array(ref)
+    lf = (lambda v: np.log(v / (1 - v))) if link == "logit" else (lambda v: v)
+    assert np.all(np.isfinite(phi))
+    compared = 0
+    for r, x in enumerate(X):
+        v = ks.varying_features(x, bg)
+        nz = np.setdiff1d(np.arange(30), v)
+        assert np.all(phi[r, nz] == 0.0), f"row {r}: attribution on a feature that does not vary"
+        if link == "logit" and ey_max[r] > 1.0 - 1e-3:
+            continue       # float32 expectations next to 1: the logit of them is below the 1e-4 bar (DESIGN.md, K3 link)
+        compared += 1
+        assert np.all(np.abs(phi[r] - ref[r]) <= 1e-4 * max(np.abs(ref[r]).max(), 1e-12) + 1e-7), (r, len(v))
+    assert compared >= 8
+    np.testing.assert_allclose(phi.sum(1) + expl.expected_value, lf(f(X)), atol=2e-5 if link == "logit" else 1e-5)
+    # fully enumerated small cases are the exact Shapley values (identity link)
+    if link == "identity":
+        for r, x in enumerate(X):
+            if 2 <= counts[r] <= 9:
+                np.testing.assert_allclose(phi[r], ks.exact_shapley(f, x, bg, ks.varying_features(x, bg)), atol=2e-6)
+    # one coalition set shared by the rows of each pattern
+    shared = expl.shap_values(X, nsamples=1024, mask_mode="shared", random=np.random.RandomState(6))
+    np.testing.assert_allclose(shared.sum(1) + expl.expected_value, lf(f(X)), atol=2e-5 if link == "logit" else 1e-5)
+    np.testing.assert_allclose(shared[7], phi[7], atol=5e-3 * np.abs(phi[7]).max() + 1e-6)
+
+
+def test_num_features_on_partially_varying_rows(params):
+    from fraud_detection_b200 import B200KernelExplainer
+    bg, X, f = _partially_varying_case(params, 6, seed=32)
+    expl = B200KernelExplainer((params.coef, params.intercept), bg)
+    phi = expl.shap_values(X, nsamples=1024, l1_reg="num_features(4)", random=np.random.RandomState(9))
+    ref = ks.shap_values(f, X, bg, nsamples=1024, l1_reg="num_features(4)", random=np.random.RandomState(9))
+    agree = 0
+    for r in range(len(X)):
+        assert np.count_nonzero(phi[r]) <= 4
+        if np.array_equal(phi[r] != 0, ref[r] != 0):
+            agree += 1
+            assert np.all(np.abs(phi[r] - ref[r]) <= 1e-4 * max(np.abs(ref[r]).max(), 1e-12) + 1e-7)
+    assert agree >= len(X) - 1
+    np.testing.assert_allclose(phi.sum(1) + expl.expected_value, f(X), atol=1e-5)
+
+
+def test_varying_plan_argument_checks(params):
+    from fraud_detection_b200 import KernelShapPlan
+    bg, _, _ = _setup(params, 4, 1)
+    bits = np.array([1, 1 << 29], dtype=np.uint32)
+    with pytest.raises(ValueError, match="feature 29"):
+        KernelShapPlan(params.coef, params.intercept, bg, bits, np.ones(2), varying_mask=0b11)
+    with pytest.raises(ValueError, match="at least 2"):
+        KernelShapPlan(params.coef, params.intercept, bg, bits, np.ones(2), varying_mask=1 << 29)
+    plan = KernelShapPlan(params.coef, params.intercept, bg, bits, np.full(2, 0.5), varying_mask=(1 << 29) | 1)
+    plan.close()
+
+
 # --------------------------------------------------------------------------- on-device sampler
 def test_device_sampler_follows_the_reference_schedule(params):
     from fraud_detection_b200 import KernelShapPlan, sampler
