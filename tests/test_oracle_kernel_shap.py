@@ -63,6 +63,22 @@ def test_full_enumeration_equals_bruteforce_shapley(M):
     np.testing.assert_allclose(phi, ks.exact_shapley(f, x, bg), atol=1e-12)
 
 
+def test_partially_varying_row_is_the_reduced_game(params):
+    """shap step 1: features equal to a constant background column are null players (phi = 0); the others get
+    the Shapley values of the game over the varying features only."""
+    bg = scoring.transform(params, synth.rows(5, seed=43))
+    x = scoring.transform(params, synth.rows(1, seed=3))[0]
+    keep = [2, 5, 11, 17, 28]
+    const = [c for c in range(30) if c not in keep]
+    bg[:, const] = bg[0, const]
+    x[const] = bg[0, const]
+    f = _f_proba(params)
+    assert ks.varying_features(x, bg).tolist() == keep
+    phi = ks.explain_row(f, x, bg, nsamples="auto")
+    assert np.all(phi[const] == 0.0)
+    np.testing.assert_allclose(phi, ks.exact_shapley(f, x, bg, keep), atol=1e-12)
+
+
 def test_additivity_probability_output(params):
     rs = np.random.RandomState(2)
     bg = scoring.transform(params, synth.rows(100, seed=43))
