@@ -68,23 +68,13 @@ __global__ void __launch_bounds__(32) kshap_wls_prepare(const uint32_t* __restri
     const int lane = threadIdx.x;
     const uint32_t* sb = bits + (size_t)s * m_pad;
     const float* sk = kw + (size_t)s * m_pad;
+    // x_i x_j = zp_i zp_j with zp = z29 ? ~z : z (x_i = z_i - z_29 = z29 ? -zp_i : zp_i);  c2 = X'W z29 = -sum w zp z29
     double a[kNV];
-#pragma unroll
-    for (int j = 0; j < kNV; ++j) a[j] = 0.0;
-    double c2 = 0.0;
-    for (int m = 0; m < m_pad; ++m) {
-        const double w = (double)sk[m];
-        if (w == 0.0) continue;
-        const uint32_t b = sb[m];
-        const bool z29 = (b >> 29) & 1u;
-        const uint32_t zp = z29 ? ~b : b;          // x_i x_j = zp_i zp_j ; x_i = z29 ? -zp_i : zp_i
-        if ((zp >> lane) & 1u) {
-#pragma unroll
-            for (int j = 0; j < kNV; ++j)
-                if ((zp >> j) & 1u) a[j] += w;
-            if (z29) c2 -= w;
-        }
-    }
+    double c2;
+    fdb_kshap_weighted_gram_row<kNV>(
+        sb, sk, m_pad, lane, [](uint32_t b) { return ((b >> 29) & 1u) ? ~b : b; },
+        [](uint32_t b) { return ((b >> 29) & 1u) != 0u; }, a, c2);
+    c2 = -c2;
     if (lane < kNV) {
 #pragma unroll
         for (int j = 0; j < kNV; ++j) {

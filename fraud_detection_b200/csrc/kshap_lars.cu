@@ -56,23 +56,22 @@ __global__ void __launch_bounds__(32) kshap_gram_prepare(const uint32_t* __restr
     const int s = blockIdx.x, lane = threadIdx.x;
     const uint32_t* sb = bits + (size_t)s * m_pad;
     const float* sk = kw + (size_t)s * m_pad;
+    // B_i = sum_m kw s_m z_mi = sum_j Gz_ij and S0 = sum_m kw s_m = trace(Gz), because s_m = sum_j z_mj
     double a[FDB_F];
+    double unused;
+    fdb_kshap_weighted_gram_row<FDB_F>(
+        sb, sk, m_pad, lane, [varying](uint32_t z) { return z & varying; }, [](uint32_t) { return false; }, a, unused);
+    double b = 0.0;
 #pragma unroll
-    for (int j = 0; j < FDB_F; ++j) a[j] = 0.0;
-    double b = 0.0, tot = 0.0;
-    for (int m = 0; m < m_pad; ++m) {
-        const double w = (double)sk[m];
-        if (w == 0.0) continue;
-        const uint32_t z = sb[m] & varying;                       // columns exist for the varying features only
-        const double cnt = (double)__popc(z);
-        tot += w * cnt;
-        if ((z >> lane) & 1u) {
+    for (int j = 0; j < FDB_F; ++j) b += a[j];
+    double diag = 0.0;
 #pragma unroll
-            for (int j = 0; j < FDB_F; ++j)
-                if ((z >> j) & 1u) a[j] += w;
-            b += w * cnt;
-        }
-    }
+    for (int j = 0; j < FDB_F; ++j)
+        if (j == lane) diag = a[j];
+    if (lane >= FDB_F) diag = 0.0;
+    double tot = diag;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
     if (lane < FDB_F) {
 #pragma unroll
         for (int j = 0; j < FDB_F; ++j) gz[((size_t)s * FDB_F + lane) * 32 + j] = a[j];

@@ -13,8 +13,10 @@
 // host sampler (fraud_detection_b200/sampler.py) remains the bit-compatible one.
 //
 // Per set (one warp, one CTA): every lane proposes one coalition per round (size from the remaining-size
-// CDF, members by drawing the r-th still-unset feature with __fns), lane 0 then walks the 32 proposals in lane
-// order through a shared-memory hash set, so a given (seed, set) always yields the same masks.
+// CDF, members by Floyd's subset algorithm); the 32 proposals are then committed as if one after the other in
+// lane order - parallel hash look-up, __match_any merging of equal proposals, slots from a prefix sum of the
+// budget each proposal takes - so a given (seed, set) always yields the same masks.  The set is assembled in
+// shared memory and written out once.
 
 #include <curand_kernel.h>
 #include <math.h>
@@ -26,8 +28,7 @@
 namespace {
 
 constexpr int kMaxSizes = 16;
-// hash-set slots: >= 4 x the number of random primary draws (nsamples / 2), so probes stay short; the smaller
-// table (24 KB) doubles the resident warps per SM for the common nsamples <= 2048
+// hash-set slots: >= 4 x the number of random primary draws (nsamples / 2), so probes stay short
 
 struct SamplerParams {
     uint32_t* bits;          // [S][m_pad]
@@ -44,85 +45,114 @@ struct SamplerParams {
     unsigned long long seed;
 };
 
-template <int kHashSlots, int kHashShift>
+// Shared memory per set: the set itself (coalition words + draw counts) and an open-addressing hash table of slot
+// indices (0xFFFF = empty; the key of an entry is s_bits[slot]).  24 KB for nsamples <= 2048, 48 KB up to 4096.
+template <int kHashSlots, int kHashShift, int kMaxSamples>
 __global__ void __launch_bounds__(32) kshap_sample_sets(const SamplerParams p) {
-    __shared__ uint32_t h_key[kHashSlots];
-    __shared__ uint16_t h_idx[kHashSlots];
+    __shared__ uint32_t s_bits[kMaxSamples];
+    __shared__ uint32_t s_cnt[kMaxSamples];
+    __shared__ unsigned short h_slot[kHashSlots];
+    const uint32_t allw = 0xffffffffu;
     const int s = blockIdx.x, lane = threadIdx.x;
     uint32_t* ob = p.bits + (size_t)s * p.m_pad;
     float* ow = p.kw + (size_t)s * p.m_pad;
-    for (int i = lane; i < kHashSlots; i += 32) h_key[i] = 0u;        // 0 is never a drawn coalition (size >= 1)
-    for (int i = lane; i < p.m_pad; i += 32) {
-        ob[i] = i < p.n_fixed ? p.fixed_bits[i] : 0u;
-        ow[i] = i < p.n_fixed ? p.fixed_kw[i] : 0.f;
+    for (int i = lane; i < kHashSlots; i += 32) h_slot[i] = 0xFFFFu;
+    for (int i = lane; i < kMaxSamples; i += 32) {
+        s_bits[i] = i < p.n_fixed ? p.fixed_bits[i] : 0u;
+        s_cnt[i] = 0u;
     }
     __syncwarp();
     int samples_left = p.nsamples - p.n_fixed;
-    if (samples_left <= 0 || p.n_sizes == 0) return;
-    curandStatePhilox4_32_10_t rng;
-    curand_init(p.seed, (unsigned long long)s * 32 + lane, 0, &rng);
-    const uint32_t full = 0x3FFFFFFFu;
     int count = p.n_fixed;                       // next free slot (uniform across the warp)
-    int draws_left = 4 * samples_left;           // the reference reads at most 4 x samples_left size draws
-    while (samples_left > 0 && draws_left > 0) {
-        // ---- every lane proposes one coalition
-        const float u = curand_uniform(&rng);
-        int si = 0;
-        while (si < p.n_sizes - 1 && u > p.cdf[si]) ++si;
-        const int size = p.first_size + si;
-        uint32_t mask = 0u;
-        for (int i = 0; i < size; ++i) {
-            const uint32_t r = __umulhi(curand(&rng), (uint32_t)(FDB_F - i));       // uniform in [0, 30 - i)
-            mask |= 1u << __fns(~mask & full, 0, (int)r + 1);
-        }
-        // ---- lane 0 commits the proposals in lane order (deterministic), the others idle
-        const int take = draws_left < 32 ? draws_left : 32;
-        for (int l = 0; l < take && samples_left > 0; ++l) {
-            const uint32_t m = __shfl_sync(0xffffffffu, mask, l);
-            const int msize = __popc(m);
-            int slot = -1;
-            bool is_new = false;
-            if (lane == 0) {
-                uint32_t h = (m * 2654435761u) >> kHashShift;
+    const uint32_t full = 0x3FFFFFFFu;
+    if (samples_left > 0 && p.n_sizes > 0) {
+        curandStatePhilox4_32_10_t rng;
+        curand_init(p.seed, (unsigned long long)s * 32 + lane, 0, &rng);
+        int draws_left = 4 * samples_left;       // the reference reads at most 4 x samples_left size draws
+        while (samples_left > 0 && draws_left > 0) {
+            // ---- every lane proposes one coalition: size from the remaining-size CDF, members by Floyd's
+            //      algorithm (a uniform size-subset of the 30 features from `size` bounded draws)
+            uint4 r4 = curand4(&rng);
+            const float u = (float)r4.x * 2.3283064365386963e-10f + 1.1641532182693481e-10f;   // (0, 1]
+            int si = 0;
+            while (si < p.n_sizes - 1 && u > p.cdf[si]) ++si;
+            const int size = p.first_size + si;
+            uint32_t mask = 0u;
+            for (int i = 0; i < size; ++i) {
+                const int q = (i + 1) & 3;
+                if (q == 0) r4 = curand4(&rng);
+                const uint32_t rnd = q == 0 ? r4.x : (q == 1 ? r4.y : (q == 2 ? r4.z : r4.w));
+                const int j = FDB_F - size + i;
+                const uint32_t t = __umulhi(rnd, (uint32_t)(j + 1));                      // uniform in [0, j]
+                mask |= ((mask >> t) & 1u) ? (1u << j) : (1u << t);
+            }
+            // ---- commit the 32 proposals AS IF one after the other in lane order (so (seed, set) is reproducible):
+            //      look every proposal up, merge equal proposals of this round, hand out slots by a prefix sum
+            const int take = draws_left < 32 ? draws_left : 32;
+            const bool active = lane < take;
+            const bool paired = __popc(mask) <= p.n_paired;
+            int found = -1;
+            if (active) {
+                uint32_t h = (mask * 2654435761u) >> kHashShift;
                 while (true) {
-                    const uint32_t k = h_key[h];
-                    if (k == 0u) { h_key[h] = m; h_idx[h] = (uint16_t)count; slot = count; is_new = true; break; }
-                    if (k == m) { slot = h_idx[h]; break; }
+                    const uint32_t sl = h_slot[h];
+                    if (sl == 0xFFFFu) break;
+                    if (s_bits[sl] == mask) { found = (int)sl; break; }
                     h = (h + 1) & (kHashSlots - 1);
                 }
-                if (is_new) {
-                    ob[slot] = m;
-                    ow[slot] = 1.0f;
-                } else {
-                    ow[slot] += 1.0f;
-                }
             }
-            is_new = __shfl_sync(0xffffffffu, (int)is_new, 0) != 0;
-            slot = __shfl_sync(0xffffffffu, slot, 0);
-            if (is_new) { ++count; --samples_left; }
-            if (samples_left > 0 && msize <= p.n_paired) {                          // the complement rides along
-                if (is_new) {
-                    if (lane == 0) { ob[count] = full ^ m; ow[count] = 1.0f; }
-                    ++count;
-                    --samples_left;
-                } else if (lane == 0) {
-                    // the complement of a known coalition sits right after it - unless the budget ran out exactly
-                    // when that coalition was added; a zero-weight slot there is still unused
-                    if (ob[slot + 1] == (full ^ m)) ow[slot + 1] += 1.0f;
-                }
+            const uint32_t peers = __match_any_sync(allw, active ? mask : (0x80000000u | (uint32_t)lane));
+            const int leader = __ffs(peers) - 1;
+            const bool is_new = active && found < 0 && leader == lane;
+            const int inc = is_new ? (paired ? 2 : 1) : 0;
+            int incl = inc;                                                               // inclusive prefix sum
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(allw, incl, o);
+                if (lane >= o) incl += v;
             }
+            const int before = incl - inc;
+            const bool processed = active && samples_left - before > 0;                  // budget left when its turn comes
+            int slot = is_new ? count + before : found;
+            if (is_new && processed) {
+                s_bits[slot] = mask;
+                s_cnt[slot] = 1u;
+                if (paired && samples_left - before > 1) {                               // the complement rides along
+                    s_bits[slot + 1] = full ^ mask;
+                    s_cnt[slot + 1] = 1u;
+                }
+                uint32_t h = (mask * 2654435761u) >> kHashShift;
+                while (atomicCAS(&h_slot[h], (unsigned short)0xFFFFu, (unsigned short)slot) != 0xFFFFu)
+                    h = (h + 1) & (kHashSlots - 1);
+            }
+            slot = __shfl_sync(allw, slot, leader);                                      // merged proposals follow their leader
+            __syncwarp();
+            if (processed && !is_new) {
+                atomicAdd(&s_cnt[slot], 1u);
+                // the complement of a known coalition sits right after it - unless the budget ran out exactly
+                // when that coalition was added
+                if (paired && slot + 1 < p.nsamples && s_bits[slot + 1] == (full ^ mask)) atomicAdd(&s_cnt[slot + 1], 1u);
+            }
+            int added = __shfl_sync(allw, incl, 31);
+            if (added > samples_left) added = samples_left;
+            count += added;
+            samples_left -= added;
+            draws_left -= take;
             __syncwarp();
         }
-        draws_left -= take;
     }
     __syncwarp();
-    // ---- random block weights sum to weight_left
-    float tot = 0.f;
-    for (int i = p.n_fixed + lane; i < count; i += 32) tot += ow[i];
+    // ---- write the set out; random block weights (draw counts) are scaled to sum to weight_left
+    uint32_t tot = 0u;
+    for (int i = p.n_fixed + lane; i < count; i += 32) tot += s_cnt[i];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
-    const float scale = tot > 0.f ? p.weight_left / tot : 0.f;
-    for (int i = p.n_fixed + lane; i < count; i += 32) ow[i] *= scale;
+    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(allw, tot, o);
+    const float scale = tot > 0u ? p.weight_left / (float)tot : 0.f;
+    for (int i = lane; i < p.m_pad; i += 32) {
+        const bool in_set = i < count;
+        ob[i] = in_set ? s_bits[i] : 0u;
+        ow[i] = !in_set ? 0.f : (i < p.n_fixed ? p.fixed_kw[i] : (float)s_cnt[i] * scale);
+    }
 }
 
 double binom(int n, int k) {
@@ -224,8 +254,8 @@ int fdb_kshap_sample_on_device(fdb_kshap_plan* pl, int nsamples, unsigned long l
     if (e == cudaSuccess) {
         sp.fixed_bits = d_fb;
         sp.fixed_kw = d_fw;
-        if (nsamples <= 2048) kshap_sample_sets<4096, 20><<<pl->n_sets, 32>>>(sp);
-        else kshap_sample_sets<8192, 19><<<pl->n_sets, 32>>>(sp);
+        if (nsamples <= 2048) kshap_sample_sets<4096, 20, 2048><<<pl->n_sets, 32>>>(sp);
+        else kshap_sample_sets<8192, 19, 4096><<<pl->n_sets, 32>>>(sp);
         e = cudaGetLastError();
     }
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
