@@ -51,7 +51,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--rows", type=int, default=int(os.environ.get("FDB_BENCH_ROWS", 100_000_000)),
                     help="rows per GPU resident in HBM (config 2: 1e8)")
-    ap.add_argument("--e2e-rows", type=int, default=int(os.environ.get("FDB_BENCH_E2E_ROWS", 8_000_000)))
+    ap.add_argument("--e2e-rows", type=int, default=int(os.environ.get("FDB_BENCH_E2E_ROWS", 32_000_000)))
     ap.add_argument("--kshap-rows", type=int, default=int(os.environ.get("FDB_BENCH_KSHAP_ROWS", 100_000)))
     ap.add_argument("--kshap-per-row", type=int, default=32768)
     ap.add_argument("--kshap4-rows", type=int, default=125_000)
@@ -231,7 +231,7 @@ def bench_kernel_shap(args, torch, dist, device, rank, world, prm, sm_max_mhz):
     """Config 3: nsamples=2048, 100-row background, 100k explained rows per GPU, shared coalition set
     (the throughput mode), plus a per-row-mask subset (the reference's sampler).  Returns a dict for
     the JSON line; timing is CUDA events on the launching stream, max over ranks."""
-    from fraud_detection_b200 import KernelShapPlan, PinnedBuffer, sampler
+    from fraud_detection_b200 import KernelShapPlan, PinnedBuffer, host_near_gpu, sampler
     from oracle import scoring, synth
 
     rows, nsamples, n_bg = args.kshap_rows, 2048, 100
@@ -285,7 +285,8 @@ def bench_kernel_shap(args, torch, dist, device, rank, world, prm, sm_max_mhz):
                               "sigmoids_per_s": sig * world / (ms_tc * 1e-3)},
     }
     # e2e through the host entry point (H2D of rows, D2H of phi inside the timed region)
-    hx, hphi = PinnedBuffer((rows, 30), np.float32), PinnedBuffer((rows, 30), np.float32)
+    with host_near_gpu(device.index):
+        hx, hphi = PinnedBuffer((rows, 30), np.float32), PinnedBuffer((rows, 30), np.float32)
     hx.array[:] = X
     import ctypes as C  # noqa: F401
     from fraud_detection_b200 import _lib
@@ -344,11 +345,21 @@ def bench_kernel_shap(args, torch, dist, device, rank, world, prm, sm_max_mhz):
     torch.cuda.synchronize()
     t_plan = time.perf_counter() - t0
     ms2 = timed(lambda: plan2.explain_dev(x2, phi=phi2), steps)
+    # steady state of a row stream: the plan is kept, its sets are redrawn in place for every new batch of rows
+    sync()
+    t0 = time.perf_counter()
+    for i in range(3):
+        plan2.resample(100 + 3 * rank + i)
+        plan2.explain_dev(x2, phi=phi2)
+    torch.cuda.synchronize()
+    t_stream = (time.perf_counter() - t0) / 3
     out["per_row_masks"] = {"rows": pr, "sets": pr, "sampler": "device (Philox, reference schedule)",
                             "value": pr * world / (ms2 * 1e-3), "unit": "explained rows/s", "ms_per_step": ms2,
                             "plan_ms": t_plan * 1e3,
                             "value_including_sampling": pr * world / (ms2 * 1e-3 + t_plan),
-                            "note": "plan_ms = drawing the sets + operand images + per-set (X'WX)^-1, paid once per batch of rows"}
+                            "stream_ms_per_batch": t_stream * 1e3, "value_stream": pr * world / t_stream,
+                            "note": "plan_ms = drawing the sets + operand images + per-set (X'WX)^-1, paid once per batch of rows; "
+                                    "value_stream = fdb_kshap_plan_resample + explain per batch (wall clock, fresh sets every batch)"}
     plan2.close()
 
     sms = torch.cuda.get_device_properties(device).multi_processor_count
@@ -396,7 +407,7 @@ def run_b200(args):
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=device)
 
-    from fraud_detection_b200 import PinnedBuffer
+    from fraud_detection_b200 import PinnedBuffer, host_near_gpu
     from fraud_detection_b200.device import FraudScorer, LinearPassOut
     from fraud_detection_b200.distributed import allreduce_abs_sum
     from oracle import scoring
@@ -447,7 +458,8 @@ def run_b200(args):
 
     # ---- e2e: pinned host buffers through fdb_linear_pass_host (H2D + kernel + D2H timed)
     ne = args.e2e_rows
-    hx, hp, hphi = PinnedBuffer((ne, 30), np.float32), PinnedBuffer((ne,), np.float32), PinnedBuffer((ne, 30), np.float32)
+    with host_near_gpu(local) as near:     # page-locked buffers on the socket this GPU's PCIe link hangs off
+        hx, hp, hphi = PinnedBuffer((ne, 30), np.float32), PinnedBuffer((ne,), np.float32), PinnedBuffer((ne, 30), np.float32)
     hx.array[:] = x[:ne].cpu().numpy() if ne <= n else 0
     host_out = {"proba": hp.array, "phi": hphi.array, "abs_sum": np.zeros(32)}
     e2e_steps = max(3, min(args.steps, 10))
@@ -463,7 +475,26 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = ne * world * e2e_steps / float(t.item())
 
-    del hx, hp, hphi
+    # what the link itself carries: plain pinned copies of the same sizes, both directions at once (the e2e roofline)
+    s_in, s_out = torch.cuda.Stream(device), torch.cuda.Stream(device)
+    t_in, t_out = torch.from_numpy(hx.array), torch.from_numpy(hphi.array)
+    d_in, d_out = torch.empty_like(x[:ne]), torch.empty_like(x[:ne])
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+    for rep in range(2):
+        barrier()
+        with torch.cuda.stream(s_in):
+            ev[0].record()
+            d_in.copy_(t_in, non_blocking=True)
+            ev[1].record()
+        with torch.cuda.stream(s_out):
+            ev[2].record()
+            t_out.copy_(d_out, non_blocking=True)
+            ev[3].record()
+        barrier()
+    pcie = {"h2d_GBps": ne * 120 / (ev[0].elapsed_time(ev[1]) * 1e-3) / 1e9, "d2h_GBps": ne * 120 / (ev[2].elapsed_time(ev[3]) * 1e-3) / 1e9,
+            "what": "plain pinned copies of one step's input and phi, both directions concurrently, this rank"}
+    pcie["rows_per_s_at_link_speed"] = min(pcie["h2d_GBps"] * 1e9 / 120, pcie["d2h_GBps"] * 1e9 / 124)
+    del hx, hp, hphi, t_in, t_out, d_in, d_out
     kshap = None if args.no_kshap else bench_kernel_shap(args, torch, dist, device, rank, world, prm, clocks.max_mhz)
 
     if rank == 0:
@@ -481,7 +512,9 @@ def run_b200(args):
             "config": workload_config(args, world),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": ne * 120,
                     "d2h_bytes_per_step": ne * 124 + 256, "rows_per_step": ne, "steps": e2e_steps,
-                    "api": "fdb_linear_pass_host (pinned host in/out, 3-stream chunked pipeline)"},
+                    "api": "fdb_linear_pass_host (pinned host in/out, 3-stream chunked pipeline)",
+                    "pcie": pcie, "frac_of_link": (e2e_value / world) / pcie["rows_per_s_at_link_speed"],
+                    "host_buffers_numa_local_cpus": None if near.cpus is None else len(near.cpus)},
             "gpu_launches": args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": NCU_TRAFFIC_BYTES_PER_ROW * n, "kernel": "linear_pass_tma_kernel<float,false,true>", "kernel_ms": kernel_ms,

@@ -10,7 +10,7 @@ the built library (``python fraud_detection_b200/build.py``); there is no CPU fa
 serving classes do not pull torch into a gunicorn/Celery worker.
 """
 
-from ._lib import FdbError, PinnedBuffer, get_ctx, lib  # noqa: F401
+from ._lib import FdbError, PinnedBuffer, get_ctx, host_near_gpu, lib  # noqa: F401
 from .estimators import B200LogisticRegression, B200StandardScaler, from_joblib, wrap  # noqa: F401
 from .explainers import B200KernelExplainer, B200LinearExplainer, KernelShapPlan  # noqa: F401
 

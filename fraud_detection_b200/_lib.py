@@ -153,3 +153,48 @@ class PinnedBuffer:
                 lib.fdb_pinned_free(ptr)
             except Exception:
                 pass
+
+
+class host_near_gpu:
+    """``with host_near_gpu(device): buf = PinnedBuffer(...)`` - run the enclosed host allocations on the CPUs next to
+    the GPU (NVML's ideal CPU affinity), so page-locked buffers land on the socket the GPU's PCIe link hangs off
+    instead of wherever the scheduler put the process; the previous affinity is restored on exit.  A no-op when
+    NVML or the affinity call is not available (``.cpus`` is then None)."""
+
+    def __init__(self, device=None):
+        self.device = device
+        self.cpus = None
+        self._saved = None
+
+    def __enter__(self):
+        import os
+        try:
+            import pynvml
+            import torch
+            idx = torch.cuda.current_device() if self.device is None else int(self.device)
+            pynvml.nvmlInit()
+            try:
+                h = pynvml.nvmlDeviceGetHandleByUUID("GPU-" + str(torch.cuda.get_device_properties(idx).uuid))
+            except Exception:
+                h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            n_words = (os.cpu_count() + 63) // 64
+            words = pynvml.nvmlDeviceGetCpuAffinity(h, n_words)
+            ideal = {w * 64 + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1}
+            allowed = os.sched_getaffinity(0)
+            cpus = ideal & allowed
+            if cpus:
+                self._saved = allowed
+                os.sched_setaffinity(0, cpus)
+                self.cpus = sorted(cpus)
+        except Exception:
+            self.cpus = None
+        return self
+
+    def __exit__(self, *exc):
+        import os
+        if self._saved is not None:
+            try:
+                os.sched_setaffinity(0, self._saved)
+            except Exception:
+                pass
+        return False

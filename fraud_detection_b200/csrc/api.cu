@@ -154,7 +154,12 @@ int run_host(fdb_ctx* ctx, int dtype, int64_t n, const void* x, const LinearPara
     // bulk path: chunk c runs on slot c % 3; stream order protects each slot's buffers, and the
     // three streams overlap H2D(c+1), kernel(c) and D2H(c-1).  Pinned caller buffers DMA
     // directly; pageable ones are staged by the driver (correct, just slower).
-    int64_t chunk = (n + 11) / 12;                      // aim for >= 12 chunks so the three stages overlap
+    // fill + drain cost one chunk's copy time, so aim for many chunks; the floor below keeps every copy large
+    // enough (>= 7.8 MB) for the link to run at speed
+    int want_chunks = 32;
+    if (const char* e = getenv("FDB_PIPE_CHUNKS")) { const int v = atoi(e); if (v >= 1 && v <= 4096) want_chunks = v; }
+    int64_t chunk = (n + want_chunks - 1) / want_chunks;
+    if (chunk < 262144 && !getenv("FDB_PIPE_CHUNKS")) chunk = 262144;     // 30 MB copies (f32 rows)
     if (chunk < 4 * kSmallRows) chunk = 4 * kSmallRows;
     chunk = (chunk + 3) & ~int64_t(3);
     if (chunk > ctx->chunk_rows) chunk = ctx->chunk_rows;
