@@ -26,7 +26,10 @@ asserts HTTP status codes only).  They follow the published algorithm as
 recalled from upstream ``shap/explainers/_linear.py`` and ``_kernel.py`` and are
 anchored by known-answer identities instead (Kernel SHAP of a linear model under
 the identity link equals linear SHAP; brute-force Shapley values on 2-4 feature
-toys; additivity) - see ``tests/test_oracle_kernel_shap.py``.
+toys; additivity) - see ``tests/test_oracle_kernel_shap.py``.  The MODEL FUNCTION inside the
+Kernel SHAP vectors is pinned: ``tests/golden/kernel_shap_golden.npz``
+(``tools/make_golden_kshap.py``) holds coalition expectations computed by the reference's own
+unpickled ``LogisticRegression.predict_proba``; only the shap algorithm around it is restated.
 """
 
 from . import scoring, linear_shap, kernel_shap, synth  # noqa: F401

@@ -492,3 +492,38 @@ def test_resample_in_place(params):
     np.testing.assert_allclose(a.sum() + expl.expected_value, f(X[:1])[0], atol=1e-5)
     np.testing.assert_allclose(b.sum() + expl.expected_value, f(X[:1])[0], atol=1e-5)
     assert np.abs(a - b).max() < 0.05
+
+
+# --------------------------------------------------------------------------- committed golden vectors
+@pytest.mark.parametrize("evaluator", [TC, FX, SIMT])
+def test_golden_vectors(params, evaluator):
+    """tests/golden/kernel_shap_golden.npz: ey from the reference's unpickled sklearn model, phi from the oracle's solve."""
+    import os
+    from fraud_detection_b200 import B200KernelExplainer, KernelShapPlan
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "kernel_shap_golden.npz"))
+    bg, X = g["background"], g["X"]
+    plan = KernelShapPlan(params.coef, params.intercept, bg, g["bits"], g["kw"])
+    assert abs(plan.expected_value - float(g["fnull"])) < 1e-12
+    phi, ey, _ = _run(plan, X, evaluator)
+    np.testing.assert_allclose(ey, g["ey"], rtol=0, atol=2e-6)
+    for a, b in zip(phi, g["phi_identity"]):
+        assert np.all(np.abs(a - b) <= 1e-4 * np.abs(b).max() + 1e-9)
+    np.testing.assert_allclose(phi.sum(1) + float(g["fnull"]), g["fx"], atol=1e-5)
+    plan.set_num_features(10)
+    phi10, _, _ = _run(plan, X, evaluator)
+    same = [np.array_equal(a != 0, b != 0) for a, b in zip(phi10, g["phi_num_features_10"])]
+    assert sum(same) >= len(X) - 1
+    for a, b, ok in zip(phi10, g["phi_num_features_10"], same):
+        if ok:
+            assert np.all(np.abs(a - b) <= 1e-4 * np.abs(b).max() + 1e-9)
+    plan.close()
+    plan = KernelShapPlan(params.coef, params.intercept, bg, g["bits"], g["kw"], link="logit")
+    phil, _, _ = _run(plan, X, evaluator)
+    for a, b in zip(phil, g["phi_logit"]):
+        assert np.all(np.abs(a - b) <= 1e-4 * np.abs(b).max() + 1e-7)
+    plan.close()
+    if evaluator == TC:
+        expl = B200KernelExplainer((params.coef, params.intercept), g["vary_background"])
+        pv = expl.shap_values(g["vary_x"], nsamples="auto", random=np.random.RandomState(1))
+        assert np.all(np.abs(pv - g["vary_phi"]) <= 1e-4 * np.abs(g["vary_phi"]).max() + 1e-8)
+        assert np.nonzero(pv)[0].tolist() == g["vary_features"].tolist()

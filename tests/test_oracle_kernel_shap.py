@@ -121,3 +121,36 @@ def test_l1_reg_num_features_selects_subset(params):
     phi = ks.explain_row(f, x, bg, nsamples=2048, l1_reg="num_features(10)", random=rs)
     assert 1 <= np.count_nonzero(phi) <= 10
     np.testing.assert_allclose(phi.sum() + ks.expected_value(f, bg), f(x[None])[0], atol=1e-12)
+
+
+# ------------------------------------------------------------------ committed golden vectors
+def _golden():
+    import os
+    return np.load(os.path.join(os.path.dirname(__file__), "golden", "kernel_shap_golden.npz"))
+
+
+def test_oracle_reproduces_the_golden_vectors(params):
+    """tests/golden/kernel_shap_golden.npz (tools/make_golden_kshap.py): coalition expectations computed with the
+    reference's own unpickled sklearn model; the oracle's numpy model function must land on them."""
+    g = _golden()
+    f = _f_proba(params)
+    Z = ((g["bits"][:, None] >> np.arange(30, dtype=np.uint32)[None, :]) & 1).astype(np.float64)
+    Zs, kws, info = ks.sample_coalitions(30, 2048, np.random.RandomState(0))
+    assert np.array_equal(Zs, Z) and np.array_equal(kws, g["kw"])          # the sampler has not drifted
+    assert info["nfixed_samples"] == int(g["nfixed"]) and abs(info["weight_left"] - float(g["weight_left"])) < 1e-15
+    bg, X = g["background"], g["X"]
+    assert abs(float(f(bg).mean()) - float(g["fnull"])) < 1e-15
+    np.testing.assert_allclose(f(X), g["fx"], rtol=0, atol=1e-15)
+    for i in range(3):
+        ey = ks.evaluate(f, X[i], bg, Z)
+        np.testing.assert_allclose(ey, g["ey"][i], rtol=0, atol=1e-15)         # sklearn vs numpy sigmoid: last bit
+        fx, fnull = float(g["fx"][i]), float(g["fnull"])
+        np.testing.assert_allclose(ks.solve(Z, g["kw"], ey, fx, fnull), g["phi_identity"][i], rtol=0, atol=1e-12)
+        np.testing.assert_allclose(ks.solve(Z, g["kw"], ey, fx, fnull, link="logit"), g["phi_logit"][i], rtol=0, atol=1e-10)
+        np.testing.assert_allclose(ks.solve(Z, g["kw"], ey, fx, fnull, l1_reg="num_features(10)"),
+                                   g["phi_num_features_10"][i], rtol=0, atol=1e-12)
+    np.testing.assert_allclose(g["phi_identity"].sum(1) + g["fnull"], g["fx"], atol=1e-12)
+    assert np.all(np.count_nonzero(g["phi_num_features_10"], axis=1) == 10)
+    phi_v = ks.explain_row(f, g["vary_x"], g["vary_background"], nsamples="auto", random=np.random.RandomState(1))
+    np.testing.assert_allclose(phi_v, g["vary_phi"], rtol=0, atol=1e-12)
+    assert np.nonzero(g["vary_phi"])[0].tolist() == g["vary_features"].tolist()
