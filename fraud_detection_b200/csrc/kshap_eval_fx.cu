@@ -73,19 +73,37 @@ __device__ __forceinline__ float fx_from_h16(uint16_t h, int fmt) {
 // SFU latency and share the loop overhead).  e0 points at E[m0][chunk columns] in smem, rows are cbs floats
 // apart; every lane reads the same addresses -> broadcast LDS.128.  WIDE: logit link, two sigmoids per
 // reciprocal and clamp 2^62 so that tiny sigmoids keep their relative accuracy.
-template <bool WIDE>
+// MODE 0 / 1 (clamped): d = min(E u + 1, clamp), u = 2^t;  0 = four sigmoids per reciprocal, clamp 2^30 (a sigmoid
+//   moves by < 1e-9);  1 = logit link: two per reciprocal and clamp 2^62 so tiny sigmoids keep their relative accuracy.
+// MODE 2 (balanced, no clamp): sigma = 1 / (1 + E u) = b / (E a + b) with (a, b) = (u, 1) for u <= 1 and (1, 1/u)
+//   otherwise, so d = E a + b never exceeds 2^hs + 1 nor falls below 2^-hs (hs = the plan's largest half-spread of a
+//   coalition's background exponents).  With hs <= 30 the product of four d stays inside fp32 range: no min(), exact
+//   relative accuracy for tiny sigmoids (both links), 3.5 issue slots per sigmoid.  acc gathers sum 1/d; the caller
+//   multiplies by b once per (row, coalition).
+enum { kFxClampedQuads = 0, kFxClampedPairs = 1, kFxBalanced = 2 };
+
+template <int MODE>
 __device__ __forceinline__ void chunk_sum4(const float* __restrict__ e0, int cbs, int nquads, int ntail,
-                                           const float* __restrict__ u, float* __restrict__ acc) {
-    constexpr float kClamp = WIDE ? 4.611686018427388e18f : 1073741824.f;
+                                           const float* __restrict__ t, float* __restrict__ acc) {
+    constexpr float kClamp = MODE == kFxClampedPairs ? 4.611686018427388e18f : 1073741824.f;
+    float a[4], b[4];
+#pragma unroll
+    for (int mm = 0; mm < 4; ++mm) {
+        a[mm] = ptx::ex2_approx(MODE == kFxBalanced ? fminf(t[mm], 0.f) : t[mm]);
+        b[mm] = MODE == kFxBalanced ? ptx::ex2_approx(fminf(-t[mm], 0.f)) : 1.0f;
+    }
 #pragma unroll 2
     for (int q = 0; q < nquads; ++q) {
 #pragma unroll
         for (int mm = 0; mm < 4; ++mm) {
             const float4 e = *reinterpret_cast<const float4*>(e0 + mm * cbs + 4 * q);
-            const float d0 = fminf(fmaf(e.x, u[mm], 1.0f), kClamp), d1 = fminf(fmaf(e.y, u[mm], 1.0f), kClamp);
-            const float d2 = fminf(fmaf(e.z, u[mm], 1.0f), kClamp), d3 = fminf(fmaf(e.w, u[mm], 1.0f), kClamp);
+            float d0 = fmaf(e.x, a[mm], b[mm]), d1 = fmaf(e.y, a[mm], b[mm]);
+            float d2 = fmaf(e.z, a[mm], b[mm]), d3 = fmaf(e.w, a[mm], b[mm]);
+            if (MODE != kFxBalanced) {
+                d0 = fminf(d0, kClamp); d1 = fminf(d1, kClamp); d2 = fminf(d2, kClamp); d3 = fminf(d3, kClamp);
+            }
             const float n01 = d0 + d1, p01 = d0 * d1, n23 = d2 + d3, p23 = d2 * d3;
-            if (WIDE) {
+            if (MODE == kFxClampedPairs) {
                 acc[mm] = fmaf(n01, ptx::rcp_approx(p01), acc[mm]);
                 acc[mm] = fmaf(n23, ptx::rcp_approx(p23), acc[mm]);
             } else {
@@ -95,8 +113,10 @@ __device__ __forceinline__ void chunk_sum4(const float* __restrict__ e0, int cbs
     }
     for (int i = 0; i < ntail; ++i)
 #pragma unroll
-        for (int mm = 0; mm < 4; ++mm)
-            acc[mm] += ptx::rcp_approx(fminf(fmaf(e0[mm * cbs + 4 * nquads + i], u[mm], 1.0f), kClamp));
+        for (int mm = 0; mm < 4; ++mm) {
+            const float d = fmaf(e0[mm * cbs + 4 * nquads + i], a[mm], b[mm]);
+            acc[mm] += ptx::rcp_approx(MODE == kFxBalanced ? d : fminf(d, kClamp));
+        }
 }
 
 #ifndef FDB_FX_SERVICE_SLEEP_NS
@@ -109,7 +129,7 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity
 
 __device__ __forceinline__ int fx_cbw(int n_bg, int c) { const int r = n_bg - 128 * c; return r < 128 ? r : 128; }
 
-template <bool WIDE>
+template <int MODE>
 __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     unsigned char* sE = smem;                                   // [2][65536]
@@ -237,27 +257,13 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
             ptx::mbar_wait(&bars->t_full[s], (k >> 1) & 1);
             ptx::tc_fence_after();
             const uint32_t ta = tmem_base + ((uint32_t)(qd * 32) << 16) + s * 128 + cg * 32;
-            uint32_t r0[16], r1[16];
-            ptx::tmem_ld16(ta, r0);
-            ptx::tmem_ld16(ta + 16, r1);
-            ptx::tmem_ld_wait();
-            ptx::tc_fence_before();
-            __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(&bars->t_empty[s]);
-            float uu[32], part[32];
+            // The exponents t[r][m] = D + o_m stay in TMEM for the whole unit (the other accumulator stage keeps the
+            // MMA warp busy meanwhile) and are fetched four coalitions at a time, so only the 32 running sums live
+            // in registers across the background chunks.
+            float part[32];
+#pragma unroll
+            for (int mi = 0; mi < 32; ++mi) part[mi] = 0.f;
             const float4* op = reinterpret_cast<const float4*>(p.eoff + tile * 128 + cg * 32);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const float4 o = __ldg(op + i);
-                const float oo[4] = {o.x, o.y, o.z, o.w};
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const int mi = i * 4 + q;
-                    const float sq = __uint_as_float(mi < 16 ? r0[mi] : r1[mi - 16]) + oo[q];
-                    uu[mi] = ptx::ex2_approx(fminf(fmaxf(sq, -126.f), 126.f));
-                    part[mi] = 0.f;
-                }
-            }
             for (int c = 0; c < p.n_chunks; ++c, ++j) {
                 const int es = j & 1;
                 const int cbw = fx_cbw(p.n_bg, c);
@@ -265,11 +271,41 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
                 ptx::mbar_wait(&bars->e_full[es], (j >> 1) & 1);
                 const float* eb = reinterpret_cast<const float*>(sE + es * kEStageBytes) + (size_t)cg * 32 * cbs;
 #pragma unroll
-                for (int g4 = 0; g4 < 8; ++g4)
-                    chunk_sum4<WIDE>(eb + (size_t)g4 * 4 * cbs, cbs, cbw >> 2, cbw & 3, uu + 4 * g4, part + 4 * g4);
+                for (int g4 = 0; g4 < 8; ++g4) {
+                    uint32_t rr[4];
+                    ptx::tmem_ld4(ta + 4 * g4, rr);
+                    ptx::tmem_ld_wait();
+                    const float4 o = __ldg(op + g4);
+                    float t4[4];
+                    t4[0] = fminf(fmaxf(__uint_as_float(rr[0]) + o.x, -126.f), 126.f);
+                    t4[1] = fminf(fmaxf(__uint_as_float(rr[1]) + o.y, -126.f), 126.f);
+                    t4[2] = fminf(fmaxf(__uint_as_float(rr[2]) + o.z, -126.f), 126.f);
+                    t4[3] = fminf(fmaxf(__uint_as_float(rr[3]) + o.w, -126.f), 126.f);
+                    chunk_sum4<MODE>(eb + (size_t)g4 * 4 * cbs, cbs, cbw >> 2, cbw & 3, t4, part + 4 * g4);
+                }
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(&bars->e_empty[es]);
             }
+            if (MODE == kFxBalanced) {                       // sigma sums were gathered as sum 1/d: scale by b = min(1, 2^-t)
+                uint32_t r0[16], r1[16];
+                ptx::tmem_ld16(ta, r0);
+                ptx::tmem_ld16(ta + 16, r1);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float4 o = __ldg(op + i);
+                    const float oo[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int mi = i * 4 + q;
+                        const float t = fminf(fmaxf(__uint_as_float(mi < 16 ? r0[mi] : r1[mi - 16]) + oo[q], -126.f), 126.f);
+                        part[mi] *= ptx::ex2_approx(fminf(-t, 0.f));
+                    }
+                }
+            }
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&bars->t_empty[s]);
             if (row < p.n_rows) {
                 // fused first half of the least-squares solve: this thread's share of X'W y,
                 //   g[j] += (kw_m x_mj) * (link(ey[r][m]) - link(fnull))   over its 32 coalitions
@@ -401,6 +437,7 @@ int fdb_kshap_build_factored(fdb_kshap_plan* pl, const double* bg_host) {
     cudaFree(d_spread);
     cudaFree(dP);
     FDB_CUDA(e);
+    pl->fx_half_spread = worst;
     if (worst > 100.f) {
         cudaFree(pl->d_E);
         pl->d_E = nullptr;
@@ -423,15 +460,20 @@ int fdb_kshap_launch_eval_fx(fdb_kshap_plan* pl, cudaStream_t st, const float* x
     const size_t smem = 2 * kEStageBytes + 2 * kTileBytes + 2 * kQBytes + sizeof(FxBars) + 64;
     static bool configured[FDB_MAX_DEVICES] = {};          // function attributes are per device
     if (!configured[pl->ctx->device]) {
-        FDB_CUDA(cudaFuncSetAttribute(kshap_eval_fx_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        FDB_CUDA(cudaFuncSetAttribute(kshap_eval_fx_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        FDB_CUDA(cudaFuncSetAttribute(kshap_eval_fx_kernel<kFxClampedQuads>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        FDB_CUDA(cudaFuncSetAttribute(kshap_eval_fx_kernel<kFxClampedPairs>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        FDB_CUDA(cudaFuncSetAttribute(kshap_eval_fx_kernel<kFxBalanced>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured[pl->ctx->device] = true;
     }
     const int64_t n_units = (int64_t)((n_rows + 127) / 128) * p.tiles;
     int64_t grid = n_units < pl->ctx->sm_count ? n_units : pl->ctx->sm_count;
     if (grid < 1) grid = 1;
-    if (pl->link == 1) kshap_eval_fx_kernel<true><<<(int)grid, kFxThreads, smem, st>>>(p);
-    else kshap_eval_fx_kernel<false><<<(int)grid, kFxThreads, smem, st>>>(p);
+    // balanced (clamp-free) inner loop whenever every coalition's background exponents stay within +-30 of their centre
+    const char* force = getenv("FDB_FX_CLAMPED");
+    const bool balanced = pl->fx_half_spread <= 30.f && !(force && atoi(force) != 0);
+    if (balanced) kshap_eval_fx_kernel<kFxBalanced><<<(int)grid, kFxThreads, smem, st>>>(p);
+    else if (pl->link == 1) kshap_eval_fx_kernel<kFxClampedPairs><<<(int)grid, kFxThreads, smem, st>>>(p);
+    else kshap_eval_fx_kernel<kFxClampedQuads><<<(int)grid, kFxThreads, smem, st>>>(p);
     FDB_CUDA(cudaGetLastError());
     return FDB_OK;
 }

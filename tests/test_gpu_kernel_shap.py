@@ -138,6 +138,27 @@ def test_logit_link(params):
     plan.close()
 
 
+@pytest.mark.parametrize("link", ["identity", "logit"])
+@pytest.mark.parametrize("n_bg", [100, 300])
+def test_factored_evaluator_clamped_inner_loops(params, monkeypatch, link, n_bg):
+    """K2f picks the clamp-free balanced inner loop when the background exponents of every coalition stay within
+    2^+-30 of their centre; FDB_FX_CLAMPED=1 forces the clamped quad / pair loops that wider backgrounds use."""
+    bg, X, f = _setup(params, n_bg, 9, seed=41)
+    Z, kw, _ = ks.sample_coalitions(30, 512, np.random.RandomState(41))
+    phi_ref, ey_ref, fnull = _oracle_rows(f, X, bg, [(Z, kw)], link=link)
+    plan = _plan(params, bg, [(Z, kw)], link=link)
+    tol = 2e-3 if link == "logit" else 1e-4
+    out = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("FDB_FX_CLAMPED", mode)
+        phi, ey, _ = _run(plan, X, FX)
+        np.testing.assert_allclose(ey, ey_ref, rtol=0, atol=2e-6)
+        assert np.all(np.abs(phi - phi_ref) <= tol * np.abs(phi_ref).max(1, keepdims=True) + 1e-9)
+        out[mode] = ey
+    assert np.abs(out["0"] - out["1"]).max() < 2e-6
+    plan.close()
+
+
 def test_many_rows_batches_and_determinism(params):
     """More rows than one evaluate->solve batch (32768): batches stitch together, reruns are bitwise equal."""
     bg, X, f = _setup(params, 20, 33000, seed=5)
