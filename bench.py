@@ -367,13 +367,13 @@ def bench_kernel_shap(args, torch, dist, device, rank, world, prm, sm_max_mhz):
     peak = 16.0 * sms * clock_hz
     # SFU roofline (north-star form: one exp per sigmoid against SFU exp throughput).  K2 issues 1.25 MUFU ops per
     # sigmoid (ex2 + a reciprocal shared by four); K2f issues 0.26 (reciprocal shared by four + one ex2 per 100), so it
-    # is bound by issue slots (4.5 per sigmoid), not by the SFU, and may exceed the one-exp-per-sigmoid line.
+    # is bound by issue slots (3.5 per sigmoid in the clamp-free loop), not by the SFU, and may exceed the one-exp-per-sigmoid line.
     out["roofline"] = {
         "bound": "sfu", "unit": "T sigmoid/s", "peak": peak / 1e12,
         "achieved": sig / (ms_tc * 1e-3) / 1e12, "frac": sig / (ms_tc * 1e-3) / peak, "kernel": "kshap_eval_tc_kernel (+K3 in the step)",
         "mufu_ops_per_sigmoid": 1.25, "mufu_frac": 1.25 * sig / (ms_tc * 1e-3) / peak,
         "factored": {"achieved": sig / (ms * 1e-3) / 1e12, "frac": sig / (ms * 1e-3) / peak, "kernel": "kshap_eval_fx_kernel (+K3 in the step)",
-                     "mufu_ops_per_sigmoid": 0.26, "issue_slots_per_sigmoid": 4.5},
+                     "mufu_ops_per_sigmoid": 0.26, "issue_slots_per_sigmoid": 3.5},
         "peak_source": f"nominal 16 MUFU/clk/SM x {sms} SMs x {clock_hz / 1e9:.3f} GHz = one exp per sigmoid (no measured SFU peak on file)",
     }
     if rank == 0 and world == 1:

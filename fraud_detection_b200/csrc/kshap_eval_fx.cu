@@ -25,7 +25,10 @@
 
 #include <math.h>
 
+#include <algorithm>
 #include <new>
+#include <utility>
+#include <vector>
 
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
@@ -76,10 +79,11 @@ __device__ __forceinline__ float fx_from_h16(uint16_t h, int fmt) {
 // MODE 0 / 1 (clamped): d = min(E u + 1, clamp), u = 2^t;  0 = four sigmoids per reciprocal, clamp 2^30 (a sigmoid
 //   moves by < 1e-9);  1 = logit link: two per reciprocal and clamp 2^62 so tiny sigmoids keep their relative accuracy.
 // MODE 2 (balanced, no clamp): sigma = 1 / (1 + E u) = b / (E a + b) with (a, b) = (u, 1) for u <= 1 and (1, 1/u)
-//   otherwise, so d = E a + b never exceeds 2^hs + 1 nor falls below 2^-hs (hs = the plan's largest half-spread of a
-//   coalition's background exponents).  With hs <= 30 the product of four d stays inside fp32 range: no min(), exact
-//   relative accuracy for tiny sigmoids (both links), 3.5 issue slots per sigmoid.  acc gathers sum 1/d; the caller
-//   multiplies by b once per (row, coalition).
+//   otherwise, so E <= d = E a + b <= E + 1 whatever the row: the product of the four d of a column quad is bounded by
+//   the E values alone.  The columns are ordered so that a quad mixes the four quarters of the logit-sorted
+//   background (fdb_kshap_build_factored) and kshap_build_E measures the bound; when every quad stays within
+//   2^+-114 there is no min() in the loop, tiny sigmoids keep their relative accuracy (both links) and a sigmoid
+//   costs 3.5 issue slots.  acc gathers sum 1/d; the caller multiplies by b once per (row, coalition).
 enum { kFxClampedQuads = 0, kFxClampedPairs = 1, kFxBalanced = 2 };
 
 template <int MODE>
@@ -350,7 +354,8 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
 // coalition, stored as E = 2^(e_b - o_m) in the [tile][chunk][128][cbs] layout the evaluator streams.
 __global__ void __launch_bounds__(128) kshap_build_E(const uint32_t* __restrict__ bits, const double* __restrict__ Pd,
                                                      int n_bg, int n_chunks, float* __restrict__ E,
-                                                     float* __restrict__ eoff, float* __restrict__ half_spread) {
+                                                     float* __restrict__ eoff, float* __restrict__ half_spread,
+                                                     float* __restrict__ quad_logsum) {
     __shared__ double s_min[128], s_max[128];
     const int m = blockIdx.x, tid = threadIdx.x;
     const uint32_t b = bits[m];
@@ -381,6 +386,27 @@ __global__ void __launch_bounds__(128) kshap_build_E(const uint32_t* __restrict_
         eoff[m] = (float)centre;
         half_spread[m] = (float)(0.5 * (s_max[0] - s_min[0]));
     }
+    // The clamp-free inner loop multiplies the four d = E a + b (a, b <= 1, one of them 1) of a column quad:
+    // prod <= 2^(4 + sum max(lev, 0)) and prod >= 2^(-sum max(-lev, 0)) with lev = log2 E.  Record the worst quad.
+    const int full_cols = n_bg & ~3;
+    double qs = 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int col = tid + i * 128;
+        const double lev = col < full_cols ? ev[i] - centre : 0.0;
+        double up = fmax(lev, 0.0), dn = fmax(-lev, 0.0);
+        up += __shfl_xor_sync(0xffffffffu, up, 1); dn += __shfl_xor_sync(0xffffffffu, dn, 1);
+        up += __shfl_xor_sync(0xffffffffu, up, 2); dn += __shfl_xor_sync(0xffffffffu, dn, 2);
+        qs = fmax(qs, fmax(up, dn));
+    }
+    __syncthreads();
+    s_max[tid] = qs;
+    __syncthreads();
+    for (int o = 64; o > 0; o >>= 1) {
+        if (tid < o) s_max[tid] = fmax(s_max[tid], s_max[tid + o]);
+        __syncthreads();
+    }
+    if (tid == 0) quad_logsum[m] = (float)s_max[0];
     const int cbs_last = (fx_cbw(n_bg, n_chunks - 1) + 3) & ~3;
     const size_t tile_floats = (size_t)128 * (128 * (n_chunks - 1) + cbs_last);
     float* et = E + (size_t)(m >> 7) * tile_floats;
@@ -406,10 +432,24 @@ int fdb_kshap_build_factored(fdb_kshap_plan* pl, const double* bg_host) {
     const size_t total = tile_floats * (pl->m_pad / 128);
     double* h = new (std::nothrow) double[(size_t)pl->n_bg * 32];
     FDB_REQUIRE(h != nullptr, FDB_ERR_NOMEM, "out of host memory");
+    // Column order of E (the mean over the background does not care): rows sorted by their logit are dealt out so
+    // that every quad of 4 consecutive columns takes one row from each quarter of the sorted order.  A quad then
+    // never holds four large (or four small) exponents at once, which keeps the product of its four denominators
+    // inside fp32 range without clamps (kshap_build_E measures the actual bound).  The n_bg % 4 last rows form the tail.
+    std::vector<std::pair<double, int>> order(pl->n_bg);
     for (int b = 0; b < pl->n_bg; ++b) {
-        for (int k = 0; k < 32; ++k) h[(size_t)b * 32 + k] = 0.0;
-        for (int k = 0; k < FDB_F; ++k) h[(size_t)b * 32 + k] = pl->coef[k] * bg_host[(size_t)b * FDB_F + k];
-        h[(size_t)b * 32 + 30] = pl->intercept;
+        double z = pl->intercept;
+        for (int k = 0; k < FDB_F; ++k) z += pl->coef[k] * bg_host[(size_t)b * FDB_F + k];
+        order[b] = {z, b};
+    }
+    std::sort(order.begin(), order.end());
+    const int n_quads = pl->n_bg / 4;
+    for (int i = 0; i < pl->n_bg; ++i) {
+        const int col = i < 4 * n_quads ? 4 * (i % n_quads) + i / n_quads : i;
+        const int b = order[i].second;
+        for (int k = 0; k < 32; ++k) h[(size_t)col * 32 + k] = 0.0;
+        for (int k = 0; k < FDB_F; ++k) h[(size_t)col * 32 + k] = pl->coef[k] * bg_host[(size_t)b * FDB_F + k];
+        h[(size_t)col * 32 + 30] = pl->intercept;
     }
     double* dP = nullptr;
     cudaError_t e = cudaMalloc((void**)&dP, (size_t)pl->n_bg * 32 * 8);
@@ -419,21 +459,25 @@ int fdb_kshap_build_factored(fdb_kshap_plan* pl, const double* bg_host) {
     if (e == cudaSuccess) e = cudaMemset(pl->d_E, 0, total * 4);
     if (e == cudaSuccess) e = cudaMalloc((void**)&pl->d_eoff, (size_t)pl->m_pad * 4);
     float* d_spread = nullptr;
-    if (e == cudaSuccess) e = cudaMalloc((void**)&d_spread, (size_t)pl->m_pad * 4);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&d_spread, (size_t)pl->m_pad * 2 * 4);
     if (e == cudaSuccess) {
-        kshap_build_E<<<pl->m_pad, 128>>>(pl->d_bits, dP, pl->n_bg, n_chunks, pl->d_E, pl->d_eoff, d_spread);
+        kshap_build_E<<<pl->m_pad, 128>>>(pl->d_bits, dP, pl->n_bg, n_chunks, pl->d_E, pl->d_eoff, d_spread, d_spread + pl->m_pad);
         e = cudaGetLastError();
     }
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
     // The factorisation needs every coalition's background exponents within +-100 of their centre (fp32 range of
     // E and u).  Backgrounds that spread the logit further (outliers of ~+-140 in logit) keep the general evaluator.
-    float worst = 0.f;
+    float worst = 0.f, worst_quad = 0.f;
     if (e == cudaSuccess) {
-        float* hs = new (std::nothrow) float[pl->m_pad];
-        if (hs && (e = cudaMemcpy(hs, d_spread, (size_t)pl->m_pad * 4, cudaMemcpyDeviceToHost)) == cudaSuccess)
-            for (int m = 0; m < pl->m_pad; ++m) worst = fmaxf(worst, hs[m]);
+        float* hs = new (std::nothrow) float[(size_t)pl->m_pad * 2];
+        if (hs && (e = cudaMemcpy(hs, d_spread, (size_t)pl->m_pad * 2 * 4, cudaMemcpyDeviceToHost)) == cudaSuccess)
+            for (int m = 0; m < pl->m_pad; ++m) {
+                worst = fmaxf(worst, hs[m]);
+                worst_quad = fmaxf(worst_quad, hs[pl->m_pad + m]);
+            }
         delete[] hs;
     }
+    pl->fx_quad_logsum = worst_quad;
     cudaFree(d_spread);
     cudaFree(dP);
     FDB_CUDA(e);
@@ -468,9 +512,10 @@ int fdb_kshap_launch_eval_fx(fdb_kshap_plan* pl, cudaStream_t st, const float* x
     const int64_t n_units = (int64_t)((n_rows + 127) / 128) * p.tiles;
     int64_t grid = n_units < pl->ctx->sm_count ? n_units : pl->ctx->sm_count;
     if (grid < 1) grid = 1;
-    // balanced (clamp-free) inner loop whenever every coalition's background exponents stay within +-30 of their centre
+    // balanced (clamp-free) inner loop whenever the product of the four denominators of every column quad is
+    // guaranteed to stay within 2^+-114 (kshap_build_E)
     const char* force = getenv("FDB_FX_CLAMPED");
-    const bool balanced = pl->fx_half_spread <= 30.f && !(force && atoi(force) != 0);
+    const bool balanced = pl->fx_quad_logsum <= 110.f && pl->fx_half_spread <= 100.f && !(force && atoi(force) != 0);
     if (balanced) kshap_eval_fx_kernel<kFxBalanced><<<(int)grid, kFxThreads, smem, st>>>(p);
     else if (pl->link == 1) kshap_eval_fx_kernel<kFxClampedPairs><<<(int)grid, kFxThreads, smem, st>>>(p);
     else kshap_eval_fx_kernel<kFxClampedQuads><<<(int)grid, kFxThreads, smem, st>>>(p);

@@ -36,6 +36,7 @@ struct fdb_kshap_plan {
     double* d_abs = nullptr;
     float* d_E = nullptr;              // factored evaluator (single set): [tile][chunk][128][cbs] 2^(e - o_m)
     float* d_eoff = nullptr;           // [m_pad] exponent centres o_m
+    float fx_quad_logsum = 0.f;        // worst sum over a column quad of |log2 E| on one side of 0 (bounds the product of four denominators)
     float fx_half_spread = 0.f;        // largest half-spread (log2) of a coalition's background exponents around o_m
     float* d_xw = nullptr;             // [m_pad][32] kw_m * x_mj
     double* d_gz = nullptr;            // [S][30][32] Z'WZ, built on demand for l1_reg = num_features(k)
