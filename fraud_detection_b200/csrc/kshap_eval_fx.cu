@@ -313,26 +313,31 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
             if (row < p.n_rows) {
                 // fused first half of the least-squares solve: this thread's share of X'W y,
                 //   g[j] += (kw_m x_mj) * (link(ey[r][m]) - link(fnull))   over its 32 coalitions
-                float gq[32];
+                // (two passes of 16 features each: 16 sums + 32 y + a batch of loads in flight fit the register budget,
+                //  so the warp-uniform xw loads are issued well ahead of the FMAs that consume them)
 #pragma unroll
-                for (int jj = 0; jj < 32; ++jj) gq[jj] = 0.f;
+                for (int mi = 0; mi < 32; ++mi) part[mi] *= p.inv_bg;
                 const float4* xwp = reinterpret_cast<const float4*>(p.xw + (size_t)(tile * 128 + cg * 32) * 32);
-#pragma unroll
-                for (int mi = 0; mi < 32; ++mi) {
-                    part[mi] *= p.inv_bg;
-                    const float yv = fdb_kshap_link(part[mi], p.link) - p.lnull;
-#pragma unroll
-                    for (int v4 = 0; v4 < 8; ++v4) {
-                        const float4 xv = __ldg(xwp + mi * 8 + v4);          // same address in every lane
-                        gq[4 * v4] = fmaf(xv.x, yv, gq[4 * v4]);
-                        gq[4 * v4 + 1] = fmaf(xv.y, yv, gq[4 * v4 + 1]);
-                        gq[4 * v4 + 2] = fmaf(xv.z, yv, gq[4 * v4 + 2]);
-                        gq[4 * v4 + 3] = fmaf(xv.w, yv, gq[4 * v4 + 3]);
-                    }
-                }
                 float4* gdst = reinterpret_cast<float4*>(p.gpart + ((size_t)row * (p.m_pad / 32) + tile * 4 + cg) * 32);
 #pragma unroll
-                for (int v4 = 0; v4 < 8; ++v4) gdst[v4] = make_float4(gq[4 * v4], gq[4 * v4 + 1], gq[4 * v4 + 2], gq[4 * v4 + 3]);
+                for (int half = 0; half < 2; ++half) {
+                    float gq[16];
+#pragma unroll
+                    for (int jj = 0; jj < 16; ++jj) gq[jj] = 0.f;
+#pragma unroll
+                    for (int mi = 0; mi < 32; ++mi) {
+                        const float yv = fdb_kshap_link(part[mi], p.link) - p.lnull;
+                        const float4 x0 = __ldg(xwp + mi * 8 + half * 4), x1 = __ldg(xwp + mi * 8 + half * 4 + 1);
+                        const float4 x2 = __ldg(xwp + mi * 8 + half * 4 + 2), x3 = __ldg(xwp + mi * 8 + half * 4 + 3);
+                        gq[0] = fmaf(x0.x, yv, gq[0]); gq[1] = fmaf(x0.y, yv, gq[1]); gq[2] = fmaf(x0.z, yv, gq[2]); gq[3] = fmaf(x0.w, yv, gq[3]);
+                        gq[4] = fmaf(x1.x, yv, gq[4]); gq[5] = fmaf(x1.y, yv, gq[5]); gq[6] = fmaf(x1.z, yv, gq[6]); gq[7] = fmaf(x1.w, yv, gq[7]);
+                        gq[8] = fmaf(x2.x, yv, gq[8]); gq[9] = fmaf(x2.y, yv, gq[9]); gq[10] = fmaf(x2.z, yv, gq[10]); gq[11] = fmaf(x2.w, yv, gq[11]);
+                        gq[12] = fmaf(x3.x, yv, gq[12]); gq[13] = fmaf(x3.y, yv, gq[13]); gq[14] = fmaf(x3.z, yv, gq[14]); gq[15] = fmaf(x3.w, yv, gq[15]);
+                    }
+#pragma unroll
+                    for (int v4 = 0; v4 < 4; ++v4)
+                        gdst[half * 4 + v4] = make_float4(gq[4 * v4], gq[4 * v4 + 1], gq[4 * v4 + 2], gq[4 * v4 + 3]);
+                }
                 if (p.ey != nullptr) {
                     float4* dst = reinterpret_cast<float4*>(p.ey + (size_t)row * p.m_pad + tile * 128 + cg * 32);
 #pragma unroll
