@@ -13,7 +13,7 @@ import threading
 import numpy as np
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG_DIR, "libfdb200.so")
+LIB_PATH = os.environ.get("FDB_LIB_PATH") or os.path.join(PKG_DIR, "libfdb200.so")   # override: A/B builds (tools/variant_build.py)
 
 F32, F64 = 0, 1
 N_FEATURES = 30

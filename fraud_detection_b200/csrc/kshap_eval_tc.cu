@@ -22,8 +22,10 @@
 //   warp g           producer : writes Bq for the item's row, bulk-copies (TMA, UBLKCP) the A tile image
 //   warp 4+g         MMA      : one lane issues tcgen05.mma / tcgen05.commit
 //   warps 8+4g..11+4g epilogue: TMEM lane quarter (warp % 4), 32 coalitions per warp
-// The B operand stays resident in shared memory for the whole kernel.  Backgrounds wider than
-// 128 rows are processed in column chunks that reuse the pipeline's TMEM columns.
+// The B operand stays resident in shared memory for the whole kernel.  The background is walked in chunks of 64
+// columns that alternate between the two halves of the pipeline's TMEM columns, so the MMA of chunk c + 1
+// (or of the next item) runs while the epilogue reads chunk c; quads of the last group that lie entirely
+// beyond the background are skipped.
 
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
@@ -38,7 +40,8 @@ constexpr int kThreadsTc = (2 * kPipes + 4 * kPipes) * 32;   // 768
 constexpr int kATileBytes = 128 * 32 * 2;     // 8192
 constexpr int kBqBytes = 3 * 512;             // 3 splits x (4 k-chunks x 8 identical rows x 16 B)
 constexpr int kAStages = 2;
-constexpr int kPipeCols = 128;                // TMEM columns per pipeline
+constexpr int kPipeCols = 128;                // TMEM columns per pipeline ...
+constexpr int kBufCols = 64;                  // ... used as two accumulator buffers: the MMA of background chunk c + 1 runs while chunk c is read
 constexpr uint32_t kLbo = 128;                // K-direction core-matrix stride (bytes)
 constexpr uint32_t kSbo = 512;                // 8-row-group stride (bytes)
 
@@ -60,8 +63,8 @@ struct TcParams {
 struct PipeBars {
     uint64_t a_full[kAStages];
     uint64_t a_empty[kAStages];
-    uint64_t t_full;
-    uint64_t t_empty;
+    uint64_t t_full[2];
+    uint64_t t_empty[2];
 };
 
 struct TcBars {
@@ -129,6 +132,7 @@ __device__ __forceinline__ float sigmoid_sum16(const uint32_t (&r)[16], int nval
     float sum = 0.f;
 #pragma unroll
     for (int q = 0; q < 16; q += 4) {
+        if (MASKED && q >= nvalid) break;              // quads that lie entirely beyond the background cost nothing
         float d[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -147,7 +151,7 @@ __device__ __forceinline__ float sigmoid_sum16(const uint32_t (&r)[16], int nval
             sum = fmaf(num, ptx::rcp_approx(p01 * p23), sum);
         }
     }
-    return MASKED ? sum - (float)(16 - nvalid) * kFloor : sum;   // masked columns sit at the clamp; take them out again
+    return MASKED ? sum - (float)(((nvalid + 3) & ~3) - nvalid) * kFloor : sum;   // masked columns of the last quad sit at the clamp; take them out again
 }
 
 template <bool WIDE>
@@ -176,8 +180,10 @@ __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcPa
                 ptx::mbar_init(&bars->pipe[g].a_full[s], 1);
                 ptx::mbar_init(&bars->pipe[g].a_empty[s], 1);
             }
-            ptx::mbar_init(&bars->pipe[g].t_full, 1);
-            ptx::mbar_init(&bars->pipe[g].t_empty, 4);
+            for (int b = 0; b < 2; ++b) {
+                ptx::mbar_init(&bars->pipe[g].t_full[b], 1);
+                ptx::mbar_init(&bars->pipe[g].t_empty[b], 4);
+            }
         }
         ptx::mbar_init(&bars->b_full, 1);
         ptx::mbar_fence_init();
@@ -247,7 +253,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcPa
             const uint32_t a0 = ptx::smem_u32(sA + (size_t)g * kAStages * kATileBytes);
             const uint32_t q0 = ptx::smem_u32(sBq + (size_t)g * kAStages * kBqBytes);
             const uint32_t b0 = ptx::smem_u32(sB);
-            const uint32_t d = tmem_base + g * kPipeCols;
+            const uint32_t d0 = tmem_base + g * kPipeCols;
             int k = 0;
             uint32_t job = 0;
             for (int64_t it = (int64_t)blockIdx.x * kPipes + g; it < n_items; it += stride, ++k) {
@@ -258,7 +264,8 @@ __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcPa
                 const uint32_t a_addr = a0 + s * kATileBytes;
                 const uint32_t q_addr = q0 + s * kBqBytes;
                 for (int c = 0; c < p.n_chunks; ++c, ++job) {
-                    mbar_wait_relaxed(&pb.t_empty, (job & 1) ^ 1);
+                    const uint32_t buf = job & 1, d = d0 + buf * kBufCols;
+                    mbar_wait_relaxed(&pb.t_empty[buf], ((job >> 1) & 1) ^ 1);
                     ptx::tc_fence_after();
                     const int col0 = c * p.chunk_cols;
                     const int nc = (p.nb_pad - col0) < p.chunk_cols ? (p.nb_pad - col0) : p.chunk_cols;
@@ -284,7 +291,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcPa
                             ptx::mma_f16(d, ad, qd, idesc, true);
                         }
                     }
-                    ptx::mma_commit(&pb.t_full);
+                    ptx::mma_commit(&pb.t_full[buf]);
                 }
                 ptx::mma_commit(&pb.a_empty[s]);
             }
@@ -295,14 +302,15 @@ __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcPa
         const int g = (warp - 2 * kPipes) >> 2;
         const int qd = warp & 3;                     // TMEM lane quarter this warp may read
         PipeBars& pb = bars->pipe[g];
-        const uint32_t ta = tmem_base + ((uint32_t)(qd * 32) << 16) + g * kPipeCols;
+        const uint32_t ta0 = tmem_base + ((uint32_t)(qd * 32) << 16) + g * kPipeCols;
         uint32_t job = 0;
         for (int64_t it = (int64_t)blockIdx.x * kPipes + g; it < n_items; it += stride) {
             const int row = (int)(it / p.tiles);
             const int tile = (int)(it % p.tiles);
             float acc = 0.f;
             for (int c = 0; c < p.n_chunks; ++c, ++job) {
-                ptx::mbar_wait(&pb.t_full, job & 1);
+                const uint32_t buf = job & 1, ta = ta0 + buf * kBufCols;
+                ptx::mbar_wait(&pb.t_full[buf], (job >> 1) & 1);
                 ptx::tc_fence_after();
                 int valid = p.n_bg - c * p.chunk_cols;
                 if (valid > p.chunk_cols) valid = p.chunk_cols;
@@ -314,12 +322,12 @@ __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcPa
                 for (int gi = 0; gi < ngroups; gi += 2) {
                     ptx::tmem_ld_wait();
                     if (gi + 1 < ngroups) ptx::tmem_ld16(ta + (gi + 1) * 16, rb);
-                    else release_tmem(&pb.t_empty, lane);
+                    else release_tmem(&pb.t_empty[buf], lane);
                     acc += p.wide ? sigmoid_group<true>(ra, valid - gi * 16) : sigmoid_group<false>(ra, valid - gi * 16);
                     if (gi + 1 < ngroups) {
                         ptx::tmem_ld_wait();
                         if (gi + 2 < ngroups) ptx::tmem_ld16(ta + (gi + 2) * 16, ra);
-                        else release_tmem(&pb.t_empty, lane);
+                        else release_tmem(&pb.t_empty[buf], lane);
                         acc += p.wide ? sigmoid_group<true>(rb, valid - (gi + 1) * 16) : sigmoid_group<false>(rb, valid - (gi + 1) * 16);
                     }
                 }
@@ -344,8 +352,8 @@ int fdb_kshap_launch_eval_tc(fdb_kshap_plan* pl, cudaStream_t st, const float* x
     p.x = x; p.set_idx = set_idx; p.aimg = pl->d_aimg; p.bimg = pl->d_bimg; p.wq = pl->d_wq; p.ey = ey;
     p.row_offset = row_offset; p.n_rows = n_rows; p.n_sets = pl->n_sets; p.tiles = pl->m_pad / 128; p.m_pad = pl->m_pad;
     p.n_bg = pl->n_bg; p.nb_pad = pl->nb_pad; p.nsplit = pl->nsplit; p.fmt = pl->fmt;
-    p.n_chunks = (pl->nb_pad + kPipeCols - 1) / kPipeCols;
-    p.chunk_cols = (((pl->nb_pad + p.n_chunks - 1) / p.n_chunks) + 15) & ~15;
+    p.n_chunks = (pl->nb_pad + kBufCols - 1) / kBufCols;
+    p.chunk_cols = kBufCols;
     p.inv_bg = 1.0f / (float)pl->n_bg;
     p.wide = pl->link == 1;
     const size_t smem = (size_t)pl->nsplit * pl->nb_pad * 64 + kPipes * kAStages * (kATileBytes + kBqBytes) + sizeof(TcBars) + 64;
