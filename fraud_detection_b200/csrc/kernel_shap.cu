@@ -285,8 +285,10 @@ void fdb_kshap_split(double v, int fmt, int n, uint16_t* out) {
 static int refresh_set_products(fdb_kshap_plan* p) {
     const size_t SM = (size_t)p->n_sets * p->m_pad;
     const uint16_t one = p->fmt == 0 ? 0x3C00 : 0x3F80;
-    kshap_expand_masks<<<(unsigned)((SM + 255) / 256), 256>>>(p->d_bits, p->d_aimg, (int64_t)SM, one);
-    FDB_CUDA(cudaGetLastError());
+    if (p->d_aimg) {      // single-set plans only: the tile images the factored evaluator streams by TMA
+        kshap_expand_masks<<<(unsigned)((SM + 255) / 256), 256>>>(p->d_bits, p->d_aimg, (int64_t)SM, one);
+        FDB_CUDA(cudaGetLastError());
+    }
     kshap_wls_prepare<<<p->n_sets, 32>>>(p->d_bits, p->d_kw, p->m_pad, p->d_ainv, p->d_c2, p->d_status, p->varying);
     FDB_CUDA(cudaGetLastError());
     FDB_CUDA(cudaDeviceSynchronize());
@@ -392,7 +394,7 @@ static int plan_create_impl(fdb_ctx* ctx, const double* coef, double intercept, 
         TRY(cudaMalloc((void**)&p->d_P, P.size() * 4));
         TRY(cudaMalloc((void**)&p->d_wq, 32 * 4));
         TRY(cudaMalloc((void**)&p->d_bimg, bimg.size() * 2));
-        TRY(cudaMalloc((void**)&p->d_aimg, SM * 32 * 2));
+        if (n_sets == 1) TRY(cudaMalloc((void**)&p->d_aimg, SM * 32 * 2));
         TRY(cudaMalloc((void**)&p->d_ainv, (size_t)n_sets * kNV * 32 * 4));
         TRY(cudaMalloc((void**)&p->d_c2, (size_t)n_sets * 32 * 4));
         TRY(cudaMalloc((void**)&p->d_status, (size_t)n_sets * 4));

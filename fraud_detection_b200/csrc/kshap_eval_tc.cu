@@ -19,7 +19,9 @@
 //
 // CTA = 24 warps, persistent, four independent pipelines g = 0..3 (each owns 128 TMEM columns), so every
 // SM sub-partition always has four epilogue warps to hide SFU and TMEM latency:
-//   warp g           producer : writes Bq for the item's row, bulk-copies (TMA, UBLKCP) the A tile image
+//   warp g           producer : writes Bq for the item's row and expands the item's 128 coalition words (512 B from
+//                               global memory) into the 8 KB A tile in shared memory - no 64-byte-per-coalition image in
+//                               HBM; single-set plans keep ready-made tile images (K2f streams them) and bulk-copy them (TMA)
 //   warp 4+g         MMA      : one lane issues tcgen05.mma / tcgen05.commit
 //   warps 8+4g..11+4g epilogue: TMEM lane quarter (warp % 4), 32 coalitions per warp
 // The B operand stays resident in shared memory for the whole kernel.  The background is walked in chunks of 64
@@ -48,7 +50,8 @@ constexpr uint32_t kSbo = 512;                // 8-row-group stride (bytes)
 struct TcParams {
     const float* x;
     const int32_t* set_idx;
-    const uint16_t* aimg;
+    const uint32_t* bits;                      // [S][m_pad] coalition words; the A tile is expanded from them in smem ...
+    const uint16_t* aimg;                      // ... unless the plan holds ready-made tile images (single-set plans): TMA
     const uint16_t* bimg;
     const float* wq;
     float* ey;
@@ -160,6 +163,7 @@ __device__ __forceinline__ float sigmoid_group(const uint32_t (&r)[16], int nval
 }
 
 // smem carve-up (dynamic): [B image][A stages x pipes][Bq stages x pipes][barriers]
+template <bool FROM_BITS>
 __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     const uint32_t b_bytes = (uint32_t)p.nsplit * p.nb_pad * 64;
@@ -229,20 +233,52 @@ __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcPa
                 h[j] = to_h16(rem, p.fmt);
                 rem -= from_h16(h[j], p.fmt);
             }
+            // the item's 128 coalition words (lane l: rows l, l + 32, l + 64, l + 96), fetched before the stage is waited for
+            const uint32_t* mb = p.bits + ((size_t)set * p.m_pad + (size_t)tile * 128);
+            uint32_t mw[4];
+            if (FROM_BITS) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) mw[j] = __ldg(mb + j * 32 + lane);
+            }
             mbar_wait_relaxed(&pb.a_empty[s], ph ^ 1);
             unsigned char* bq = sBq + (size_t)(g * kAStages + s) * kBqBytes + (lane >> 3) * 128 + (lane & 7) * 2;
 #pragma unroll
             for (int j = 0; j < 3; ++j)
 #pragma unroll
                 for (int rr = 0; rr < 8; ++rr) *reinterpret_cast<uint16_t*>(bq + j * 512 + rr * 16) = h[j];
+            // A tile (128 coalitions x 32 k, canonical K-major no-swizzle layout) straight from the coalition words:
+            //   a[m][k] = 1 - z_mk (k < 30), a[m][30] = 1 (bias lane), a[m][31] = 0.  16 B per (row, k-chunk of 8);
+            //   a quarter warp writes 128 contiguous bytes -> conflict-free STS.128.  64 B of operand per 4 B read.
+            if (!FROM_BITS) {                 // ready-made tile image: one bulk copy (TMA, UBLKCP)
+                ptx::fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    ptx::mbar_arrive_expect_tx(&pb.a_full[s], kATileBytes);
+                    ptx::bulk_g2s(sA + (size_t)(g * kAStages + s) * kATileBytes,
+                                  reinterpret_cast<const unsigned char*>(p.aimg) + ((size_t)set * p.tiles + tile) * kATileBytes,
+                                  kATileBytes, &pb.a_full[s]);
+                }
+                continue;
+            }
+            unsigned char* at = sA + (size_t)(g * kAStages + s) * kATileBytes + (lane >> 3) * 512 + (lane & 7) * 16;
+            const uint32_t one = p.fmt == 0 ? 0x3C00u : 0x3F80u;      // 1.0 in f16 / bf16
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t abar = (~mw[j] & 0x3FFFFFFFu) | (1u << 30);
+#pragma unroll
+                for (int kc = 0; kc < 4; ++kc) {
+                    uint32_t w4[4];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const uint32_t two = (abar >> (kc * 8 + q * 2)) & 3u;          // two adjacent k
+                        w4[q] = ((two & 1u) | ((two & 2u) << 15)) * one;
+                    }
+                    *reinterpret_cast<uint4*>(at + j * 2048 + kc * 128) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+                }
+            }
             ptx::fence_proxy_async_smem();
             __syncwarp();
-            if (lane == 0) {
-                ptx::mbar_arrive_expect_tx(&pb.a_full[s], kATileBytes);
-                ptx::bulk_g2s(sA + (size_t)(g * kAStages + s) * kATileBytes,
-                              reinterpret_cast<const unsigned char*>(p.aimg) + ((size_t)set * p.tiles + tile) * kATileBytes,
-                              kATileBytes, &pb.a_full[s]);
-            }
+            if (lane == 0) ptx::mbar_arrive(&pb.a_full[s]);
         }
     } else if (warp < 2 * kPipes) {
         // =================================================================== MMA issuer of pipeline g
@@ -349,7 +385,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcPa
 int fdb_kshap_launch_eval_tc(fdb_kshap_plan* pl, cudaStream_t st, const float* x, int64_t row_offset, int n_rows,
                              const int32_t* set_idx, float* ey) {
     TcParams p;
-    p.x = x; p.set_idx = set_idx; p.aimg = pl->d_aimg; p.bimg = pl->d_bimg; p.wq = pl->d_wq; p.ey = ey;
+    p.x = x; p.set_idx = set_idx; p.bits = pl->d_bits; p.aimg = pl->d_aimg; p.bimg = pl->d_bimg; p.wq = pl->d_wq; p.ey = ey;
     p.row_offset = row_offset; p.n_rows = n_rows; p.n_sets = pl->n_sets; p.tiles = pl->m_pad / 128; p.m_pad = pl->m_pad;
     p.n_bg = pl->n_bg; p.nb_pad = pl->nb_pad; p.nsplit = pl->nsplit; p.fmt = pl->fmt;
     p.n_chunks = (pl->nb_pad + kBufCols - 1) / kBufCols;
@@ -361,14 +397,16 @@ int fdb_kshap_launch_eval_tc(fdb_kshap_plan* pl, cudaStream_t st, const float* x
                 pl->n_bg, pl->nsplit, smem);
     static size_t configured[FDB_MAX_DEVICES] = {};        // function attributes are per device
     if (smem > configured[pl->ctx->device]) {
-        FDB_CUDA(cudaFuncSetAttribute(kshap_eval_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        FDB_CUDA(cudaFuncSetAttribute(kshap_eval_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        FDB_CUDA(cudaFuncSetAttribute(kshap_eval_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured[pl->ctx->device] = smem;
     }
     const int64_t n_items = (int64_t)n_rows * p.tiles;
     int64_t grid = (n_items + kPipes - 1) / kPipes;
     if (grid > pl->ctx->sm_count) grid = pl->ctx->sm_count;
     if (grid < 1) grid = 1;
-    kshap_eval_tc_kernel<<<(int)grid, kThreadsTc, smem, st>>>(p);
+    if (pl->d_aimg != nullptr) kshap_eval_tc_kernel<false><<<(int)grid, kThreadsTc, smem, st>>>(p);
+    else kshap_eval_tc_kernel<true><<<(int)grid, kThreadsTc, smem, st>>>(p);
     FDB_CUDA(cudaGetLastError());
     return FDB_OK;
 }

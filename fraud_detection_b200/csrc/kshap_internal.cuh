@@ -25,7 +25,7 @@ struct fdb_kshap_plan {
     float* d_P = nullptr;              // [B][32] w_k * bg_bk, column 30 = intercept (SIMT evaluator)
     float* d_wq = nullptr;             // [32] w_k
     uint16_t* d_bimg = nullptr;        // B operand, smem image: [split][nb_pad/8][4][8][8]
-    uint16_t* d_aimg = nullptr;        // A operand tiles, smem image: [S][m_pad/128][16][4][8][8]
+    uint16_t* d_aimg = nullptr;        // single-set plans: coalition tile images [m_pad/128][16][4][8][8] for K2f (K2 expands d_bits itself)
     float* d_ainv = nullptr;           // [S][29][32] (X'WX)^-1
     float* d_c2 = nullptr;             // [S][32]     X'W z29
     int* d_status = nullptr;           // [S] 1 = singular
