@@ -58,12 +58,12 @@ __global__ void kshap_expand_masks(const uint32_t* __restrict__ bits, uint16_t* 
 
 // ---------------------------------------------------------------------------------------
 // Per mask set: A = X'WX (29x29, f64), c2 = X'W z29, then A^-1 by Gauss-Jordan (SPD, no pivoting).
-// One warp per set; lane i owns row i of A while accumulating.
+// One warp per set.  Lane j owns column j of [A | I] in registers (A is symmetric, so the row it accumulated is that
+// column): step k needs the pivot row - element (k, j) is already in lane j - and the multipliers A[i][k], which
+// are lane k's column and travel by shuffle.  No shared memory, no barriers.
 __global__ void __launch_bounds__(32) kshap_wls_prepare(const uint32_t* __restrict__ bits, const float* __restrict__ kw,
                                                         int m_pad, float* __restrict__ ainv, float* __restrict__ c2out,
                                                         int* __restrict__ status, uint32_t varying) {
-    __shared__ double A[kNV][kNV + 1];
-    __shared__ double I[kNV][kNV + 1];
     const int s = blockIdx.x;
     const int lane = threadIdx.x;
     const uint32_t* sb = bits + (size_t)s * m_pad;
@@ -74,44 +74,36 @@ __global__ void __launch_bounds__(32) kshap_wls_prepare(const uint32_t* __restri
     fdb_kshap_weighted_gram_row<kNV>(
         sb, sk, m_pad, lane, [](uint32_t b) { return ((b >> 29) & 1u) ? ~b : b; },
         [](uint32_t b) { return ((b >> 29) & 1u) != 0u; }, a, c2);
-    c2 = -c2;
-    if (lane < kNV) {
+    c2out[(size_t)s * 32 + lane] = lane < kNV ? (float)(-c2) : 0.f;
+    double inv[kNV];
 #pragma unroll
-        for (int j = 0; j < kNV; ++j) {
-            A[lane][j] = a[j];
-            I[lane][j] = (j == lane) ? 1.0 : 0.0;
-        }
-        // a feature outside `varying` has an all-zero column (its bits follow bit 29): pin its unknown at 0
-        if (!((varying >> lane) & 1u)) A[lane][lane] = 1.0;
-        c2out[(size_t)s * 32 + lane] = (float)c2;
-    } else {
-        c2out[(size_t)s * 32 + lane] = 0.f;
+    for (int i = 0; i < kNV; ++i) {
+        inv[i] = (i == lane) ? 1.0 : 0.0;
+        // a feature outside `varying` has an all-zero row and column (its bits follow bit 29): pin its unknown at 0
+        if (i == lane && !((varying >> lane) & 1u)) a[i] = 1.0;
+        if (lane >= kNV) a[i] = 0.0;
     }
-    __syncwarp();
     bool singular = false;
+#pragma unroll
     for (int k = 0; k < kNV; ++k) {
-        const double pk = A[k][k];
+        const double pk = __shfl_sync(0xffffffffu, a[k], k);          // A[k][k]
         if (!(fabs(pk) > 1e-300)) { singular = true; break; }
-        const double inv = 1.0 / pk;
-        __syncwarp();
-        if (lane < kNV) {
-            A[k][lane] *= inv;
-            I[k][lane] *= inv;
-        }
-        __syncwarp();
+        const double r = 1.0 / pk;
+        const double ak = a[k] * r, ik = inv[k] * r;                    // pivot row, scaled: elements (k, lane)
+#pragma unroll
         for (int i = 0; i < kNV; ++i) {
-            if (i == k) continue;
-            const double f = A[i][k];
-            __syncwarp();
-            if (lane < kNV) {
-                A[i][lane] -= f * A[k][lane];
-                I[i][lane] -= f * I[k][lane];
+            const double f = __shfl_sync(0xffffffffu, a[i], k);       // A[i][k] before this step
+            if (i != k) {
+                a[i] = fma(-f, ak, a[i]);
+                inv[i] = fma(-f, ik, inv[i]);
             }
         }
-        __syncwarp();
+        a[k] = ak;
+        inv[k] = ik;
     }
+#pragma unroll
     for (int i = 0; i < kNV; ++i)
-        ainv[((size_t)s * kNV + i) * 32 + lane] = (lane < kNV && !singular) ? (float)I[i][lane] : 0.f;
+        ainv[((size_t)s * kNV + i) * 32 + lane] = (lane < kNV && !singular) ? (float)inv[i] : 0.f;
     if (lane == 0) status[s] = singular ? 1 : 0;
 }
 
