@@ -28,7 +28,6 @@
 namespace {
 
 constexpr int kMaxSizes = 16;
-// hash-set slots: >= 4 x the number of random primary draws (nsamples / 2), so probes stay short
 
 struct SamplerParams {
     uint32_t* bits;          // [S][m_pad]
@@ -46,21 +45,20 @@ struct SamplerParams {
 };
 
 // Shared memory per set: the set itself (coalition words + draw counts) and an open-addressing hash table of slot
-// indices (0xFFFF = empty; the key of an entry is s_bits[slot]).  24 KB for nsamples <= 2048, 48 KB up to 4096.
+// indices (0xFFFF = empty; the key of an entry is s_bits[slot]; at most nsamples / 2 entries, load <= 1/2).
+// 16 KB for nsamples <= 2048 (14 sets in flight per SM), 32 KB up to 4096.
 template <int kHashSlots, int kHashShift, int kMaxSamples>
 __global__ void __launch_bounds__(32) kshap_sample_sets(const SamplerParams p) {
     __shared__ uint32_t s_bits[kMaxSamples];
-    __shared__ uint32_t s_cnt[kMaxSamples];
+    __shared__ uint32_t s_cnt[kMaxSamples / 2];       // 16-bit draw counts, two per word (at most 4 x nsamples draws in all)
     __shared__ unsigned short h_slot[kHashSlots];
     const uint32_t allw = 0xffffffffu;
     const int s = blockIdx.x, lane = threadIdx.x;
     uint32_t* ob = p.bits + (size_t)s * p.m_pad;
     float* ow = p.kw + (size_t)s * p.m_pad;
     for (int i = lane; i < kHashSlots; i += 32) h_slot[i] = 0xFFFFu;
-    for (int i = lane; i < kMaxSamples; i += 32) {
-        s_bits[i] = i < p.n_fixed ? p.fixed_bits[i] : 0u;
-        s_cnt[i] = 0u;
-    }
+    for (int i = lane; i < kMaxSamples; i += 32) s_bits[i] = i < p.n_fixed ? p.fixed_bits[i] : 0u;
+    for (int i = lane; i < kMaxSamples / 2; i += 32) s_cnt[i] = 0u;
     __syncwarp();
     int samples_left = p.nsamples - p.n_fixed;
     int count = p.n_fixed;                       // next free slot (uniform across the warp)
@@ -116,10 +114,10 @@ __global__ void __launch_bounds__(32) kshap_sample_sets(const SamplerParams p) {
             int slot = is_new ? count + before : found;
             if (is_new && processed) {
                 s_bits[slot] = mask;
-                s_cnt[slot] = 1u;
+                atomicAdd(&s_cnt[slot >> 1], 1u << ((slot & 1) * 16));
                 if (paired && samples_left - before > 1) {                               // the complement rides along
                     s_bits[slot + 1] = full ^ mask;
-                    s_cnt[slot + 1] = 1u;
+                    atomicAdd(&s_cnt[(slot + 1) >> 1], 1u << (((slot + 1) & 1) * 16));
                 }
                 uint32_t h = (mask * 2654435761u) >> kHashShift;
                 while (atomicCAS(&h_slot[h], (unsigned short)0xFFFFu, (unsigned short)slot) != 0xFFFFu)
@@ -128,10 +126,11 @@ __global__ void __launch_bounds__(32) kshap_sample_sets(const SamplerParams p) {
             slot = __shfl_sync(allw, slot, leader);                                      // merged proposals follow their leader
             __syncwarp();
             if (processed && !is_new) {
-                atomicAdd(&s_cnt[slot], 1u);
+                atomicAdd(&s_cnt[slot >> 1], 1u << ((slot & 1) * 16));
                 // the complement of a known coalition sits right after it - unless the budget ran out exactly
                 // when that coalition was added
-                if (paired && slot + 1 < p.nsamples && s_bits[slot + 1] == (full ^ mask)) atomicAdd(&s_cnt[slot + 1], 1u);
+                if (paired && slot + 1 < p.nsamples && s_bits[slot + 1] == (full ^ mask))
+                    atomicAdd(&s_cnt[(slot + 1) >> 1], 1u << (((slot + 1) & 1) * 16));
             }
             int added = __shfl_sync(allw, incl, 31);
             if (added > samples_left) added = samples_left;
@@ -144,14 +143,14 @@ __global__ void __launch_bounds__(32) kshap_sample_sets(const SamplerParams p) {
     __syncwarp();
     // ---- write the set out; random block weights (draw counts) are scaled to sum to weight_left
     uint32_t tot = 0u;
-    for (int i = p.n_fixed + lane; i < count; i += 32) tot += s_cnt[i];
+    for (int i = p.n_fixed + lane; i < count; i += 32) tot += (s_cnt[i >> 1] >> ((i & 1) * 16)) & 0xFFFFu;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(allw, tot, o);
     const float scale = tot > 0u ? p.weight_left / (float)tot : 0.f;
     for (int i = lane; i < p.m_pad; i += 32) {
         const bool in_set = i < count;
         ob[i] = in_set ? s_bits[i] : 0u;
-        ow[i] = !in_set ? 0.f : (i < p.n_fixed ? p.fixed_kw[i] : (float)s_cnt[i] * scale);
+        ow[i] = !in_set ? 0.f : (i < p.n_fixed ? p.fixed_kw[i] : (float)((s_cnt[i >> 1] >> ((i & 1) * 16)) & 0xFFFFu) * scale);
     }
 }
 
@@ -254,8 +253,8 @@ int fdb_kshap_sample_on_device(fdb_kshap_plan* pl, int nsamples, unsigned long l
     if (e == cudaSuccess) {
         sp.fixed_bits = d_fb;
         sp.fixed_kw = d_fw;
-        if (nsamples <= 2048) kshap_sample_sets<4096, 20, 2048><<<pl->n_sets, 32>>>(sp);
-        else kshap_sample_sets<8192, 19, 4096><<<pl->n_sets, 32>>>(sp);
+        if (nsamples <= 2048) kshap_sample_sets<2048, 21, 2048><<<pl->n_sets, 32>>>(sp);
+        else kshap_sample_sets<4096, 20, 4096><<<pl->n_sets, 32>>>(sp);
         e = cudaGetLastError();
     }
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
