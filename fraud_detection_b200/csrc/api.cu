@@ -53,6 +53,18 @@ void free_pipeline(fdb_ctx* ctx) {
     ctx->chunk_elem = 0;
 }
 
+// batches up to this many rows are served without copy commands (kernel reads / writes mapped pinned memory)
+int64_t zero_copy_rows() {
+    static int64_t v = -1;
+    if (v < 0) {
+        const char* env = getenv("FDB_ZERO_COPY_ROWS");
+        v = env ? atoll(env) : kSmallRows;      // measured: faster than copy commands up to the whole serving range
+        if (v < 0) v = 0;
+        if (v > kSmallRows) v = kSmallRows;
+    }
+    return v;
+}
+
 int64_t chunk_rows_cap() {
     const char* env = getenv("FDB_CHUNK_ROWS");
     if (env) {
@@ -124,6 +136,29 @@ int run_host(fdb_ctx* ctx, int dtype, int64_t n, const void* x, const LinearPara
         fdb_pipe_slot& s = ctx->slot[0];
         char* st = static_cast<char*>(ctx->h_stage);
         const bool x_pinned = is_device_accessible_host(x);
+        // output blocks inside the pinned staging buffer (offsets keep 16-byte alignment)
+        char* o_phi = st + (size_t)kSmallRows * row_b;
+        char* o_p = o_phi + (size_t)kSmallRows * row_b;
+        char* o_z = o_p + (size_t)kSmallRows * es * 2;
+        char* o_c = o_z + (size_t)kSmallRows * es;
+        char* o_a = o_c + (size_t)kSmallRows;
+        if (n <= zero_copy_rows()) {
+            // request-size batches: no copy commands at all.  The staging buffer is page-locked and mapped, so the
+            // kernel reads the rows and writes every output straight over PCIe; one launch, one stream wait.
+            const void* src = x;
+            if (!x_pinned || !fdb_aligned16(x)) { memcpy(st, x, (size_t)n * row_b); src = st; }
+            rc = fdb_launch_linear_pass(ctx, s.stream, dtype, n, src, prm, divide, proba ? o_p : nullptr, proba_cols,
+                                        logit ? o_z : nullptr, phi ? o_phi : nullptr, cls ? reinterpret_cast<uint8_t*>(o_c) : nullptr,
+                                        abs_sum ? reinterpret_cast<double*>(o_a) : nullptr, ctx->d_partials, ctx->d_ticket);
+            if (rc != FDB_OK) return rc;
+            FDB_CUDA(cudaStreamSynchronize(s.stream));
+            if (phi) memcpy(ph, o_phi, (size_t)n * row_b);
+            if (proba) memcpy(pp, o_p, (size_t)n * es * proba_cols);
+            if (logit) memcpy(pz, o_z, (size_t)n * es);
+            if (cls) memcpy(cls, o_c, (size_t)n);
+            if (abs_sum) memcpy(abs_sum, o_a, 32 * sizeof(double));
+            return FDB_OK;
+        }
         const void* src = x;
         if (!x_pinned) { memcpy(st, x, (size_t)n * row_b); src = st; }
         FDB_CUDA(cudaMemcpyAsync(s.d_in, src, (size_t)n * row_b, cudaMemcpyHostToDevice, s.stream));
@@ -131,12 +166,6 @@ int run_host(fdb_ctx* ctx, int dtype, int64_t n, const void* x, const LinearPara
                                     logit ? s.d_z : nullptr, phi ? s.d_out : nullptr, cls ? s.d_cls : nullptr,
                                     abs_sum ? ctx->d_abs_sum : nullptr, ctx->d_partials, ctx->d_ticket);
         if (rc != FDB_OK) return rc;
-        // outputs land in staging (offsets keep 16-byte alignment), then one memcpy each
-        char* o_phi = st + (size_t)kSmallRows * row_b;
-        char* o_p = o_phi + (size_t)kSmallRows * row_b;
-        char* o_z = o_p + (size_t)kSmallRows * es * 2;
-        char* o_c = o_z + (size_t)kSmallRows * es;
-        char* o_a = o_c + (size_t)kSmallRows;
         if (phi) FDB_CUDA(cudaMemcpyAsync(o_phi, s.d_out, (size_t)n * row_b, cudaMemcpyDeviceToHost, s.stream));
         if (proba) FDB_CUDA(cudaMemcpyAsync(o_p, s.d_p, (size_t)n * es * proba_cols, cudaMemcpyDeviceToHost, s.stream));
         if (logit) FDB_CUDA(cudaMemcpyAsync(o_z, s.d_z, (size_t)n * es, cudaMemcpyDeviceToHost, s.stream));
