@@ -170,19 +170,37 @@ class B200LogisticRegression:
                    getattr(sk, "feature_names_in_", None), device=device)
 
     # -- one kernel launch; which outputs are materialised is chosen per method ------------
+    #: Request-size batches (up to this many rows) always get proba, logit and class from ONE launch, and the result
+    #: is kept for the next call on byte-identical rows: the reference calls ``predict`` and ``predict_proba`` back
+    #: to back on the same request (api/app.py:209,223), which sklearn answers with two full passes.
+    pair_cache_rows = 512
+
     def _pass(self, X, *, proba=False, logit=False, cls=False):
         A = _rows(X, self)
         n = A.shape[0]
         dt = A.dtype
-        out_p = np.empty((n, 2), dtype=dt) if proba else None
-        out_z = np.empty((n,), dtype=dt) if logit else None
-        out_c = np.empty((n,), dtype=np.uint8) if cls else None
+        small = 0 < n <= self.pair_cache_rows
+        if small:
+            key = (dt.str, id(self._coef_c), float(self.intercept_[0]), A.tobytes())
+            last = getattr(self, "_last_pass", None)
+            if last is not None and last[0] == key:
+                _, p, z, c = last
+                return (p.copy() if proba else None), (z.copy() if logit else None), (c.copy() if cls else None)
+            proba_k = logit_k = cls_k = True
+        else:
+            proba_k, logit_k, cls_k = proba, logit, cls
+        out_p = np.empty((n, 2), dtype=dt) if proba_k else None
+        out_z = np.empty((n,), dtype=dt) if logit_k else None
+        out_c = np.empty((n,), dtype=np.uint8) if cls_k else None
         abs_sum = np.zeros(32, dtype=np.float64)
         _lib.check(_lib.lib.fdb_linear_pass_host(
             _lib.get_ctx(self.device), _lib.dtype_code(dt), n, _lib.np_ptr(A), None, self._coef_c,
             float(self.intercept_[0]), _lib.np_ptr(out_p), 2, _lib.np_ptr(out_z), None, _lib.np_ptr(out_c),
             _lib.np_ptr(abs_sum)))
         _check_abs_sum(abs_sum, A)
+        if small:
+            self._last_pass = (key, out_p, out_z, out_c)      # one reference assignment: safe against concurrent readers
+            return (out_p.copy() if proba else None), (out_z.copy() if logit else None), (out_c.copy() if cls else None)
         return out_p, out_z, out_c
 
     def decision_function(self, X):

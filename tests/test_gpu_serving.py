@@ -78,3 +78,29 @@ def test_score_file_end_to_end(params, tmp_path):
     ref_abs, ref_top3 = linear_shap.global_summary(phi_ref)
     np.testing.assert_allclose(out["mean_abs_shap"], ref_abs, rtol=1e-10)
     assert list(out["top3"]) == list(ref_top3) and out["rows"] == 50000
+
+
+def test_paired_predict_calls_share_one_pass(params):
+    """api/app.py:209,223 calls predict and predict_proba on the same request: request-size batches keep the fused
+    result for byte-identical rows; returned arrays are the caller's own and different rows never hit the cache."""
+    import warnings
+    from fraud_detection_b200 import wrap
+    warnings.filterwarnings("ignore")
+    _, model_sk, _ = scoring.live_estimators(params)
+    model = wrap(model_sk)
+    rs = np.random.RandomState(5)
+    for n in (1, 7, 64, 65, 300, 512, 513):
+        Xs = rs.randn(n, 30) * 2.0
+        c1 = model.predict(Xs)
+        p1 = model.predict_proba(Xs)
+        z1 = model.decision_function(Xs)
+        np.testing.assert_array_equal(c1, model_sk.predict(Xs))
+        np.testing.assert_allclose(p1, model_sk.predict_proba(Xs), atol=1e-12)
+        np.testing.assert_allclose(z1, model_sk.decision_function(Xs), atol=1e-12)
+        p1[:] = 7.0                                   # the caller owns what it got
+        np.testing.assert_allclose(model.predict_proba(Xs), model_sk.predict_proba(Xs), atol=1e-12)
+        Xs2 = Xs.copy()
+        Xs2[0, 3] += 1.0                              # different bytes -> a fresh pass
+        np.testing.assert_allclose(model.predict_proba(Xs2), model_sk.predict_proba(Xs2), atol=1e-12)
+        X32 = Xs.astype(np.float32)                   # same values, other dtype -> its own pass and dtype rules
+        np.testing.assert_allclose(model.predict_proba(X32), model_sk.predict_proba(X32), atol=1e-5)

@@ -54,18 +54,32 @@ def run(batches=(1, 2, 4, 8, 16, 32, 64, 128, 256, 512, 1024, 2048, 4096), calls
     coef = model_sk.coef_[0]
     out = {"estimators": origin, "calls": calls, "host_cpus": os.cpu_count(), "rows": []}
     for bsz in batches:
-        raw = pd.DataFrame(synth.rows(bsz, seed=bsz))
-        Xs = pd.DataFrame(scaler_sk.transform(raw), columns=names)        # api/app.py:194-197
-        Xw = pd.DataFrame(raw.values, columns=[f"feature_{i}" for i in range(30)])   # api/worker.py:70
+        # every call gets a DIFFERENT request (a ring of distinct batches): the drop-in keeps the fused result of a
+        # request-size batch for the paired predict / predict_proba calls, so repeating one request would time a
+        # dictionary look-up instead of the device path
+        ring = max(2, min(64, (1 << 16) // bsz))
+        raws = [pd.DataFrame(synth.rows(bsz, seed=1000 * bsz + r)) for r in range(ring)]
+        Xss = [pd.DataFrame(scaler_sk.transform(raw), columns=names) for raw in raws]              # api/app.py:194-197
+        Xws = [pd.DataFrame(raw.values, columns=[f"feature_{i}" for i in range(30)]) for raw in raws]   # api/worker.py:70
         n = max(200, calls // max(1, bsz // 64)) if bsz > 64 else calls
-        row = {"batch": bsz, "calls": n}
-        row["b200_predict_bracket"] = _percentiles(lambda: (model.predict(Xs), model.predict_proba(Xs)), n)
-        row["b200_score_rows"] = _percentiles(lambda: model.score_rows(Xs), n)
-        row["sklearn_predict_bracket"] = _percentiles(lambda: (model_sk.predict(Xs), model_sk.predict_proba(Xs)), n)
-        row["b200_shap_bracket"] = _percentiles(lambda: expl.shap_values(Xw), n)
-        row["cpu_shap_bracket"] = _percentiles(lambda: linear_shap.shap_values(coef, np.zeros(30), Xw), n)
-        row["b200_transform"] = _percentiles(lambda: scaler.transform(raw), n)
-        row["sklearn_transform"] = _percentiles(lambda: scaler_sk.transform(raw), n)
+        row = {"batch": bsz, "calls": n, "distinct_requests": ring}
+        tick = [0]
+
+        def nxt(seq):
+            tick[0] += 1
+            return seq[tick[0] % ring]
+
+        def pair(m):
+            Xs = nxt(Xss)
+            return m.predict(Xs), m.predict_proba(Xs)
+
+        row["b200_predict_bracket"] = _percentiles(lambda: pair(model), n)
+        row["b200_score_rows"] = _percentiles(lambda: model.score_rows(nxt(Xss)), n)
+        row["sklearn_predict_bracket"] = _percentiles(lambda: pair(model_sk), n)
+        row["b200_shap_bracket"] = _percentiles(lambda: expl.shap_values(nxt(Xws)), n)
+        row["cpu_shap_bracket"] = _percentiles(lambda: linear_shap.shap_values(coef, np.zeros(30), nxt(Xws)), n)
+        row["b200_transform"] = _percentiles(lambda: scaler.transform(nxt(raws)), n)
+        row["sklearn_transform"] = _percentiles(lambda: scaler_sk.transform(nxt(raws)), n)
         out["rows"].append(row)
     return out
 
