@@ -459,6 +459,17 @@ def test_bf16_three_term_operands(params, monkeypatch):
         np.testing.assert_allclose(ey, ey_ref, rtol=0, atol=2e-6)
         _check_phi(phi, phi_ref, f, X, fnull)
     plan.close()
+    # several coalition sets: K2 expands its A tiles from the coalition words (bf16 ones here) instead of copying images
+    sets = [ks.sample_coalitions(30, 300, np.random.RandomState(31 + i))[:2] for i in range(3)]
+    phi_ref, ey_ref, fnull = _oracle_rows(f, X, bg, sets)
+    plan = _plan(params, bg, sets)
+    assert plan.info()["fmt"] == 1
+    phi, ey, _ = _run(plan, X, TC)
+    for i in range(len(X)):
+        n_i = len(sets[i % 3][1])
+        np.testing.assert_allclose(ey[i, :n_i], ey_ref[i], rtol=0, atol=2e-6)
+    _check_phi(phi, phi_ref, f, X, fnull)
+    plan.close()
 
 
 def test_large_magnitude_rows_select_bf16_and_stay_finite(params):
