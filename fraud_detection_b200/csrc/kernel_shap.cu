@@ -26,9 +26,13 @@ namespace {
 
 constexpr int kNV = FDB_F - 1;   // 29 unknowns after eliminating the last feature
 
-__device__ __forceinline__ float link_apply(float v, int link) {
+__device__ __forceinline__ float link_apply(float v, int link) {       // see fdb_kshap_link (stored-value encoding)
     if (link != 1) return v;
-    v = fminf(fmaxf(v, 1e-30f), 0.99999994f);       // see fdb_kshap_link: saturate instead of inf / NaN
+    if (v < 0.f) {
+        const float c = fmaxf(-v, 1e-37f);
+        return logf((1.0f - c) / c);
+    }
+    v = fminf(fmaxf(v, 1e-37f), 0.99999994f);
     return logf(v / (1.0f - v));
 }
 
@@ -125,7 +129,7 @@ __global__ void __launch_bounds__(128) kshap_eval_simt(const float* __restrict__
                                                        const int32_t* __restrict__ set_idx, int n_sets,
                                                        const uint32_t* __restrict__ bits, int m_pad,
                                                        const float* __restrict__ P, int n_bg,
-                                                       const float* __restrict__ wq, float* __restrict__ ey) {
+                                                       const float* __restrict__ wq, float* __restrict__ ey, int link) {
     __shared__ float q[32];
     const int r = blockIdx.y;
     const int m = blockIdx.x * 128 + threadIdx.x;
@@ -136,15 +140,26 @@ __global__ void __launch_bounds__(128) kshap_eval_simt(const float* __restrict__
     float sq = 0.f;
 #pragma unroll
     for (int k = 0; k < FDB_F; ++k) sq += ((b >> k) & 1u) ? q[k] : 0.f;
-    float acc = 0.f;
+    float acc = 0.f, comp = 0.f;
     for (int j = 0; j < n_bg; ++j) {
         const float* pr = P + (size_t)j * 32;
         float g = pr[30];   // intercept
 #pragma unroll
         for (int k = 0; k < FDB_F; ++k) g += ((b >> k) & 1u) ? 0.f : pr[k];
         acc += 1.0f / (1.0f + expf(-(g + sq)));
+        if (link == 1) comp += 1.0f / (1.0f + expf(g + sq));
     }
-    ey[(size_t)r * m_pad + m] = acc / (float)n_bg;
+    ey[(size_t)r * m_pad + m] = link == 1 ? fdb_kshap_encode_ey(acc, comp, 1.0f / (float)n_bg) : acc / (float)n_bg;
+}
+
+// ey_out: the caller's view of the coalition expectations (plain values, n_masks per row)
+__global__ void kshap_copy_ey(const float* __restrict__ ey, int m_pad, float* __restrict__ out, int n_masks, int64_t total,
+                              int link) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const int64_t r = i / n_masks;
+    const float v = ey[r * m_pad + (i - r * n_masks)];
+    out[i] = link == 1 ? fdb_kshap_decode_ey(v) : v;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -523,12 +538,15 @@ extern "C" int fdb_kshap_explain_dev(fdb_kshap_plan* p, void* stream, int64_t n_
             if (rc != FDB_OK) return rc;
         } else {
             dim3 grid(p->m_pad / 128, nb);
-            kshap_eval_simt<<<grid, 128, 0, st>>>(xb, r0, sb, p->n_sets, p->d_bits, p->m_pad, p->d_P, p->n_bg, p->d_wq, p->d_ey);
+            kshap_eval_simt<<<grid, 128, 0, st>>>(xb, r0, sb, p->n_sets, p->d_bits, p->m_pad, p->d_P, p->n_bg, p->d_wq, p->d_ey, p->link);
             FDB_CUDA(cudaGetLastError());
         }
-        if (ey_out)
-            FDB_CUDA(cudaMemcpy2DAsync(ey_out + r0 * p->n_masks, (size_t)p->n_masks * 4, p->d_ey, (size_t)p->m_pad * 4,
-                                       (size_t)p->n_masks * 4, nb, cudaMemcpyDeviceToDevice, st));
+        if (ey_out) {
+            const int64_t total = (int64_t)nb * p->n_masks;
+            kshap_copy_ey<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(p->d_ey, p->m_pad, ey_out + r0 * p->n_masks, p->n_masks, total,
+                                                                                 p->link);
+            FDB_CUDA(cudaGetLastError());
+        }
         if (p->num_features > 0) {
             int rc = fdb_kshap_launch_lars_solve(p, st, xb, r0, nb, sb, phi + r0 * FDB_F, abs_sum, r0 > 0 ? 1 : 0, n_rows);
             if (rc != FDB_OK) return rc;

@@ -84,26 +84,40 @@ __device__ __forceinline__ float fx_from_h16(uint16_t h, int fmt) {
 //   background (fdb_kshap_build_factored) and kshap_build_E measures the bound; when every quad stays within
 //   2^+-114 there is no min() in the loop, tiny sigmoids keep their relative accuracy (both links) and a sigmoid
 //   costs 3.5 issue slots.  acc gathers sum 1/d; the caller multiplies by b once per (row, coalition).
-enum { kFxClampedQuads = 0, kFxClampedPairs = 1, kFxBalanced = 2 };
+// MODE 3 (balanced, logit link): as MODE 2 plus the complements  1 - sigma = g / d,  g = E a  (d = g + b), summed with
+//   the same reciprocal:  sum_quad g_i / d_i = ((g0 d1 + g1 d0) p23 + (g2 d3 + g3 d2) p01) / (p01 p23).  accc gathers
+//   them; with both sums the stored expectation is exact to float32 in both tails (fdb_kshap_encode_ey).
+enum { kFxClampedQuads = 0, kFxClampedPairs = 1, kFxBalanced = 2, kFxBalancedLogit = 3 };
 
 template <int MODE>
 __device__ __forceinline__ void chunk_sum4(const float* __restrict__ e0, int cbs, int nquads, int ntail,
-                                           const float* __restrict__ t, float* __restrict__ acc) {
+                                           const float* __restrict__ t, float* __restrict__ acc, float* __restrict__ accc) {
+    constexpr bool kBal = MODE == kFxBalanced || MODE == kFxBalancedLogit;
     constexpr float kClamp = MODE == kFxClampedPairs ? 4.611686018427388e18f : 1073741824.f;
     float a[4], b[4];
 #pragma unroll
     for (int mm = 0; mm < 4; ++mm) {
-        a[mm] = ptx::ex2_approx(MODE == kFxBalanced ? fminf(t[mm], 0.f) : t[mm]);
-        b[mm] = MODE == kFxBalanced ? ptx::ex2_approx(fminf(-t[mm], 0.f)) : 1.0f;
+        a[mm] = ptx::ex2_approx(kBal ? fminf(t[mm], 0.f) : t[mm]);
+        b[mm] = kBal ? ptx::ex2_approx(fminf(-t[mm], 0.f)) : 1.0f;
     }
 #pragma unroll 2
     for (int q = 0; q < nquads; ++q) {
 #pragma unroll
         for (int mm = 0; mm < 4; ++mm) {
             const float4 e = *reinterpret_cast<const float4*>(e0 + mm * cbs + 4 * q);
+            if (MODE == kFxBalancedLogit) {
+                const float g0 = e.x * a[mm], g1 = e.y * a[mm], g2 = e.z * a[mm], g3 = e.w * a[mm];
+                const float d0 = g0 + b[mm], d1 = g1 + b[mm], d2 = g2 + b[mm], d3 = g3 + b[mm];
+                const float n01 = d0 + d1, p01 = d0 * d1, n23 = d2 + d3, p23 = d2 * d3;
+                const float r = ptx::rcp_approx(p01 * p23);
+                acc[mm] = fmaf(fmaf(n01, p23, n23 * p01), r, acc[mm]);
+                const float c01 = fmaf(g0, d1, g1 * d0), c23 = fmaf(g2, d3, g3 * d2);
+                accc[mm] = fmaf(fmaf(c01, p23, c23 * p01), r, accc[mm]);
+                continue;
+            }
             float d0 = fmaf(e.x, a[mm], b[mm]), d1 = fmaf(e.y, a[mm], b[mm]);
             float d2 = fmaf(e.z, a[mm], b[mm]), d3 = fmaf(e.w, a[mm], b[mm]);
-            if (MODE != kFxBalanced) {
+            if (!kBal) {
                 d0 = fminf(d0, kClamp); d1 = fminf(d1, kClamp); d2 = fminf(d2, kClamp); d3 = fminf(d3, kClamp);
             }
             const float n01 = d0 + d1, p01 = d0 * d1, n23 = d2 + d3, p23 = d2 * d3;
@@ -118,8 +132,12 @@ __device__ __forceinline__ void chunk_sum4(const float* __restrict__ e0, int cbs
     for (int i = 0; i < ntail; ++i)
 #pragma unroll
         for (int mm = 0; mm < 4; ++mm) {
-            const float d = fmaf(e0[mm * cbs + 4 * nquads + i], a[mm], b[mm]);
-            acc[mm] += ptx::rcp_approx(MODE == kFxBalanced ? d : fminf(d, kClamp));
+            const float ev = e0[mm * cbs + 4 * nquads + i];
+            const float g = ev * a[mm];
+            const float d = MODE == kFxBalancedLogit ? g + b[mm] : fmaf(ev, a[mm], b[mm]);
+            const float r = ptx::rcp_approx(kBal ? d : fminf(d, kClamp));
+            acc[mm] += r;
+            if (MODE == kFxBalancedLogit) accc[mm] = fmaf(g, r, accc[mm]);
         }
 }
 
@@ -265,8 +283,11 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
             // MMA warp busy meanwhile) and are fetched four coalitions at a time, so only the 32 running sums live
             // in registers across the background chunks.
             float part[32];
+            float partc[MODE == kFxBalancedLogit ? 32 : 4];      // complement sums (logit link only)
 #pragma unroll
             for (int mi = 0; mi < 32; ++mi) part[mi] = 0.f;
+#pragma unroll
+            for (int mi = 0; mi < (MODE == kFxBalancedLogit ? 32 : 4); ++mi) partc[mi] = 0.f;
             const float4* op = reinterpret_cast<const float4*>(p.eoff + tile * 128 + cg * 32);
             for (int c = 0; c < p.n_chunks; ++c, ++j) {
                 const int es = j & 1;
@@ -285,12 +306,13 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
                     t4[1] = fminf(fmaxf(__uint_as_float(rr[1]) + o.y, -126.f), 126.f);
                     t4[2] = fminf(fmaxf(__uint_as_float(rr[2]) + o.z, -126.f), 126.f);
                     t4[3] = fminf(fmaxf(__uint_as_float(rr[3]) + o.w, -126.f), 126.f);
-                    chunk_sum4<MODE>(eb + (size_t)g4 * 4 * cbs, cbs, cbw >> 2, cbw & 3, t4, part + 4 * g4);
+                    chunk_sum4<MODE>(eb + (size_t)g4 * 4 * cbs, cbs, cbw >> 2, cbw & 3, t4, part + 4 * g4,
+                                     partc + (MODE == kFxBalancedLogit ? 4 * g4 : 0));
                 }
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(&bars->e_empty[es]);
             }
-            if (MODE == kFxBalanced) {                       // sigma sums were gathered as sum 1/d: scale by b = min(1, 2^-t)
+            if (MODE == kFxBalanced || MODE == kFxBalancedLogit) {   // sigma sums were gathered as sum 1/d: scale by b = min(1, 2^-t)
                 uint32_t r0[16], r1[16];
                 ptx::tmem_ld16(ta, r0);
                 ptx::tmem_ld16(ta + 16, r1);
@@ -304,6 +326,8 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
                         const int mi = i * 4 + q;
                         const float t = fminf(fmaxf(__uint_as_float(mi < 16 ? r0[mi] : r1[mi - 16]) + oo[q], -126.f), 126.f);
                         part[mi] *= ptx::ex2_approx(fminf(-t, 0.f));
+                        if (MODE == kFxBalancedLogit)     // both sums known: keep the smaller one (sign tells which)
+                            part[mi] = fdb_kshap_encode_ey(part[mi], partc[mi], p.inv_bg);
                     }
                 }
             }
@@ -315,8 +339,10 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
                 //   g[j] += (kw_m x_mj) * (link(ey[r][m]) - link(fnull))   over its 32 coalitions
                 // (two passes of 16 features each: 16 sums + 32 y + a batch of loads in flight fit the register budget,
                 //  so the warp-uniform xw loads are issued well ahead of the FMAs that consume them)
+                if (MODE != kFxBalancedLogit) {
 #pragma unroll
-                for (int mi = 0; mi < 32; ++mi) part[mi] *= p.inv_bg;
+                    for (int mi = 0; mi < 32; ++mi) part[mi] *= p.inv_bg;
+                }
                 const float4* xwp = reinterpret_cast<const float4*>(p.xw + (size_t)(tile * 128 + cg * 32) * 32);
                 float4* gdst = reinterpret_cast<float4*>(p.gpart + ((size_t)row * (p.m_pad / 32) + tile * 4 + cg) * 32);
 #pragma unroll
@@ -512,6 +538,7 @@ int fdb_kshap_launch_eval_fx(fdb_kshap_plan* pl, cudaStream_t st, const float* x
         FDB_CUDA(cudaFuncSetAttribute(kshap_eval_fx_kernel<kFxClampedQuads>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         FDB_CUDA(cudaFuncSetAttribute(kshap_eval_fx_kernel<kFxClampedPairs>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         FDB_CUDA(cudaFuncSetAttribute(kshap_eval_fx_kernel<kFxBalanced>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        FDB_CUDA(cudaFuncSetAttribute(kshap_eval_fx_kernel<kFxBalancedLogit>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured[pl->ctx->device] = true;
     }
     const int64_t n_units = (int64_t)((n_rows + 127) / 128) * p.tiles;
@@ -521,7 +548,8 @@ int fdb_kshap_launch_eval_fx(fdb_kshap_plan* pl, cudaStream_t st, const float* x
     // guaranteed to stay within 2^+-114 (kshap_build_E)
     const char* force = getenv("FDB_FX_CLAMPED");
     const bool balanced = pl->fx_quad_logsum <= 110.f && pl->fx_half_spread <= 100.f && !(force && atoi(force) != 0);
-    if (balanced) kshap_eval_fx_kernel<kFxBalanced><<<(int)grid, kFxThreads, smem, st>>>(p);
+    if (balanced && pl->link == 1) kshap_eval_fx_kernel<kFxBalancedLogit><<<(int)grid, kFxThreads, smem, st>>>(p);
+    else if (balanced) kshap_eval_fx_kernel<kFxBalanced><<<(int)grid, kFxThreads, smem, st>>>(p);
     else if (pl->link == 1) kshap_eval_fx_kernel<kFxClampedPairs><<<(int)grid, kFxThreads, smem, st>>>(p);
     else kshap_eval_fx_kernel<kFxClampedQuads><<<(int)grid, kFxThreads, smem, st>>>(p);
     FDB_CUDA(cudaGetLastError());

@@ -59,7 +59,7 @@ struct TcParams {
     int n_rows, n_sets, tiles, m_pad;
     int n_bg, nb_pad, nsplit, fmt;
     int n_chunks, chunk_cols;
-    int wide;                                  // logit link: keep relative accuracy of tiny sigmoids
+    int wide;                                  // logit link: sigmoid AND complement sums, stored value encoded (fdb_kshap_encode_ey)
     float inv_bg;
 };
 
@@ -160,6 +160,30 @@ __device__ __forceinline__ float sigmoid_sum16(const uint32_t (&r)[16], int nval
 template <bool WIDE>
 __device__ __forceinline__ float sigmoid_group(const uint32_t (&r)[16], int nvalid) {
     return nvalid >= 16 ? sigmoid_sum16<false, WIDE>(r, 16) : sigmoid_sum16<true, WIDE>(r, nvalid);
+}
+
+// Logit link: sum of the sigmoids AND of their complements over up to 16 accumulator columns, two columns per
+// reciprocal:  s0 + s1 = (d0 + d1) / (d0 d1),  (1 - s0) + (1 - s1) = (e0 d1 + e1 d0) / (d0 d1),  e = 2^t, d = 1 + e.
+// t is clamped at 62 (e0 d1 + e1 d0 < 2^126); a sigmoid keeps its relative accuracy down to 2^-62 and a
+// complement down to 2^-126, so the stored expectation is exact to float32 in both tails (fdb_kshap_encode_ey).
+// Columns beyond the background are simply left out (an odd last column takes a reciprocal of its own).
+__device__ __forceinline__ void sigmoid_and_complement_sums16(const uint32_t (&r)[16], int nvalid, float& S, float& C) {
+#pragma unroll
+    for (int q = 0; q < 16; q += 2) {
+        if (q >= nvalid) break;
+        const float e0 = ptx::ex2_approx(fminf(__uint_as_float(r[q]), 62.f));
+        const float e1 = ptx::ex2_approx(fminf(__uint_as_float(r[q + 1]), 62.f));
+        const float d0 = 1.0f + e0, d1 = 1.0f + e1;
+        if (q + 1 < nvalid) {
+            const float rp = ptx::rcp_approx(d0 * d1);
+            S = fmaf(d0 + d1, rp, S);
+            C = fmaf(fmaf(e0, d1, e1 * d0), rp, C);
+        } else {
+            const float r0 = ptx::rcp_approx(d0);
+            S += r0;
+            C = fmaf(e0, r0, C);
+        }
+    }
 }
 
 // smem carve-up (dynamic): [B image][A stages x pipes][Bq stages x pipes][barriers]
@@ -343,7 +367,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcPa
         for (int64_t it = (int64_t)blockIdx.x * kPipes + g; it < n_items; it += stride) {
             const int row = (int)(it / p.tiles);
             const int tile = (int)(it % p.tiles);
-            float acc = 0.f;
+            float acc = 0.f, comp = 0.f;
             for (int c = 0; c < p.n_chunks; ++c, ++job) {
                 const uint32_t buf = job & 1, ta = ta0 + buf * kBufCols;
                 ptx::mbar_wait(&pb.t_full[buf], (job >> 1) & 1);
@@ -359,16 +383,18 @@ __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcPa
                     ptx::tmem_ld_wait();
                     if (gi + 1 < ngroups) ptx::tmem_ld16(ta + (gi + 1) * 16, rb);
                     else release_tmem(&pb.t_empty[buf], lane);
-                    acc += p.wide ? sigmoid_group<true>(ra, valid - gi * 16) : sigmoid_group<false>(ra, valid - gi * 16);
+                    if (p.wide) sigmoid_and_complement_sums16(ra, valid - gi * 16, acc, comp);
+                    else acc += sigmoid_group<false>(ra, valid - gi * 16);
                     if (gi + 1 < ngroups) {
                         ptx::tmem_ld_wait();
                         if (gi + 2 < ngroups) ptx::tmem_ld16(ta + (gi + 2) * 16, ra);
                         else release_tmem(&pb.t_empty[buf], lane);
-                        acc += p.wide ? sigmoid_group<true>(rb, valid - (gi + 1) * 16) : sigmoid_group<false>(rb, valid - (gi + 1) * 16);
+                        if (p.wide) sigmoid_and_complement_sums16(rb, valid - (gi + 1) * 16, acc, comp);
+                        else acc += sigmoid_group<false>(rb, valid - (gi + 1) * 16);
                     }
                 }
             }
-            p.ey[(size_t)row * p.m_pad + tile * 128 + qd * 32 + lane] = acc * p.inv_bg;
+            p.ey[(size_t)row * p.m_pad + tile * 128 + qd * 32 + lane] = p.wide ? fdb_kshap_encode_ey(acc, comp, p.inv_bg) : acc * p.inv_bg;
         }
     }
 

@@ -59,12 +59,24 @@ int fdb_kshap_launch_eval_tc(fdb_kshap_plan* p, cudaStream_t st, const float* x,
 int fdb_kshap_build_factored(fdb_kshap_plan* pl, const double* bg_host);
 int fdb_kshap_launch_eval_fx(fdb_kshap_plan* pl, cudaStream_t st, const float* x, int n_rows, float* ey);
 
-// Link applied to a float32 coalition expectation.  The logit keeps its argument inside [1e-30, 1 - 2^-24]: an
-// expectation that rounds to 1 in float32 (|logit| beyond ~16.6) saturates there instead of giving inf / NaN.
+// Coalition expectations between evaluate and solve (d_ey).  Identity link: ey itself.  Logit link: an expectation
+// above 1/2 would lose its distance to 1 in float32 (1 - ey < 6e-8 already breaks logit(ey)), so the evaluators
+// sum the sigmoids AND their complements and store  ey  when ey <= 1/2,  -(1 - ey)  otherwise: either way the
+// small quantity keeps its relative accuracy and logit(ey) is exact to float32 in both tails.
 #ifdef __CUDACC__
+__device__ __forceinline__ float fdb_kshap_encode_ey(float sum_sigma, float sum_complement, float inv_bg) {
+    return sum_sigma <= sum_complement ? sum_sigma * inv_bg : -(sum_complement * inv_bg);
+}
+__device__ __forceinline__ float fdb_kshap_decode_ey(float v) { return v < 0.f ? 1.0f + v : v; }
+// link(ey) from the stored value.  A plain (unsigned) expectation that rounded to 1 - possible only from the clamped
+// evaluator variants - saturates at 1 - 2^-24 instead of giving inf / NaN.
 __device__ __forceinline__ float fdb_kshap_link(float v, int link) {
     if (link != 1) return v;
-    v = fminf(fmaxf(v, 1e-30f), 0.99999994f);
+    if (v < 0.f) {
+        const float c = fmaxf(-v, 1e-37f);            // 1 - ey
+        return __logf((1.0f - c) / c);
+    }
+    v = fminf(fmaxf(v, 1e-37f), 0.99999994f);
     return __logf(v / (1.0f - v));
 }
 #endif

@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(128) kshap_lars_solve(
             const uint32_t b = sb[m0 + lane];
             const float kwv = sk[m0 + lane];
             const float ev = er[m0 + lane];
-            const float v = kwv != 0.f ? kwv * ((link == 1 ? logf(fminf(fmaxf(ev, 1e-30f), 0.99999994f) / (1.0f - fminf(fmaxf(ev, 1e-30f), 0.99999994f))) : ev) - lnull_f) : 0.f;
+            const float v = kwv != 0.f ? kwv * (fdb_kshap_link(ev, link) - lnull_f) : 0.f;
 #pragma unroll
             for (int j = 0; j < FDB_F; ++j) gj[j] += ((b >> j) & 1u) ? v : 0.f;
         }

@@ -17,11 +17,12 @@ nsamples = int(sys.argv[2]) if len(sys.argv) > 2 else 2048
 n_bg = int(sys.argv[3]) if len(sys.argv) > 3 else 100
 reps = int(sys.argv[4]) if len(sys.argv) > 4 else 5
 num_features = int(sys.argv[5]) if len(sys.argv) > 5 else 0
+link = sys.argv[6] if len(sys.argv) > 6 else "identity"
 prm = scoring.load_params()
 bg = scoring.transform(prm, synth.rows(n_bg, seed=43))
 X = scoring.transform(prm, synth.rows(rows, seed=1)).astype(np.float32)
 bits, kw = sampler.sample_coalitions(30, nsamples, np.random.RandomState(0))
-plan = KernelShapPlan(prm.coef, prm.intercept, bg, bits, kw)
+plan = KernelShapPlan(prm.coef, prm.intercept, bg, bits, kw, link)
 if num_features:
     plan.set_num_features(num_features)
 x = torch.from_numpy(X).cuda()
