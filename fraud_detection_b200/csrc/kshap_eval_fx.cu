@@ -91,33 +91,22 @@ enum { kFxClampedQuads = 0, kFxClampedPairs = 1, kFxBalanced = 2, kFxBalancedLog
 
 template <int MODE>
 __device__ __forceinline__ void chunk_sum4(const float* __restrict__ e0, int cbs, int nquads, int ntail,
-                                           const float* __restrict__ t, float* __restrict__ acc, float* __restrict__ accc) {
-    constexpr bool kBal = MODE == kFxBalanced || MODE == kFxBalancedLogit;
+                                           const float* __restrict__ t, float* __restrict__ acc) {
     constexpr float kClamp = MODE == kFxClampedPairs ? 4.611686018427388e18f : 1073741824.f;
     float a[4], b[4];
 #pragma unroll
     for (int mm = 0; mm < 4; ++mm) {
-        a[mm] = ptx::ex2_approx(kBal ? fminf(t[mm], 0.f) : t[mm]);
-        b[mm] = kBal ? ptx::ex2_approx(fminf(-t[mm], 0.f)) : 1.0f;
+        a[mm] = ptx::ex2_approx(MODE == kFxBalanced ? fminf(t[mm], 0.f) : t[mm]);
+        b[mm] = MODE == kFxBalanced ? ptx::ex2_approx(fminf(-t[mm], 0.f)) : 1.0f;
     }
 #pragma unroll 2
     for (int q = 0; q < nquads; ++q) {
 #pragma unroll
         for (int mm = 0; mm < 4; ++mm) {
             const float4 e = *reinterpret_cast<const float4*>(e0 + mm * cbs + 4 * q);
-            if (MODE == kFxBalancedLogit) {
-                const float g0 = e.x * a[mm], g1 = e.y * a[mm], g2 = e.z * a[mm], g3 = e.w * a[mm];
-                const float d0 = g0 + b[mm], d1 = g1 + b[mm], d2 = g2 + b[mm], d3 = g3 + b[mm];
-                const float n01 = d0 + d1, p01 = d0 * d1, n23 = d2 + d3, p23 = d2 * d3;
-                const float r = ptx::rcp_approx(p01 * p23);
-                acc[mm] = fmaf(fmaf(n01, p23, n23 * p01), r, acc[mm]);
-                const float c01 = fmaf(g0, d1, g1 * d0), c23 = fmaf(g2, d3, g3 * d2);
-                accc[mm] = fmaf(fmaf(c01, p23, c23 * p01), r, accc[mm]);
-                continue;
-            }
             float d0 = fmaf(e.x, a[mm], b[mm]), d1 = fmaf(e.y, a[mm], b[mm]);
             float d2 = fmaf(e.z, a[mm], b[mm]), d3 = fmaf(e.w, a[mm], b[mm]);
-            if (!kBal) {
+            if (MODE != kFxBalanced) {
                 d0 = fminf(d0, kClamp); d1 = fminf(d1, kClamp); d2 = fminf(d2, kClamp); d3 = fminf(d3, kClamp);
             }
             const float n01 = d0 + d1, p01 = d0 * d1, n23 = d2 + d3, p23 = d2 * d3;
@@ -132,12 +121,41 @@ __device__ __forceinline__ void chunk_sum4(const float* __restrict__ e0, int cbs
     for (int i = 0; i < ntail; ++i)
 #pragma unroll
         for (int mm = 0; mm < 4; ++mm) {
-            const float ev = e0[mm * cbs + 4 * nquads + i];
-            const float g = ev * a[mm];
-            const float d = MODE == kFxBalancedLogit ? g + b[mm] : fmaf(ev, a[mm], b[mm]);
-            const float r = ptx::rcp_approx(kBal ? d : fminf(d, kClamp));
+            const float d = fmaf(e0[mm * cbs + 4 * nquads + i], a[mm], b[mm]);
+            acc[mm] += ptx::rcp_approx(MODE == kFxBalanced ? d : fminf(d, kClamp));
+        }
+}
+
+// MODE 3 body: sigmoid and complement sums for four coalitions over one background chunk (see the mode list above)
+__device__ __forceinline__ void chunk_sum4_logit(const float* __restrict__ e0, int cbs, int nquads, int ntail,
+                                                 const float* __restrict__ t, float* __restrict__ acc, float* __restrict__ accc) {
+    float a[4], b[4];
+#pragma unroll
+    for (int mm = 0; mm < 4; ++mm) {
+        a[mm] = ptx::ex2_approx(fminf(t[mm], 0.f));
+        b[mm] = ptx::ex2_approx(fminf(-t[mm], 0.f));
+    }
+#pragma unroll 2
+    for (int q = 0; q < nquads; ++q) {
+#pragma unroll
+        for (int mm = 0; mm < 4; ++mm) {
+            const float4 e = *reinterpret_cast<const float4*>(e0 + mm * cbs + 4 * q);
+            const float g0 = e.x * a[mm], g1 = e.y * a[mm], g2 = e.z * a[mm], g3 = e.w * a[mm];
+            const float d0 = g0 + b[mm], d1 = g1 + b[mm], d2 = g2 + b[mm], d3 = g3 + b[mm];
+            const float n01 = d0 + d1, p01 = d0 * d1, n23 = d2 + d3, p23 = d2 * d3;
+            const float r = ptx::rcp_approx(p01 * p23);
+            acc[mm] = fmaf(fmaf(n01, p23, n23 * p01), r, acc[mm]);
+            const float c01 = fmaf(g0, d1, g1 * d0), c23 = fmaf(g2, d3, g3 * d2);
+            accc[mm] = fmaf(fmaf(c01, p23, c23 * p01), r, accc[mm]);
+        }
+    }
+    for (int i = 0; i < ntail; ++i)
+#pragma unroll
+        for (int mm = 0; mm < 4; ++mm) {
+            const float g = e0[mm * cbs + 4 * nquads + i] * a[mm];
+            const float r = ptx::rcp_approx(g + b[mm]);
             acc[mm] += r;
-            if (MODE == kFxBalancedLogit) accc[mm] = fmaf(g, r, accc[mm]);
+            accc[mm] = fmaf(g, r, accc[mm]);
         }
 }
 
@@ -283,11 +301,11 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
             // MMA warp busy meanwhile) and are fetched four coalitions at a time, so only the 32 running sums live
             // in registers across the background chunks.
             float part[32];
-            float partc[MODE == kFxBalancedLogit ? 32 : 4];      // complement sums (logit link only)
+            float partc[MODE == kFxBalancedLogit ? 32 : 1];      // complement sums (logit link only)
 #pragma unroll
             for (int mi = 0; mi < 32; ++mi) part[mi] = 0.f;
 #pragma unroll
-            for (int mi = 0; mi < (MODE == kFxBalancedLogit ? 32 : 4); ++mi) partc[mi] = 0.f;
+            for (int mi = 0; mi < (MODE == kFxBalancedLogit ? 32 : 1); ++mi) partc[mi] = 0.f;
             const float4* op = reinterpret_cast<const float4*>(p.eoff + tile * 128 + cg * 32);
             for (int c = 0; c < p.n_chunks; ++c, ++j) {
                 const int es = j & 1;
@@ -306,8 +324,10 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
                     t4[1] = fminf(fmaxf(__uint_as_float(rr[1]) + o.y, -126.f), 126.f);
                     t4[2] = fminf(fmaxf(__uint_as_float(rr[2]) + o.z, -126.f), 126.f);
                     t4[3] = fminf(fmaxf(__uint_as_float(rr[3]) + o.w, -126.f), 126.f);
-                    chunk_sum4<MODE>(eb + (size_t)g4 * 4 * cbs, cbs, cbw >> 2, cbw & 3, t4, part + 4 * g4,
-                                     partc + (MODE == kFxBalancedLogit ? 4 * g4 : 0));
+                    if (MODE == kFxBalancedLogit)
+                        chunk_sum4_logit(eb + (size_t)g4 * 4 * cbs, cbs, cbw >> 2, cbw & 3, t4, part + 4 * g4, partc + (MODE == kFxBalancedLogit ? 4 * g4 : 0));
+                    else
+                        chunk_sum4<MODE>(eb + (size_t)g4 * 4 * cbs, cbs, cbw >> 2, cbw & 3, t4, part + 4 * g4);
                 }
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(&bars->e_empty[es]);
@@ -352,7 +372,8 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
                     for (int jj = 0; jj < 16; ++jj) gq[jj] = 0.f;
 #pragma unroll
                     for (int mi = 0; mi < 32; ++mi) {
-                        const float yv = fdb_kshap_link(part[mi], p.link) - p.lnull;
+                        // the link is a property of the instantiation (modes 1 and 3 serve the logit link): no dead logit code in the others
+                        const float yv = fdb_kshap_link(part[mi], (MODE == kFxClampedPairs || MODE == kFxBalancedLogit) ? 1 : 0) - p.lnull;
                         const float4 x0 = __ldg(xwp + mi * 8 + half * 4), x1 = __ldg(xwp + mi * 8 + half * 4 + 1);
                         const float4 x2 = __ldg(xwp + mi * 8 + half * 4 + 2), x3 = __ldg(xwp + mi * 8 + half * 4 + 3);
                         gq[0] = fmaf(x0.x, yv, gq[0]); gq[1] = fmaf(x0.y, yv, gq[1]); gq[2] = fmaf(x0.z, yv, gq[2]); gq[3] = fmaf(x0.w, yv, gq[3]);

@@ -59,7 +59,6 @@ struct TcParams {
     int n_rows, n_sets, tiles, m_pad;
     int n_bg, nb_pad, nsplit, fmt;
     int n_chunks, chunk_cols;
-    int wide;                                  // logit link: sigmoid AND complement sums, stored value encoded (fdb_kshap_encode_ey)
     float inv_bg;
 };
 
@@ -126,12 +125,11 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity
 // n_ab = d_a + d_b, p_ab = d_a d_b.  t is clamped to 30 so the product of four d stays below 2^121;
 // the clamp changes a sigmoid by < 1e-9 absolute.  Masked columns (beyond the background) are pinned at the
 // clamp, where the sigmoid is 1 / (1 + 2^30), and that known amount is subtracted again (no cancellation).
-template <bool MASKED, bool WIDE>
+// (Identity link; the logit link uses sigmoid_and_complement_sums16 below.)
+template <bool MASKED>
 __device__ __forceinline__ float sigmoid_sum16(const uint32_t (&r)[16], int nvalid) {
-    // WIDE (logit link): sigmoids down to ~1e-19 must keep their relative accuracy because logit(ey) is taken
-    // afterwards, so only TWO sigmoids share a reciprocal and the clamp moves to 62 (d0 d1 < 2^125).
-    constexpr float kClamp = WIDE ? 62.f : 30.f;
-    constexpr float kFloor = WIDE ? 2.16840434e-19f : 9.31322574e-10f;   // sigmoid at the clamp, 1 / (1 + 2^clamp)
+    constexpr float kClamp = 30.f;
+    constexpr float kFloor = 9.31322574e-10f;   // sigmoid at the clamp, 1 / (1 + 2^clamp)
     float sum = 0.f;
 #pragma unroll
     for (int q = 0; q < 16; q += 4) {
@@ -146,20 +144,14 @@ __device__ __forceinline__ float sigmoid_sum16(const uint32_t (&r)[16], int nval
         }
         const float n01 = d[0] + d[1], p01 = d[0] * d[1];
         const float n23 = d[2] + d[3], p23 = d[2] * d[3];
-        if (WIDE) {
-            sum = fmaf(n01, ptx::rcp_approx(p01), sum);
-            sum = fmaf(n23, ptx::rcp_approx(p23), sum);
-        } else {
-            const float num = fmaf(n01, p23, n23 * p01);
-            sum = fmaf(num, ptx::rcp_approx(p01 * p23), sum);
-        }
+        const float num = fmaf(n01, p23, n23 * p01);
+        sum = fmaf(num, ptx::rcp_approx(p01 * p23), sum);
     }
     return MASKED ? sum - (float)(((nvalid + 3) & ~3) - nvalid) * kFloor : sum;   // masked columns of the last quad sit at the clamp; take them out again
 }
 
-template <bool WIDE>
 __device__ __forceinline__ float sigmoid_group(const uint32_t (&r)[16], int nvalid) {
-    return nvalid >= 16 ? sigmoid_sum16<false, WIDE>(r, 16) : sigmoid_sum16<true, WIDE>(r, nvalid);
+    return nvalid >= 16 ? sigmoid_sum16<false>(r, 16) : sigmoid_sum16<true>(r, nvalid);
 }
 
 // Logit link: sum of the sigmoids AND of their complements over up to 16 accumulator columns, two columns per
@@ -187,7 +179,7 @@ __device__ __forceinline__ void sigmoid_and_complement_sums16(const uint32_t (&r
 }
 
 // smem carve-up (dynamic): [B image][A stages x pipes][Bq stages x pipes][barriers]
-template <bool FROM_BITS>
+template <bool FROM_BITS, bool WIDE>
 __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     const uint32_t b_bytes = (uint32_t)p.nsplit * p.nb_pad * 64;
@@ -383,18 +375,18 @@ __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcPa
                     ptx::tmem_ld_wait();
                     if (gi + 1 < ngroups) ptx::tmem_ld16(ta + (gi + 1) * 16, rb);
                     else release_tmem(&pb.t_empty[buf], lane);
-                    if (p.wide) sigmoid_and_complement_sums16(ra, valid - gi * 16, acc, comp);
-                    else acc += sigmoid_group<false>(ra, valid - gi * 16);
+                    if (WIDE) sigmoid_and_complement_sums16(ra, valid - gi * 16, acc, comp);
+                    else acc += sigmoid_group(ra, valid - gi * 16);
                     if (gi + 1 < ngroups) {
                         ptx::tmem_ld_wait();
                         if (gi + 2 < ngroups) ptx::tmem_ld16(ta + (gi + 2) * 16, ra);
                         else release_tmem(&pb.t_empty[buf], lane);
-                        if (p.wide) sigmoid_and_complement_sums16(rb, valid - (gi + 1) * 16, acc, comp);
-                        else acc += sigmoid_group<false>(rb, valid - (gi + 1) * 16);
+                        if (WIDE) sigmoid_and_complement_sums16(rb, valid - (gi + 1) * 16, acc, comp);
+                        else acc += sigmoid_group(rb, valid - (gi + 1) * 16);
                     }
                 }
             }
-            p.ey[(size_t)row * p.m_pad + tile * 128 + qd * 32 + lane] = p.wide ? fdb_kshap_encode_ey(acc, comp, p.inv_bg) : acc * p.inv_bg;
+            p.ey[(size_t)row * p.m_pad + tile * 128 + qd * 32 + lane] = WIDE ? fdb_kshap_encode_ey(acc, comp, p.inv_bg) : acc * p.inv_bg;
         }
     }
 
@@ -417,22 +409,26 @@ int fdb_kshap_launch_eval_tc(fdb_kshap_plan* pl, cudaStream_t st, const float* x
     p.n_chunks = (pl->nb_pad + kBufCols - 1) / kBufCols;
     p.chunk_cols = kBufCols;
     p.inv_bg = 1.0f / (float)pl->n_bg;
-    p.wide = pl->link == 1;
     const size_t smem = (size_t)pl->nsplit * pl->nb_pad * 64 + kPipes * kAStages * (kATileBytes + kBqBytes) + sizeof(TcBars) + 64;
     FDB_REQUIRE(smem <= 227 * 1024, FDB_ERR_ARG, "background of %d rows with %d operand splits needs %zu bytes of shared memory",
                 pl->n_bg, pl->nsplit, smem);
     static size_t configured[FDB_MAX_DEVICES] = {};        // function attributes are per device
     if (smem > configured[pl->ctx->device]) {
-        FDB_CUDA(cudaFuncSetAttribute(kshap_eval_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        FDB_CUDA(cudaFuncSetAttribute(kshap_eval_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        FDB_CUDA(cudaFuncSetAttribute(kshap_eval_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        FDB_CUDA(cudaFuncSetAttribute(kshap_eval_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        FDB_CUDA(cudaFuncSetAttribute(kshap_eval_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        FDB_CUDA(cudaFuncSetAttribute(kshap_eval_tc_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured[pl->ctx->device] = smem;
     }
     const int64_t n_items = (int64_t)n_rows * p.tiles;
     int64_t grid = (n_items + kPipes - 1) / kPipes;
     if (grid > pl->ctx->sm_count) grid = pl->ctx->sm_count;
     if (grid < 1) grid = 1;
-    if (pl->d_aimg != nullptr) kshap_eval_tc_kernel<false><<<(int)grid, kThreadsTc, smem, st>>>(p);
-    else kshap_eval_tc_kernel<true><<<(int)grid, kThreadsTc, smem, st>>>(p);
+    const bool from_bits = pl->d_aimg == nullptr, wide = pl->link == 1;
+    if (!from_bits && !wide) kshap_eval_tc_kernel<false, false><<<(int)grid, kThreadsTc, smem, st>>>(p);
+    else if (from_bits && !wide) kshap_eval_tc_kernel<true, false><<<(int)grid, kThreadsTc, smem, st>>>(p);
+    else if (!from_bits) kshap_eval_tc_kernel<false, true><<<(int)grid, kThreadsTc, smem, st>>>(p);
+    else kshap_eval_tc_kernel<true, true><<<(int)grid, kThreadsTc, smem, st>>>(p);
     FDB_CUDA(cudaGetLastError());
     return FDB_OK;
 }
