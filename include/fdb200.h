@@ -16,7 +16,9 @@
  *   - "_dev" entry points take DEVICE pointers and a cudaStream_t passed as void*
  *     (NULL = legacy default stream); they enqueue work and return without synchronising;
  *   - "_host" entry points take HOST pointers (pinned or pageable), run the
- *     H2D -> kernel -> D2H pipeline themselves and return when the outputs are complete;
+ *     H2D -> kernel -> D2H pipeline themselves and return when the outputs are complete
+ *     (up to 16,384 rows without any copy command: the kernel works on a mapped, page-locked
+ *     staging buffer; FDB_ZERO_COPY_ROWS=0 in the environment restores the copies);
  *   - matrices are row-major, 30 features per row (Time, V1..V28, Amount);
  *   - dtype: FDB_F32 or FDB_F64 selects the element type of every x / out / phi / proba
  *     buffer of that call (parameters are always passed as host doubles).
@@ -114,7 +116,8 @@ int fdb_linear_pass_host(fdb_ctx* ctx, int dtype, int64_t n_rows, const void* x,
  * is the Shapley-kernel weight (maskMatrix / kernelWeights of the reference run).  With
  * n_sets == 1 all rows share the set; otherwise row r uses set set_idx[r] (or r mod n_sets
  * when set_idx is NULL), which reproduces the reference's per-row sampling.
- * link: 0 identity, 1 logit.  evaluator: FDB_KSHAP_EVAL_TC (tcgen05 tensor cores, any plan),
+ * link: 0 identity, 1 logit (the evaluators then also sum the complements 1 - f, so that
+ * logit(ey) stays exact to float32 for expectations arbitrarily close to 0 or 1).  evaluator: FDB_KSHAP_EVAL_TC (tcgen05 tensor cores, any plan),
  * FDB_KSHAP_EVAL_FACTORED (single-set plans only: background part of every coalition is
  * precomputed, one exponential per (row, coalition)), FDB_KSHAP_EVAL_SIMT (plain fp32 CUDA
  * cores; the cross-check) or FDB_KSHAP_EVAL_AUTO (FACTORED for single-set plans, else TC).
