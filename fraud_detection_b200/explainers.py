@@ -378,6 +378,27 @@ class B200KernelExplainer:
         out[rows] = phi
         return out[0] if single else out
 
+    @staticmethod
+    def _varying_layout(v):
+        """For the sorted indices ``v`` of the varying features: (perm, pos, mask).  ``perm`` swaps the last varying
+        feature with feature 29 (column j of the permuted problem is original column perm[j]); the j-th varying
+        feature sits at bit ``pos[j]`` of the 30-bit coalition words; ``mask`` has those bits set."""
+        v = np.asarray(v, dtype=np.int64)
+        perm = np.arange(N_FEATURES)
+        perm[[v[-1], N_FEATURES - 1]] = perm[[N_FEATURES - 1, v[-1]]]
+        pos = v.copy()
+        pos[-1] = N_FEATURES - 1
+        return perm, pos, int(np.bitwise_or.reduce(np.uint32(1) << pos.astype(np.uint32)))
+
+    @staticmethod
+    def _spread_bits(bits, pos):
+        """Coalition words over M varying features (bit j = j-th varying feature) -> 30-bit words (bit pos[j])."""
+        b = np.asarray(bits, dtype=np.uint32)
+        out = np.zeros_like(b)
+        for j, pz in enumerate(pos):
+            out |= ((b >> np.uint32(j)) & np.uint32(1)) << np.uint32(pz)
+        return out
+
     def _explain_partial(self, A, varying, part, host_sets, shared_set, num_features, evaluator, out):
         """Rows where 2..29 features differ from the background (shap: M = len(varyingInds) < 30): coalitions are
         drawn over the M varying features, the others get phi = 0.  Rows are grouped by their varying pattern;
@@ -387,19 +408,9 @@ class B200KernelExplainer:
         for pat in np.unique(packed, axis=0):
             grp = part[(packed == pat).all(1)]
             v = np.nonzero(varying[grp[0]])[0]
-            perm = np.arange(N_FEATURES)
-            perm[[v[-1], N_FEATURES - 1]] = perm[[N_FEATURES - 1, v[-1]]]
-            pos = v.copy()
-            pos[-1] = N_FEATURES - 1                     # j-th varying feature -> bit pos[j] of the 30-bit coalition word
-            vmask = int(np.bitwise_or.reduce(np.uint32(1) << pos.astype(np.uint32)))
+            perm, pos, vmask = self._varying_layout(v)
             sets = [shared_set(len(v))] if host_sets is None else [host_sets[int(r)] for r in grp]
-            spread = []
-            for b, w in sets:
-                b = np.asarray(b, dtype=np.uint32)
-                b30 = np.zeros_like(b)
-                for j, pz in enumerate(pos):
-                    b30 |= ((b >> np.uint32(j)) & np.uint32(1)) << np.uint32(pz)
-                spread.append((b30, np.asarray(w)))
+            spread = [(self._spread_bits(b, pos), np.asarray(w)) for b, w in sets]
             bits, kw = self._pad_sets(spread)
             plan = KernelShapPlan(self.coef[perm], self.intercept, self.data[:, perm], bits, kw, self.link, self.device,
                                   varying_mask=vmask)
