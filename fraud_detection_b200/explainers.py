@@ -245,8 +245,9 @@ class B200KernelExplainer:
     ``masks=(Z, kw)`` or a list of per-row pairs feeds exported reference masks instead.
     ``sampler="device"`` draws the coalition sets on the GPU (same schedule, Philox stream: statistically but
     not bitwise equivalent to shap; ~5 orders of magnitude faster than the Python sampler).
-    ``l1_reg=False`` (plain WLS over all features) and ``l1_reg="num_features(k)"`` (shap's recalled default
-    is k = 10: LARS feature selection on the augmented system, then WLS over the selected features) run on the GPU.
+    ``l1_reg`` defaults to ``"num_features(10)"`` like the pinned shap release [recalled]: LARS feature selection on
+    the augmented system, then WLS over the 10 selected features, the other 20 get 0.  ``l1_reg=False`` is the
+    plain WLS over all features (BASELINE.json's parity configuration).  Both run on the GPU.
     """
 
     def __init__(self, model, data, link="identity", device=None, keep_index=False, **kwargs):
@@ -289,7 +290,7 @@ class B200KernelExplainer:
             kw[i, :len(w)] = w
         return bits, kw
 
-    def shap_values(self, X, nsamples="auto", l1_reg=False, mask_mode="per_row", masks=None, evaluator=EVAL_AUTO,
+    def shap_values(self, X, nsamples="auto", l1_reg="num_features(10)", mask_mode="per_row", masks=None, evaluator=EVAL_AUTO,
                     random=None, silent=True, sampler="host", seed=0, **kwargs):
         from . import sampler as _sampler
         num_features = 0

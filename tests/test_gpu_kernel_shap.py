@@ -230,10 +230,10 @@ def test_explainer_class_matches_oracle_with_same_seed(params):
     phi = expl.shap_values(X, nsamples=2048, l1_reg=False, random=np.random.RandomState(7))
     phi_ref = ks.shap_values(f, X, bg, nsamples=2048, l1_reg=False, random=np.random.RandomState(7))
     _check_phi(phi, phi_ref, f, X, expl.expected_value)
-    one = expl.shap_values(X[0], nsamples=2048, random=np.random.RandomState(7))
+    one = expl.shap_values(X[0], nsamples=2048, random=np.random.RandomState(7), l1_reg=False)
     assert one.shape == (30,)
     np.testing.assert_allclose(one, phi[0], atol=1e-6)      # one set -> factored evaluator, five sets -> general one
-    shared = expl.shap_values(X, nsamples=2048, mask_mode="shared", random=np.random.RandomState(8))
+    shared = expl.shap_values(X, nsamples=2048, mask_mode="shared", random=np.random.RandomState(8), l1_reg=False)
     np.testing.assert_allclose(shared.sum(1) + expl.expected_value, f(X), atol=1e-5)
     with pytest.raises(NotImplementedError):
         expl.shap_values(X, l1_reg="aic")
@@ -273,6 +273,8 @@ def test_num_features_end_to_end_vs_oracle(params):
     bg, X, f = _setup(params, 100, 16, seed=13)
     expl = B200KernelExplainer((params.coef, params.intercept), bg)
     phi = expl.shap_values(X, nsamples=2048, l1_reg="num_features(10)", random=np.random.RandomState(3))
+    # ... which is also what a call without l1_reg does, like the pinned shap release
+    np.testing.assert_array_equal(expl.shap_values(X, nsamples=2048, random=np.random.RandomState(3)), phi)
     ref = ks.shap_values(f, X, bg, nsamples=2048, l1_reg="num_features(10)", random=np.random.RandomState(3))
     agree = [np.array_equal(a != 0, b != 0) for a, b in zip(phi, ref)]
     assert sum(agree) >= len(X) - 1
@@ -288,7 +290,7 @@ def test_degenerate_rows_and_errors(params):
     expl = B200KernelExplainer((params.coef, params.intercept), bg)
     f = lambda A: scoring.predict_proba(params, A)[:, 1]  # noqa: E731
     x1 = bg[0].copy(); x1[3] += 1.0
-    phi = expl.shap_values(np.stack([bg[0], x1]), nsamples=256)
+    phi = expl.shap_values(np.stack([bg[0], x1]), nsamples=256, l1_reg=False)
     assert np.all(phi[0] == 0) and np.count_nonzero(phi[1]) == 1
     np.testing.assert_allclose(phi[1, 3], f(x1[None])[0] - f(bg).mean(), atol=1e-12)
     # too few coalitions -> singular normal matrix -> ValueError at plan creation, like shap's LinAlgError path
@@ -337,7 +339,7 @@ def test_rows_where_only_some_features_vary(params, n_bg, link):
     counts = [len(ks.varying_features(x, bg)) for x in X]
     assert min(counts) <= 5 and any(5 < c < 30 for c in counts)
     expl = B200KernelExplainer((params.coef, params.intercept), bg, link=link)
-    phi = expl.shap_values(X, nsamples=1024, random=np.random.RandomState(5))
+    phi = expl.shap_values(X, nsamples=1024, random=np.random.RandomState(5), l1_reg=False)
     rs = np.random.RandomState(5)
     ref, ey_max = [], []
     for x in X:
@@ -362,7 +364,7 @@ def test_rows_where_only_some_features_vary(params, n_bg, link):
             if 2 <= counts[r] <= 9:
                 np.testing.assert_allclose(phi[r], ks.exact_shapley(f, x, bg, ks.varying_features(x, bg)), atol=2e-6)
     # one coalition set shared by the rows of each pattern
-    shared = expl.shap_values(X, nsamples=1024, mask_mode="shared", random=np.random.RandomState(6))
+    shared = expl.shap_values(X, nsamples=1024, mask_mode="shared", random=np.random.RandomState(6), l1_reg=False)
     np.testing.assert_allclose(shared.sum(1) + expl.expected_value, lf(f(X)), atol=2e-5 if link == "logit" else 1e-5)
     np.testing.assert_allclose(shared[7], phi[7], atol=5e-3 * np.abs(phi[7]).max() + 1e-6)
 
@@ -466,16 +468,16 @@ def test_explainer_with_device_sampler_is_statistically_the_same(params):
     from fraud_detection_b200 import B200KernelExplainer
     bg, X, f = _setup(params, 100, 6, seed=22)
     expl = B200KernelExplainer((params.coef, params.intercept), bg)
-    dev = expl.shap_values(X, nsamples=2048, sampler="device", seed=11)
-    h1 = expl.shap_values(X, nsamples=2048, random=np.random.RandomState(1))
-    h2 = expl.shap_values(X, nsamples=2048, random=np.random.RandomState(2))
+    dev = expl.shap_values(X, nsamples=2048, sampler="device", seed=11, l1_reg=False)
+    h1 = expl.shap_values(X, nsamples=2048, random=np.random.RandomState(1), l1_reg=False)
+    h2 = expl.shap_values(X, nsamples=2048, random=np.random.RandomState(2), l1_reg=False)
     np.testing.assert_allclose(dev.sum(1) + expl.expected_value, f(X), atol=1e-5)
     spread = np.abs(h1 - h2).max() + 1e-4
     assert np.abs(dev - h1).max() < 4 * spread
-    shared = expl.shap_values(X, nsamples=2048, sampler="device", mask_mode="shared", seed=11)
+    shared = expl.shap_values(X, nsamples=2048, sampler="device", mask_mode="shared", seed=11, l1_reg=False)
     np.testing.assert_allclose(shared.sum(1) + expl.expected_value, f(X), atol=1e-5)
     with pytest.raises(ValueError, match="64 <= nsamples <= 4096"):
-        expl.shap_values(X, nsamples=100000, sampler="device")
+        expl.shap_values(X, nsamples=100000, sampler="device", l1_reg=False)
 
 
 def test_bf16_three_term_operands(params, monkeypatch):
@@ -550,8 +552,8 @@ def test_resample_in_place(params):
     host_plan.close()
     # the explainer keeps its device plan across calls and draws new coalitions each time (like shap does per call)
     expl = B200KernelExplainer((params.coef, params.intercept), bg)
-    a = expl.shap_values(X[0], nsamples=2048, sampler="device", seed=5)
-    b = expl.shap_values(X[0], nsamples=2048, sampler="device", seed=5)
+    a = expl.shap_values(X[0], nsamples=2048, sampler="device", seed=5, l1_reg=False)
+    b = expl.shap_values(X[0], nsamples=2048, sampler="device", seed=5, l1_reg=False)
     assert len(expl._device_plans) == 1 and not np.array_equal(a, b)
     np.testing.assert_allclose(a.sum() + expl.expected_value, f(X[:1])[0], atol=1e-5)
     np.testing.assert_allclose(b.sum() + expl.expected_value, f(X[:1])[0], atol=1e-5)
@@ -588,6 +590,6 @@ def test_golden_vectors(params, evaluator):
     plan.close()
     if evaluator == TC:
         expl = B200KernelExplainer((params.coef, params.intercept), g["vary_background"])
-        pv = expl.shap_values(g["vary_x"], nsamples="auto", random=np.random.RandomState(1))
+        pv = expl.shap_values(g["vary_x"], nsamples="auto", random=np.random.RandomState(1), l1_reg=False)
         assert np.all(np.abs(pv - g["vary_phi"]) <= 1e-4 * np.abs(g["vary_phi"]).max() + 1e-8)
         assert np.nonzero(pv)[0].tolist() == g["vary_features"].tolist()
