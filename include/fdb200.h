@@ -117,7 +117,8 @@ int fdb_linear_pass_host(fdb_ctx* ctx, int dtype, int64_t n_rows, const void* x,
  * n_sets == 1 all rows share the set; otherwise row r uses set set_idx[r] (or r mod n_sets
  * when set_idx is NULL), which reproduces the reference's per-row sampling.
  * link: 0 identity, 1 logit (the evaluators then also sum the complements 1 - f, so that
- * logit(ey) stays exact to float32 for expectations arbitrarily close to 0 or 1).  evaluator: FDB_KSHAP_EVAL_TC (tcgen05 tensor cores, any plan),
+ * logit(ey) stays exact to float32 for expectations arbitrarily close to 0 or 1).
+ * evaluator: FDB_KSHAP_EVAL_TC (tcgen05 tensor cores, any plan),
  * FDB_KSHAP_EVAL_FACTORED (single-set plans only: background part of every coalition is
  * precomputed, one exponential per (row, coalition)), FDB_KSHAP_EVAL_SIMT (plain fp32 CUDA
  * cores; the cross-check) or FDB_KSHAP_EVAL_AUTO (FACTORED for single-set plans, else TC).
@@ -125,6 +126,10 @@ int fdb_linear_pass_host(fdb_ctx* ctx, int dtype, int64_t n_rows, const void* x,
  * sum_k phi[r][k] = link(f(x_r)) - expected_value exactly by construction; ey_out
  * (optional, n_rows x n_masks) returns the coalition expectations; abs_sum as in K1b.
  * A singular X'WX (too few coalitions) makes plan creation fail with FDB_ERR_ARG.
+ * A plan owns its scratch (coalition expectations of the batch in flight): explain calls on the
+ * SAME plan must not overlap on the GPU; use one plan per stream for concurrent work.  Memory per
+ * coalition set: 8 bytes per coalition + 3.8 KB (a 64-byte-per-coalition operand image is kept for
+ * single-set plans only).
  * ------------------------------------------------------------------------------- */
 typedef struct fdb_kshap_plan fdb_kshap_plan;
 enum { FDB_KSHAP_EVAL_AUTO = -1, FDB_KSHAP_EVAL_TC = 0, FDB_KSHAP_EVAL_SIMT = 1, FDB_KSHAP_EVAL_FACTORED = 2 };
