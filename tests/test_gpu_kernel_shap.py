@@ -408,6 +408,7 @@ def test_device_sampler_follows_the_reference_schedule(params):
     wv, _, n_paired = sampler.size_weights(30)
     seen_sets = set()
     size_hist = np.zeros(31)
+    member_count, member_total = np.zeros(30), 0
     for s in range(n_sets):
         bits, kw = plan.masks(s)
         # enumerated block: identical to the host schedule (30 singletons + complements, weight 4.352e-3)
