@@ -87,11 +87,18 @@ __global__ void __launch_bounds__(32) kshap_wls_prepare(const uint32_t* __restri
         if (i == lane && !((varying >> lane) & 1u)) a[i] = 1.0;
         if (lane >= kNV) a[i] = 0.0;
     }
+    // A pivot that has lost 11 digits against its own diagonal entry means X'WX is singular to working precision
+    // (too few or linearly dependent coalitions): report it instead of returning an inverse made of rounding noise.
+    double diag0 = 0.0;
+#pragma unroll
+    for (int i = 0; i < kNV; ++i)
+        if (i == lane) diag0 = a[i];
     bool singular = false;
 #pragma unroll
     for (int k = 0; k < kNV; ++k) {
         const double pk = __shfl_sync(0xffffffffu, a[k], k);          // A[k][k]
-        if (!(fabs(pk) > 1e-300)) { singular = true; break; }
+        const double dk = __shfl_sync(0xffffffffu, diag0, k);
+        if (!(pk > 1e-11 * dk) || !(pk > 1e-300)) { singular = true; break; }
         const double r = 1.0 / pk;
         const double ak = a[k] * r, ik = inv[k] * r;                    // pivot row, scaled: elements (k, lane)
 #pragma unroll

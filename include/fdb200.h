@@ -125,7 +125,8 @@ int fdb_linear_pass_host(fdb_ctx* ctx, int dtype, int64_t n_rows, const void* x,
  * explain: x is n_rows x 30 float32; phi is n_rows x 30 float32 with
  * sum_k phi[r][k] = link(f(x_r)) - expected_value exactly by construction; ey_out
  * (optional, n_rows x n_masks) returns the coalition expectations; abs_sum as in K1b.
- * A singular X'WX (too few coalitions) makes plan creation fail with FDB_ERR_ARG.
+ * A singular X'WX (too few or dependent coalitions: a pivot that lost 11 digits against its diagonal
+ * entry) makes plan creation fail with FDB_ERR_ARG.
  * A plan owns its scratch (coalition expectations of the batch in flight): explain calls on the
  * SAME plan must not overlap on the GPU; use one plan per stream for concurrent work.  Memory per
  * coalition set: 8 bytes per coalition + 3.8 KB (a 64-byte-per-coalition operand image is kept for

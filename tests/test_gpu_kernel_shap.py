@@ -594,3 +594,45 @@ def test_golden_vectors(params, evaluator):
         pv = expl.shap_values(g["vary_x"], nsamples="auto", random=np.random.RandomState(1), l1_reg=False)
         assert np.all(np.abs(pv - g["vary_phi"]) <= 1e-4 * np.abs(g["vary_phi"]).max() + 1e-8)
         assert np.nonzero(pv)[0].tolist() == g["vary_features"].tolist()
+
+
+@pytest.mark.parametrize("nsamples", ["auto", 4096, 300, 64])
+def test_device_sampler_sizes(params, nsamples):
+    """Both shared-memory layouts of the sampler (<= 2048 and <= 4096 coalitions), budgets below the first enumerated
+    size, and shap's default budget ("auto" = 2 * 30 + 2048)."""
+    from fraud_detection_b200 import KernelShapPlan, sampler
+    bg, X, f = _setup(params, 50, 6, seed=61)
+    if nsamples == 64:
+        # 64 coalitions (32 draws and their complements) for 29 unknowns: some of the six sets are singular to working
+        # precision; the plan must say so instead of explaining rows with an inverse made of rounding noise
+        try:
+            plan = KernelShapPlan.sampled(params.coef, params.intercept, bg, len(X), nsamples, seed=61)
+        except ValueError as exc:
+            assert "singular" in str(exc)
+            return
+    else:
+        plan = KernelShapPlan.sampled(params.coef, params.intercept, bg, len(X), nsamples, seed=61)
+    want = sampler.resolve_nsamples(30, nsamples)
+    assert plan.n_masks == want
+    host_bits, host_kw = sampler.sample_coalitions(30, nsamples, np.random.RandomState(0))
+    n_fixed = int(np.sum(np.isclose(host_kw, host_kw[0]))) if want >= 230 else 0     # the enumerated block, if any
+    for s in range(len(X)):
+        bits, kw = plan.masks(s)
+        used = kw > 0
+        assert len(np.unique(bits[used])) == int(used.sum())
+        assert int(used.sum()) == want or int(used.sum()) >= want - 1
+        np.testing.assert_allclose(kw.sum(), 1.0, rtol=1e-5)
+        if n_fixed:
+            assert np.array_equal(bits[:60], host_bits[:60])
+    x = torch.from_numpy(np.ascontiguousarray(X, dtype=np.float32)).cuda()
+    phi = plan.explain_dev(x)
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(phi.double().sum(1).cpu().numpy() + plan.expected_value, f(X), atol=1e-5)
+    # exported sets, fed to the oracle: same phi
+    for s in (0, len(X) - 1):
+        bits, kw = plan.masks(s)
+        Z = sampler.bits_to_masks(bits)
+        ref = ks.solve(Z, kw.astype(np.float64), ks.evaluate(f, X[s], bg, Z), float(f(X[s:s + 1])[0]), float(f(bg).mean()))
+        got = phi[s].cpu().numpy().astype(np.float64)
+        assert np.all(np.abs(got - ref) <= 1e-4 * np.abs(ref).max() + 1e-8)
+    plan.close()
