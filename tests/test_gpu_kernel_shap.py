@@ -636,3 +636,51 @@ def test_device_sampler_sizes(params, nsamples):
         got = phi[s].cpu().numpy().astype(np.float64)
         assert np.all(np.abs(got - ref) <= 1e-4 * np.abs(ref).max() + 1e-8)
     plan.close()
+
+
+def test_several_sets_across_batches(params):
+    """Row r uses set r mod n_sets, also when the rows span several evaluate->solve batches (32,768 rows each) and
+    when the same rows arrive through the host entry point or in two separate calls with explicit set indices."""
+    bg, X, f = _setup(params, 20, 70_001, seed=71)
+    sets = [ks.sample_coalitions(30, 128, np.random.RandomState(71 + i))[:2] for i in range(3)]
+    plan = _plan(params, bg, sets)
+    x = torch.from_numpy(np.ascontiguousarray(X, dtype=np.float32)).cuda()
+    phi = plan.explain_dev(x).clone()
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(phi.double().sum(1).cpu().numpy() + plan.expected_value, f(X), atol=1e-5)
+    # explicit indices, two calls that split the rows at a place that is no batch boundary
+    idx = torch.arange(len(X), device="cuda", dtype=torch.int32) % 3
+    a = plan.explain_dev(x[:40_003], set_idx=idx[:40_003]).clone()
+    b = plan.explain_dev(x[40_003:].contiguous(), set_idx=idx[40_003:].contiguous()).clone()
+    torch.cuda.synchronize()
+    assert torch.equal(torch.cat([a, b]), phi)
+    host = plan.explain_host(np.ascontiguousarray(X, dtype=np.float32))
+    assert np.array_equal(host, phi.cpu().numpy())
+    fnull = float(f(bg).mean())
+    for r in (0, 32_767, 32_768, 32_769, 65_536, 70_000):
+        Z, kw = sets[r % 3]
+        ref = ks.solve(Z, kw, ks.evaluate(f, X[r], bg, Z), float(f(X[r:r + 1])[0]), fnull)
+        got = phi[r].cpu().numpy().astype(np.float64)
+        assert np.all(np.abs(got - ref) <= 1e-4 * np.abs(ref).max() + 1e-8), r
+    plan.close()
+
+
+def test_num_features_with_the_logit_link(params):
+    bg, X, f = _setup(params, 60, 24, seed=72)
+    Z, kw, _ = ks.sample_coalitions(30, 1024, np.random.RandomState(72))
+    plan = _plan(params, bg, [(Z, kw)], link="logit")
+    plan.set_num_features(6)
+    fnull = float(f(bg).mean())
+    lg = lambda v: np.log(v / (1 - v))  # noqa: E731
+    for ev in (TC, FX):
+        phi, ey, _ = _run(plan, X, ev)
+        same = 0
+        for i, x in enumerate(X):
+            ref = ks.solve(Z, kw, ey[i].astype(np.float64), float(f(x[None])[0]), fnull, link="logit", l1_reg="num_features(6)")
+            assert np.count_nonzero(phi[i]) <= 6
+            if np.array_equal(ref != 0, phi[i] != 0):
+                same += 1
+                assert np.all(np.abs(phi[i] - ref) <= 1e-4 * np.abs(ref).max() + 1e-7)
+        assert same >= len(X) - 1
+        np.testing.assert_allclose(phi.sum(1) + lg(fnull), lg(f(X)), atol=2e-4)
+    plan.close()
