@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(128) kshap_eval_simt(const float* __restrict__
     float sq = 0.f;
 #pragma unroll
     for (int k = 0; k < FDB_F; ++k) sq += ((b >> k) & 1u) ? q[k] : 0.f;
-    float acc = 0.f, comp = 0.f;
+    double acc = 0.0, comp = 0.0;          // (float64 running sums: a plain float32 sum over 1000 rows drifts by 1e-5)
     for (int j = 0; j < n_bg; ++j) {
         const float* pr = P + (size_t)j * 32;
         float g = pr[30];   // intercept
@@ -156,7 +156,7 @@ __global__ void __launch_bounds__(128) kshap_eval_simt(const float* __restrict__
         acc += 1.0f / (1.0f + expf(-(g + sq)));
         if (link == 1) comp += 1.0f / (1.0f + expf(g + sq));
     }
-    ey[(size_t)r * m_pad + m] = link == 1 ? fdb_kshap_encode_ey(acc, comp, 1.0f / (float)n_bg) : acc / (float)n_bg;
+    ey[(size_t)r * m_pad + m] = link == 1 ? fdb_kshap_encode_ey((float)(acc / n_bg), (float)(comp / n_bg), 1.0f) : (float)(acc / n_bg);
 }
 
 // ey_out: the caller's view of the coalition expectations (plain values, n_masks per row)

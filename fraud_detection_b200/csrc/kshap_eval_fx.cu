@@ -93,7 +93,9 @@ template <int MODE>
 __device__ __forceinline__ void chunk_sum4(const float* __restrict__ e0, int cbs, int nquads, int ntail,
                                            const float* __restrict__ t, float* __restrict__ acc) {
     constexpr float kClamp = MODE == kFxClampedPairs ? 4.611686018427388e18f : 1073741824.f;
-    float a[4], b[4];
+    // sums of this chunk are gathered apart and added to the running totals once: with ~1000 background rows a
+    // single float32 chain drifts by 1e-5 on saturated coalitions (every term 1, every add rounded the same way)
+    float a[4], b[4], sum[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int mm = 0; mm < 4; ++mm) {
         a[mm] = ptx::ex2_approx(MODE == kFxBalanced ? fminf(t[mm], 0.f) : t[mm]);
@@ -111,10 +113,10 @@ __device__ __forceinline__ void chunk_sum4(const float* __restrict__ e0, int cbs
             }
             const float n01 = d0 + d1, p01 = d0 * d1, n23 = d2 + d3, p23 = d2 * d3;
             if (MODE == kFxClampedPairs) {
-                acc[mm] = fmaf(n01, ptx::rcp_approx(p01), acc[mm]);
-                acc[mm] = fmaf(n23, ptx::rcp_approx(p23), acc[mm]);
+                sum[mm] = fmaf(n01, ptx::rcp_approx(p01), sum[mm]);
+                sum[mm] = fmaf(n23, ptx::rcp_approx(p23), sum[mm]);
             } else {
-                acc[mm] = fmaf(fmaf(n01, p23, n23 * p01), ptx::rcp_approx(p01 * p23), acc[mm]);
+                sum[mm] = fmaf(fmaf(n01, p23, n23 * p01), ptx::rcp_approx(p01 * p23), sum[mm]);
             }
         }
     }
@@ -122,14 +124,16 @@ __device__ __forceinline__ void chunk_sum4(const float* __restrict__ e0, int cbs
 #pragma unroll
         for (int mm = 0; mm < 4; ++mm) {
             const float d = fmaf(e0[mm * cbs + 4 * nquads + i], a[mm], b[mm]);
-            acc[mm] += ptx::rcp_approx(MODE == kFxBalanced ? d : fminf(d, kClamp));
+            sum[mm] += ptx::rcp_approx(MODE == kFxBalanced ? d : fminf(d, kClamp));
         }
+#pragma unroll
+    for (int mm = 0; mm < 4; ++mm) acc[mm] += sum[mm];
 }
 
 // MODE 3 body: sigmoid and complement sums for four coalitions over one background chunk (see the mode list above)
 __device__ __forceinline__ void chunk_sum4_logit(const float* __restrict__ e0, int cbs, int nquads, int ntail,
                                                  const float* __restrict__ t, float* __restrict__ acc, float* __restrict__ accc) {
-    float a[4], b[4];
+    float a[4], b[4], sum[4] = {0.f, 0.f, 0.f, 0.f}, sumc[4] = {0.f, 0.f, 0.f, 0.f};      // per-chunk sums, see chunk_sum4
 #pragma unroll
     for (int mm = 0; mm < 4; ++mm) {
         a[mm] = ptx::ex2_approx(fminf(t[mm], 0.f));
@@ -144,9 +148,9 @@ __device__ __forceinline__ void chunk_sum4_logit(const float* __restrict__ e0, i
             const float d0 = g0 + b[mm], d1 = g1 + b[mm], d2 = g2 + b[mm], d3 = g3 + b[mm];
             const float n01 = d0 + d1, p01 = d0 * d1, n23 = d2 + d3, p23 = d2 * d3;
             const float r = ptx::rcp_approx(p01 * p23);
-            acc[mm] = fmaf(fmaf(n01, p23, n23 * p01), r, acc[mm]);
+            sum[mm] = fmaf(fmaf(n01, p23, n23 * p01), r, sum[mm]);
             const float c01 = fmaf(g0, d1, g1 * d0), c23 = fmaf(g2, d3, g3 * d2);
-            accc[mm] = fmaf(fmaf(c01, p23, c23 * p01), r, accc[mm]);
+            sumc[mm] = fmaf(fmaf(c01, p23, c23 * p01), r, sumc[mm]);
         }
     }
     for (int i = 0; i < ntail; ++i)
@@ -154,9 +158,14 @@ __device__ __forceinline__ void chunk_sum4_logit(const float* __restrict__ e0, i
         for (int mm = 0; mm < 4; ++mm) {
             const float g = e0[mm * cbs + 4 * nquads + i] * a[mm];
             const float r = ptx::rcp_approx(g + b[mm]);
-            acc[mm] += r;
-            accc[mm] = fmaf(g, r, accc[mm]);
+            sum[mm] += r;
+            sumc[mm] = fmaf(g, r, sumc[mm]);
         }
+#pragma unroll
+    for (int mm = 0; mm < 4; ++mm) {
+        acc[mm] += sum[mm];
+        accc[mm] += sumc[mm];
+    }
 }
 
 #ifndef FDB_FX_SERVICE_SLEEP_NS

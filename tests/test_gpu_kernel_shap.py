@@ -65,7 +65,7 @@ def _check_phi(phi, phi_ref, f, X, expected, rel=1e-4, link=lambda v: v):
 
 
 @pytest.mark.parametrize("evaluator", [SIMT, TC, FX])
-@pytest.mark.parametrize("nsamples,n_bg", [(2048, 100), (256, 100), (100, 37), (2048, 1), (300, 130)])
+@pytest.mark.parametrize("nsamples,n_bg", [(2048, 100), (256, 100), (100, 37), (2048, 1), (300, 130), (8192, 64), (512, 1024)])
 def test_shared_masks_vs_oracle(params, evaluator, nsamples, n_bg):
     bg, X, f = _setup(params, n_bg, 12)
     Z, kw, _ = ks.sample_coalitions(30, nsamples, np.random.RandomState(0))
