@@ -115,7 +115,8 @@ int fdb_linear_pass_host(fdb_ctx* ctx, int dtype, int64_t n_rows, const void* x,
  * sets: bits[s][m] has bit k set when feature k takes the explained row's value, kw[s][m]
  * is the Shapley-kernel weight (maskMatrix / kernelWeights of the reference run).  With
  * n_sets == 1 all rows share the set; otherwise row r uses set set_idx[r] (or r mod n_sets
- * when set_idx is NULL), which reproduces the reference's per-row sampling.
+ * when set_idx is NULL), which reproduces the reference's per-row sampling.  set_idx lives on the
+ * device (explain_dev) and is not checked: every entry must lie in [0, n_sets).
  * link: 0 identity, 1 logit (the evaluators then also sum the complements 1 - f, so that
  * logit(ey) stays exact to float32 for expectations arbitrarily close to 0 or 1).
  * evaluator: FDB_KSHAP_EVAL_TC (tcgen05 tensor cores, any plan),

@@ -684,3 +684,23 @@ def test_num_features_with_the_logit_link(params):
         assert same >= len(X) - 1
         np.testing.assert_allclose(phi.sum(1) + lg(fnull), lg(f(X)), atol=2e-4)
     plan.close()
+
+
+def test_wide_background_limits(params, monkeypatch):
+    """1024 background rows is the stated maximum: it runs under both links; with three-term bf16 operands the
+    resident B image no longer fits shared memory and the tensor-core evaluator says so (the factored one still runs)."""
+    bg, X, f = _setup(params, 1024, 5, seed=81)
+    Z, kw, _ = ks.sample_coalitions(30, 256, np.random.RandomState(81))
+    phi_ref, _, fnull = _oracle_rows(f, X, bg, [(Z, kw)], link="logit")
+    plan = _plan(params, bg, [(Z, kw)], link="logit")
+    for ev in (TC, FX):
+        phi, _, _ = _run(plan, X, ev, want_ey=False)
+        assert np.all(np.abs(phi - phi_ref) <= 1e-4 * np.abs(phi_ref).max(1, keepdims=True) + 1e-7)
+    plan.close()
+    monkeypatch.setenv("FDB_KSHAP_FMT", "1")
+    plan = _plan(params, bg, [(Z, kw)])
+    with pytest.raises(Exception, match="shared memory"):
+        _run(plan, X, TC, want_ey=False)
+    phi, _, _ = _run(plan, X, FX, want_ey=False)
+    np.testing.assert_allclose(phi.sum(1) + plan.expected_value, f(X), atol=1e-5)
+    plan.close()
