@@ -704,3 +704,46 @@ def test_wide_background_limits(params, monkeypatch):
     phi, _, _ = _run(plan, X, FX, want_ey=False)
     np.testing.assert_allclose(phi.sum(1) + plan.expected_value, f(X), atol=1e-5)
     plan.close()
+
+
+@pytest.mark.parametrize("rows,nsamples", [(1, 100), (1, 128), (2, 129), (3, 2048)])
+def test_tiny_jobs_leave_pipelines_idle(params, rows, nsamples):
+    """Fewer (row, tile) items than the four pipelines of K2 / the SMs of K2f: idle pipelines must fall through."""
+    bg, X, f = _setup(params, 30, rows, seed=91)
+    Z, kw, _ = ks.sample_coalitions(30, nsamples, np.random.RandomState(91))
+    phi_ref, ey_ref, fnull = _oracle_rows(f, X, bg, [(Z, kw)])
+    plan = _plan(params, bg, [(Z, kw)])
+    for ev in (TC, FX, SIMT):
+        phi, ey, abs_sum = _run(plan, X, ev)
+        np.testing.assert_allclose(ey, ey_ref, rtol=0, atol=2e-6)
+        _check_phi(phi, phi_ref, f, X, fnull)
+        assert abs_sum[30] == rows
+    plan.close()
+
+
+def test_resample_keeps_feature_selection_consistent(params):
+    """A redrawn plan rebuilds everything derived from the coalition sets, including the Gram matrices of the
+    num_features(k) selection."""
+    from fraud_detection_b200 import KernelShapPlan, sampler
+    bg, X, f = _setup(params, 40, 6, seed=92)
+    plan = KernelShapPlan.sampled(params.coef, params.intercept, bg, len(X), 1024, seed=1)
+    plan.set_num_features(5)
+    x = torch.from_numpy(np.ascontiguousarray(X, dtype=np.float32)).cuda()
+    for seed in (2, 3):
+        plan.resample(seed)
+        ey = torch.empty((len(X), plan.n_masks), dtype=torch.float32, device="cuda")
+        phi = plan.explain_dev(x, ey=ey).cpu().numpy().astype(np.float64)
+        torch.cuda.synchronize()
+        fnull = float(f(bg).mean())
+        agree = 0
+        for r in range(len(X)):
+            bits, kw = plan.masks(r)
+            Z = sampler.bits_to_masks(bits)
+            ref = ks.solve(Z, kw.astype(np.float64), ey[r].cpu().numpy().astype(np.float64), float(f(X[r:r + 1])[0]), fnull,
+                           l1_reg="num_features(5)")
+            assert np.count_nonzero(phi[r]) <= 5
+            if np.array_equal(ref != 0, phi[r] != 0):
+                agree += 1
+                assert np.all(np.abs(phi[r] - ref) <= 1e-4 * np.abs(ref).max() + 1e-8)
+        assert agree >= len(X) - 1
+    plan.close()
