@@ -236,3 +236,49 @@ def test_host_entry_point_with_pinned_buffers(params):
     assert np.all(np.abs(out["phi"] - phi_ref) <= _phi_tol(phi_ref))
     np.testing.assert_allclose(out["abs_sum"][:30], np.abs(phi_ref).sum(0), rtol=1e-5)
     assert out["abs_sum"][30] == n
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("n", [16384, 16385, 3 * 262144 + 5])
+def test_host_entry_point_every_output_at_once(params, dtype, n):
+    """fdb_linear_pass_host straight through the C ABI with pageable buffers and every output requested: the
+    copy-free serving path (<= 16,384 rows) and the chunked pipeline (more) against the oracle."""
+    from fraud_detection_b200 import _lib
+    Xs = scoring.transform(params, synth.rows(n, seed=17)).astype(dtype)
+    mean_bg = Xs[:100].astype(np.float64).mean(0)
+    ev = float(params.coef @ mean_bg + params.intercept)
+    proba = np.empty((n, 2), dtype=dtype)
+    logit = np.empty(n, dtype=dtype)
+    phi = np.empty((n, 30), dtype=dtype)
+    cls = np.empty(n, dtype=np.uint8)
+    abs_sum = np.zeros(32)
+    _lib.check(_lib.lib.fdb_linear_pass_host(_lib.get_ctx(None), _lib.dtype_code(np.dtype(dtype)), n, _lib.np_ptr(Xs),
+                                             _lib.dvec(mean_bg), _lib.dvec(params.coef), ev, _lib.np_ptr(proba), 2,
+                                             _lib.np_ptr(logit), _lib.np_ptr(phi), _lib.np_ptr(cls), _lib.np_ptr(abs_sum)))
+    X64 = Xs.astype(np.float64)
+    z_ref = scoring.decision_function(params, X64)
+    p_ref = scoring.predict_proba(params, X64)
+    phi_ref = linear_shap.shap_values(params.coef, mean_bg, X64)
+    tol = 1e-12 if dtype == np.float64 else 1e-5
+    np.testing.assert_allclose(proba, p_ref, rtol=0, atol=tol)
+    np.testing.assert_allclose(logit, z_ref, rtol=0, atol=1e-11 if dtype == np.float64 else 2e-4)
+    assert np.all(np.abs(phi.astype(np.float64) - phi_ref) <= (1e-12 if dtype == np.float64 else _phi_tol(phi_ref)))
+    decided = np.abs(z_ref) > 1e-3
+    assert np.array_equal(cls[decided], (z_ref > 0)[decided].astype(np.uint8))
+    assert abs_sum[30] == n
+    np.testing.assert_allclose(abs_sum[:30], np.abs(phi_ref).sum(0), rtol=1e-9 if dtype == np.float64 else 1e-5)
+
+
+def test_serving_path_takes_unaligned_pinned_rows(params):
+    """Page-locked caller memory is read in place by the copy-free path - unless it is not 16-byte aligned."""
+    from fraud_detection_b200 import PinnedBuffer, _lib
+    n = 37
+    buf = PinnedBuffer((n * 30 + 2,), np.float64)
+    X = scoring.transform(params, synth.rows(n, seed=18))
+    for off in (0, 1):                              # 0: aligned, read in place; 1: 8-byte offset, staged
+        view = buf.array[off:off + n * 30].reshape(n, 30)
+        view[:] = X
+        p = np.empty(n)
+        _lib.check(_lib.lib.fdb_linear_pass_host(_lib.get_ctx(None), _lib.F64, n, _lib.np_ptr(view), None, _lib.dvec(params.coef),
+                                                 float(params.intercept), _lib.np_ptr(p), 1, None, None, None, None))
+        np.testing.assert_allclose(p, scoring.predict_proba(params, X)[:, 1], rtol=0, atol=1e-12)
