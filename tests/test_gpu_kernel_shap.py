@@ -747,3 +747,61 @@ def test_resample_keeps_feature_selection_consistent(params):
                 assert np.all(np.abs(phi[r] - ref) <= 1e-4 * np.abs(ref).max() + 1e-8)
         assert agree >= len(X) - 1
     plan.close()
+
+
+def test_evaluators_agree_on_many_shapes(params):
+    """A sweep over background sizes around every chunk boundary of the two tensor-core evaluators (64-column
+    accumulator buffers, 128-column E chunks, 16-column groups, quads), odd coalition counts and row counts, both
+    links: K2 and K2f against the plain SIMT evaluator (all on the device), plus additivity."""
+    from fraud_detection_b200 import KernelShapPlan, sampler
+    rs = np.random.RandomState(2025)
+    n_bgs = [1, 2, 3, 4, 5, 15, 16, 17, 31, 33, 63, 64, 65, 66, 79, 80, 81, 127, 128, 129, 130, 131, 191, 192, 193, 255, 256, 257, 383, 385, 511, 513]
+    f = lambda A: scoring.predict_proba(params, A)[:, 1]  # noqa: E731
+    lg = lambda v: np.log(v / (1 - v))  # noqa: E731
+    for i, n_bg in enumerate(n_bgs):
+        nsamples = int(rs.choice([230, 256, 257, 300, 383, 384, 385, 500, 640]))
+        rows = int(rs.choice([1, 2, 31, 32, 33, 127, 128, 129, 200]))
+        link = "logit" if i % 3 == 2 else "identity"
+        bg = scoring.transform(params, synth.rows(n_bg, seed=500 + i))
+        X = scoring.transform(params, synth.rows(rows, seed=900 + i))
+        bits, kw = sampler.sample_coalitions(30, nsamples, np.random.RandomState(i))
+        plan = KernelShapPlan(params.coef, params.intercept, bg, bits, kw, link)
+        ref, ey_ref, _ = _run(plan, X, SIMT)
+        scale = np.abs(ref).max(1, keepdims=True)
+        for ev in (TC, FX):
+            phi, ey, abs_sum = _run(plan, X, ev)
+            assert np.all(np.isfinite(phi)), (n_bg, nsamples, rows, link, ev)
+            assert np.abs(ey - ey_ref).max() <= 2e-6, (n_bg, nsamples, rows, link, ev, float(np.abs(ey - ey_ref).max()))
+            assert np.all(np.abs(phi - ref) <= 1e-4 * scale + 1e-7), (n_bg, nsamples, rows, link, ev)
+            assert abs_sum[30] == rows
+        want = lg(f(X)) if link == "logit" else f(X)
+        np.testing.assert_allclose(ref.sum(1) + plan.expected_value, want, atol=2e-4 if link == "logit" else 1e-5)
+        plan.close()
+
+
+@pytest.mark.parametrize("fmt", ["0", "1"])
+def test_several_sets_on_many_shapes(params, monkeypatch, fmt):
+    """The same sweep for plans with several coalition sets (K2 expands its A tiles from the coalition words), with
+    f16 two-term and bf16 three-term operands: K2 against the SIMT evaluator."""
+    from fraud_detection_b200 import KernelShapPlan, sampler
+    monkeypatch.setenv("FDB_KSHAP_FMT", fmt)
+    rs = np.random.RandomState(7 + int(fmt))
+    f = lambda A: scoring.predict_proba(params, A)[:, 1]  # noqa: E731
+    for i, n_bg in enumerate([1, 7, 16, 48, 63, 64, 65, 100, 128, 129, 200, 256, 300, 512]):
+        nsamples = int(rs.choice([230, 256, 300, 385, 512]))
+        rows = int(rs.choice([1, 5, 64, 129, 257]))
+        n_sets = int(rs.choice([2, 3, 7]))
+        link = "logit" if i % 4 == 1 else "identity"
+        bg = scoring.transform(params, synth.rows(n_bg, seed=300 + i))
+        X = scoring.transform(params, synth.rows(rows, seed=700 + i))
+        sets = [sampler.sample_coalitions(30, nsamples, np.random.RandomState(100 * i + s)) for s in range(n_sets)]
+        plan = KernelShapPlan(params.coef, params.intercept, bg, np.stack([b for b, _ in sets]), np.stack([w for _, w in sets]), link)
+        assert plan.info()["fmt"] == int(fmt)
+        ref, ey_ref, _ = _run(plan, X, SIMT)
+        phi, ey, abs_sum = _run(plan, X, TC)
+        assert np.abs(ey - ey_ref).max() <= 2e-6, (n_bg, nsamples, rows, n_sets, link)
+        assert np.all(np.abs(phi - ref) <= 1e-4 * np.abs(ref).max(1, keepdims=True) + 1e-7), (n_bg, nsamples, rows, n_sets, link)
+        assert abs_sum[30] == rows
+        if link == "identity":
+            np.testing.assert_allclose(phi.sum(1) + plan.expected_value, f(X), atol=1e-5)
+        plan.close()
