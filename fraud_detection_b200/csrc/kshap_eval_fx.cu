@@ -87,6 +87,11 @@ __device__ __forceinline__ float fx_from_h16(uint16_t h, int fmt) {
 // MODE 3 (balanced, logit link): as MODE 2 plus the complements  1 - sigma = g / d,  g = E a  (d = g + b), summed with
 //   the same reciprocal:  sum_quad g_i / d_i = ((g0 d1 + g1 d0) p23 + (g2 d3 + g3 d2) p01) / (p01 p23).  accc gathers
 //   them; with both sums the stored expectation is exact to float32 in both tails (fdb_kshap_encode_ey).
+#ifndef FDB_FX_QUAD_UNROLL
+#define FDB_FX_QUAD_UNROLL 2      // quads of one coalition in flight (x 4 interleaved coalitions)
+#endif
+#define FDB_FX_PRAGMA(x) _Pragma(#x)
+#define FDB_FX_UNROLL(n) FDB_FX_PRAGMA(unroll n)
 enum { kFxClampedQuads = 0, kFxClampedPairs = 1, kFxBalanced = 2, kFxBalancedLogit = 3 };
 
 template <int MODE>
@@ -101,7 +106,7 @@ __device__ __forceinline__ void chunk_sum4(const float* __restrict__ e0, int cbs
         a[mm] = ptx::ex2_approx(MODE == kFxBalanced ? fminf(t[mm], 0.f) : t[mm]);
         b[mm] = MODE == kFxBalanced ? ptx::ex2_approx(fminf(-t[mm], 0.f)) : 1.0f;
     }
-#pragma unroll 2
+FDB_FX_UNROLL(FDB_FX_QUAD_UNROLL)
     for (int q = 0; q < nquads; ++q) {
 #pragma unroll
         for (int mm = 0; mm < 4; ++mm) {
