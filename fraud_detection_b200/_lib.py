@@ -62,6 +62,7 @@ _SIGS = {
     "fdb_kshap_plan_set_num_features": (_i, [_vp, _i]),
     "fdb_kshap_explain_dev": (_i, [_vp, _vp, _i64, _vp, _vp, _i, _vp, _vp, _vp]),
     "fdb_kshap_explain_host": (_i, [_vp, _i64, _vp, _vp, _i, _vp, _vp]),
+    "fdb_probe_pipes": (_i, [_vp, _dp]),
 }
 
 
@@ -109,6 +110,15 @@ def get_ctx(device: int | None = None) -> int:
 
 def sm_count(device: int | None = None) -> int:
     return int(lib.fdb_ctx_sm_count(get_ctx(device)))
+
+
+def probe_pipes(device: int | None = None) -> dict:
+    """Measured instruction-pipe rates of the device (fdb_probe_pipes): the Kernel SHAP roofline denominators."""
+    out = (C.c_double * 8)()
+    check(lib.fdb_probe_pipes(get_ctx(device), out))
+    keys = ("ex2_per_s", "rcp_per_s", "ffma_per_s", "k2f_quad_regs_sigmoids_per_s", "k2f_quad_lds_sigmoids_per_s",
+            "sm_clock_hz", "sm_count")
+    return dict(zip(keys, list(out)[:7]))
 
 
 # ------------------------------------------------------------------ small helpers

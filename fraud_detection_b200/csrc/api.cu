@@ -27,7 +27,7 @@ namespace {
 
 constexpr int64_t kSmallRows = 16384;            // serving-size batches go through pinned staging
 constexpr int64_t kDefaultChunkRows = 1 << 20;   // rows per pipeline chunk for large host batches
-constexpr int kScratchSets = FDB_PIPE_SLOTS + 1; // one per pipeline slot + one for _dev callers
+constexpr int kScratchSets = FDB_PIPE_SLOTS + 1; // set 0: _dev callers; sets 1..: the host entry points (one per pipeline slot)
 
 struct DeviceGuard {
     int prev = -1;
@@ -134,6 +134,9 @@ int run_host(fdb_ctx* ctx, int dtype, int64_t n, const void* x, const LinearPara
     if (n <= kSmallRows) {
         // serving path: one stream, everything through the context's pinned staging buffer
         fdb_pipe_slot& s = ctx->slot[0];
+        // scratch set 1 (pipeline slot 0's): set 0 belongs to _dev callers, whose launches may overlap this one
+        double* h_partials = ctx->d_partials + (size_t)FDB_MAX_GRID * 32;
+        unsigned int* h_ticket = ctx->d_ticket + 1;
         char* st = static_cast<char*>(ctx->h_stage);
         const bool x_pinned = is_device_accessible_host(x);
         // output blocks inside the pinned staging buffer (offsets keep 16-byte alignment)
@@ -149,7 +152,7 @@ int run_host(fdb_ctx* ctx, int dtype, int64_t n, const void* x, const LinearPara
             if (!x_pinned || !fdb_aligned16(x)) { memcpy(st, x, (size_t)n * row_b); src = st; }
             rc = fdb_launch_linear_pass(ctx, s.stream, dtype, n, src, prm, divide, proba ? o_p : nullptr, proba_cols,
                                         logit ? o_z : nullptr, phi ? o_phi : nullptr, cls ? reinterpret_cast<uint8_t*>(o_c) : nullptr,
-                                        abs_sum ? reinterpret_cast<double*>(o_a) : nullptr, ctx->d_partials, ctx->d_ticket);
+                                        abs_sum ? reinterpret_cast<double*>(o_a) : nullptr, h_partials, h_ticket);
             if (rc != FDB_OK) return rc;
             FDB_CUDA(cudaStreamSynchronize(s.stream));
             if (phi) memcpy(ph, o_phi, (size_t)n * row_b);
@@ -164,13 +167,13 @@ int run_host(fdb_ctx* ctx, int dtype, int64_t n, const void* x, const LinearPara
         FDB_CUDA(cudaMemcpyAsync(s.d_in, src, (size_t)n * row_b, cudaMemcpyHostToDevice, s.stream));
         rc = fdb_launch_linear_pass(ctx, s.stream, dtype, n, s.d_in, prm, divide, proba ? s.d_p : nullptr, proba_cols,
                                     logit ? s.d_z : nullptr, phi ? s.d_out : nullptr, cls ? s.d_cls : nullptr,
-                                    abs_sum ? ctx->d_abs_sum : nullptr, ctx->d_partials, ctx->d_ticket);
+                                    abs_sum ? ctx->d_abs_sum + 32 : nullptr, h_partials, h_ticket);
         if (rc != FDB_OK) return rc;
         if (phi) FDB_CUDA(cudaMemcpyAsync(o_phi, s.d_out, (size_t)n * row_b, cudaMemcpyDeviceToHost, s.stream));
         if (proba) FDB_CUDA(cudaMemcpyAsync(o_p, s.d_p, (size_t)n * es * proba_cols, cudaMemcpyDeviceToHost, s.stream));
         if (logit) FDB_CUDA(cudaMemcpyAsync(o_z, s.d_z, (size_t)n * es, cudaMemcpyDeviceToHost, s.stream));
         if (cls) FDB_CUDA(cudaMemcpyAsync(o_c, s.d_cls, (size_t)n, cudaMemcpyDeviceToHost, s.stream));
-        if (abs_sum) FDB_CUDA(cudaMemcpyAsync(o_a, ctx->d_abs_sum, 32 * sizeof(double), cudaMemcpyDeviceToHost, s.stream));
+        if (abs_sum) FDB_CUDA(cudaMemcpyAsync(o_a, ctx->d_abs_sum + 32, 32 * sizeof(double), cudaMemcpyDeviceToHost, s.stream));
         FDB_CUDA(cudaStreamSynchronize(s.stream));
         if (phi) memcpy(ph, o_phi, (size_t)n * row_b);
         if (proba) memcpy(pp, o_p, (size_t)n * es * proba_cols);

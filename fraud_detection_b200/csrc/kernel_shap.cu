@@ -279,6 +279,7 @@ void free_plan(fdb_kshap_plan* p) {
     cudaFree(p->d_bits); cudaFree(p->d_kw); cudaFree(p->d_P); cudaFree(p->d_wq); cudaFree(p->d_bimg); cudaFree(p->d_aimg);
     cudaFree(p->d_ainv); cudaFree(p->d_c2); cudaFree(p->d_status); cudaFree(p->d_ey); cudaFree(p->d_x); cudaFree(p->d_phi);
     cudaFree(p->d_set); cudaFree(p->d_abs); cudaFree(p->d_E); cudaFree(p->d_eoff); cudaFree(p->d_xw); cudaFree(p->d_gpart); cudaFree(p->d_gz); cudaFree(p->d_bv); cudaFree(p->d_s0);
+    cudaFree(p->d_partials); cudaFree(p->d_ticket);
     delete p;
 }
 
@@ -418,6 +419,9 @@ static int plan_create_impl(fdb_ctx* ctx, const double* coef, double intercept, 
         TRY(cudaMalloc((void**)&p->d_phi, (size_t)p->batch_rows * FDB_F * 4));
         TRY(cudaMalloc((void**)&p->d_set, (size_t)p->batch_rows * 4));
         TRY(cudaMalloc((void**)&p->d_abs, 32 * 8));
+        TRY(cudaMalloc((void**)&p->d_partials, (size_t)FDB_MAX_GRID * 32 * sizeof(double)));
+        TRY(cudaMalloc((void**)&p->d_ticket, sizeof(unsigned int)));
+        TRY(cudaMemset(p->d_ticket, 0, sizeof(unsigned int)));
         if (bits) {
             TRY(cudaMemcpy(p->d_bits, hbits.data(), SM * 4, cudaMemcpyHostToDevice));
             TRY(cudaMemcpy(p->d_kw, hkw.data(), SM * 4, cudaMemcpyHostToDevice));
@@ -564,8 +568,8 @@ extern "C" int fdb_kshap_explain_dev(fdb_kshap_plan* p, void* stream, int64_t n_
         if (grid > cap) grid = cap;
         kshap_wls_solve<<<grid, 128, 0, st>>>(xb, r0, nb, sb, p->n_sets, p->d_bits, p->d_kw, p->m_pad, p->d_ey, p->d_ainv,
                                              p->d_c2, p->d_wq, (float)p->intercept, (float)p->fnull, p->link,
-                                             phi + r0 * FDB_F, abs_sum, r0 > 0 ? 1 : 0, n_rows, ctx->d_partials,
-                                             ctx->d_ticket, evaluator == FDB_KSHAP_EVAL_FACTORED ? p->d_gpart : nullptr,
+                                             phi + r0 * FDB_F, abs_sum, r0 > 0 ? 1 : 0, n_rows, p->d_partials,
+                                             p->d_ticket, evaluator == FDB_KSHAP_EVAL_FACTORED ? p->d_gpart : nullptr,
                                              p->m_pad / 32);
         FDB_CUDA(cudaGetLastError());
     }

@@ -47,6 +47,8 @@ struct fdb_kshap_plan {
     int num_features = 0;              // 0 = plain WLS over all features; k = LARS selection of k features first
     uint32_t varying = 0x3FFFFFFFu;    // features that differ from the background for the rows of this plan (bit 29 always set)
     float* d_gpart = nullptr;          // [batch_rows][m_pad/32][32] partial X'W y written by K2f, folded by K3
+    double* d_partials = nullptr;      // [FDB_MAX_GRID][32] per-CTA |phi| column sums of K3 / K3L (the plan's own: plans on
+    unsigned int* d_ticket = nullptr;  //   different streams, and K1 calls on the same context, never share an arrival ticket)
 };
 
 void fdb_kshap_split(double v, int fmt, int n, uint16_t* out);

@@ -348,7 +348,7 @@ int fdb_kshap_launch_lars_solve(fdb_kshap_plan* p, cudaStream_t st, const float*
     kshap_lars_solve<<<grid, 128, 0, st>>>(x, row_offset, n_rows, set_idx, p->n_sets, p->d_bits, p->d_kw, p->m_pad, p->d_ey,
                                           p->d_gz, p->d_bv, p->d_s0, p->d_wq, p->intercept, p->fnull, p->link,
                                           p->num_features, 2.0 * (double)p->n_masks, phi, abs_sum, accumulate, total_rows,
-                                          p->ctx->d_partials, p->ctx->d_ticket, p->varying);
+                                          p->d_partials, p->d_ticket, p->varying);
     FDB_CUDA(cudaGetLastError());
     return FDB_OK;
 }

@@ -37,16 +37,30 @@ def _parse_model(model):
     raise ValueError("An unknown model type was passed: " + str(type(model)))
 
 
-def _background(data, max_samples=MAX_BACKGROUND) -> np.ndarray:
-    """maskers.Independent: keep <= max_samples rows (resample without replacement, seed 0)."""
+#: How a background of more than ``max_samples`` rows is cut down.  shap does this inside ``maskers.Independent``
+#: through ``shap.utils.sample(data, max_samples)``; which rule the pinned release applies is RECALLED, not verified
+#: (shap is not installable in the build image - DESIGN.md section 3 lists every such detail), so the rule is a
+#: constructor argument: a user who has shap can align the drop-in with it (or pass the mean directly).
+SUBSAMPLE_RULES = ("resample_without_replacement", "resample_with_replacement", "first", "none")
+
+
+def _background(data, max_samples=MAX_BACKGROUND, subsample="resample_without_replacement", random_state=0) -> np.ndarray:
+    """maskers.Independent: keep <= max_samples rows.  ``subsample`` is one of SUBSAMPLE_RULES or a callable
+    ``(data, max_samples) -> rows``; the default is the recalled shap rule (sklearn resample, seed 0, no replacement)."""
     data = data.values if hasattr(data, "values") else data
     data = np.asarray(data, dtype=np.float64)
     if data.ndim != 2:
         raise ValueError("background data must be 2-D")
-    if data.shape[0] > max_samples:
+    if max_samples is None or data.shape[0] <= max_samples or subsample == "none":
+        return data
+    if callable(subsample):
+        return np.asarray(subsample(data, max_samples), dtype=np.float64)
+    if subsample == "first":
+        return data[:max_samples]
+    if subsample in ("resample_without_replacement", "resample_with_replacement"):
         from sklearn.utils import resample
-        data = resample(data, n_samples=max_samples, random_state=0, replace=False)
-    return data
+        return resample(data, n_samples=max_samples, random_state=random_state, replace=subsample.endswith("with_replacement"))
+    raise ValueError(f"subsample must be one of {SUBSAMPLE_RULES} or a callable")
 
 
 def _plain_rows(X) -> np.ndarray:
@@ -71,7 +85,10 @@ class B200LinearExplainer:
     coef . mean + intercept), exactly as the reference uses it.
     """
 
-    def __init__(self, model, data, feature_perturbation="interventional", device=None, **kwargs):
+    def __init__(self, model, data, feature_perturbation="interventional", device=None, max_samples=MAX_BACKGROUND,
+                 subsample="resample_without_replacement", random_state=0, **kwargs):
+        """``max_samples`` / ``subsample`` / ``random_state``: how a background of more than ``max_samples`` rows is cut
+        down before its mean is taken (see SUBSAMPLE_RULES; the default is the recalled shap rule)."""
         if feature_perturbation not in (None, "interventional"):
             raise NotImplementedError("only feature_perturbation='interventional' is on the reference path")
         self.feature_perturbation = "interventional"
@@ -81,7 +98,7 @@ class B200LinearExplainer:
         if isinstance(data, tuple) and len(data) == 2:          # (mean, cov) form
             self.mean = np.asarray(data[0], dtype=np.float64).reshape(-1)
         else:
-            self.mean = np.array(np.mean(_background(data), 0)).flatten()
+            self.mean = np.array(np.mean(_background(data, max_samples, subsample, random_state), 0)).flatten()
         self.expected_value = float(np.dot(self.coef, self.mean) + self.intercept)
         self.M = len(self.mean)
         self.device = device
@@ -117,14 +134,60 @@ EVAL_AUTO, EVAL_TC, EVAL_SIMT, EVAL_FACTORED = -1, 0, 1, 2
 _LINKS = {"identity": 0, "logit": 1}
 
 
-def _linear_model_of(model):
-    """Accept what a reference-style caller would hand to KernelExplainer for this model:
-    the estimator, its bound ``predict_proba`` (``lambda X: model.predict_proba(X)[:, 1]`` cannot
-    be introspected, so pass the estimator or the bound method instead), or ``(coef, intercept)``."""
+def _linear_model_of(model, data=None):
+    """Accept what a reference-style caller would hand to KernelExplainer for this model: the estimator, its bound
+    ``predict_proba``, ``(coef, intercept)``, or ANY callable ``f(X) -> P(class 1)`` such as
+    ``lambda X: model.predict_proba(X)[:, 1]``.  A callable cannot be introspected, so it is identified instead: the
+    kernels evaluate f(u) = sigmoid(w.u + c) and nothing else, and such an f is fixed by 31 evaluations
+    (logit f is affine).  The recovered (w, c) must then reproduce f on points the fit never saw, otherwise
+    the function is not a logistic-linear model and the B200 path refuses it.
+    Returns (coef, intercept, n_outputs): n_outputs = 2 when f returns both predict_proba columns."""
     owner = getattr(model, "__self__", None)
     if owner is not None and hasattr(owner, "coef_"):
-        model = owner
-    return _parse_model(model)
+        coef, intercept = _parse_model(owner)
+        return coef, intercept, (2 if getattr(model, "__name__", "") == "predict_proba" else 1)
+    if not callable(model) or hasattr(model, "coef_") or isinstance(model, tuple):
+        coef, intercept = _parse_model(model)
+        return coef, intercept, 1
+    return _identify_logistic(model, data)
+
+
+def _identify_logistic(f, data):
+    """(coef, intercept, n_outputs) of a callable that is a logistic-linear model; ValueError otherwise."""
+    bg = np.zeros((1, N_FEATURES)) if data is None else np.asarray(getattr(data, "values", data), dtype=np.float64).reshape(-1, N_FEATURES)
+    centre = bg.mean(0)
+    span = np.maximum(bg.std(0), 0.1 * np.maximum(np.abs(centre), 1.0))
+    span[~np.isfinite(span)] = 1.0
+
+    def logit_of(P):
+        out = np.asarray(f(P), dtype=np.float64)
+        n_out = 1
+        if out.ndim == 2:
+            if out.shape[1] == 2:
+                n_out, out = 2, out[:, 1]
+            elif out.shape[1] == 1:
+                out = out[:, 0]
+            else:
+                raise ValueError("the B200 path explains a binary model: f must return P(class 1) or two predict_proba columns")
+        with np.errstate(divide="ignore", invalid="ignore"):
+            return np.log(out) - np.log1p(-out), out, n_out
+
+    pts = np.vstack([centre[None, :], centre[None, :] + np.diag(span)])
+    z, p, n_out = logit_of(pts)
+    if not (np.all(np.isfinite(z)) and np.all((p > 0) & (p < 1))):
+        raise ValueError("the model function saturates around the background; pass the estimator or (coef, intercept) instead")
+    coef = (z[1:] - z[0]) / span
+    intercept = float(z[0] - coef @ centre)
+    rng = np.random.RandomState(12345)
+    chk = centre[None, :] + rng.uniform(-1.0, 1.0, (16, N_FEATURES)) * span[None, :]
+    if bg.shape[0] > 1:
+        chk = np.vstack([chk, bg[:16]])
+    _, p_chk, _ = logit_of(chk)
+    want = 1.0 / (1.0 + np.exp(-(chk @ coef + intercept)))
+    if not np.allclose(p_chk, want, rtol=1e-7, atol=1e-9):
+        raise ValueError("the model function is not sigmoid(w.x + c): only logistic-linear models run on the B200 path "
+                         f"(worst deviation {np.abs(p_chk - want).max():.3g})")
+    return coef, intercept, n_out
 
 
 class KernelShapPlan:
@@ -250,10 +313,15 @@ class B200KernelExplainer:
     plain WLS over all features (BASELINE.json's parity configuration).  Both run on the GPU.
     """
 
-    def __init__(self, model, data, link="identity", device=None, keep_index=False, **kwargs):
+    def __init__(self, model, data, link="identity", device=None, keep_index=False, multi_output=False, **kwargs):
+        """``model``: the estimator, its bound ``predict_proba``, ``(coef, intercept)`` or any callable returning
+        P(class 1) (or both ``predict_proba`` columns) of a logistic-linear model - see ``_linear_model_of``.
+        ``multi_output=True`` with a two-column function returns what shap returns for it [recalled]: ``(N, 30, 2)``
+        attributions (class 0 = minus class 1 under both links) and a two-element ``expected_value``; the default
+        keeps the class-1 explanation only."""
         if link not in _LINKS:
             raise ValueError(f"link must be one of {list(_LINKS)}")
-        self.coef, self.intercept = _linear_model_of(model)
+        self.coef, self.intercept, self.n_outputs = _linear_model_of(model, data)
         data = data.values if hasattr(data, "values") else data
         self.data = np.ascontiguousarray(data, dtype=np.float64)
         if self.data.ndim == 1:
@@ -269,6 +337,10 @@ class B200KernelExplainer:
         z = self.data @ self.coef + self.intercept
         self.fnull = float(np.mean(1.0 / (1.0 + np.exp(-z))))
         self.expected_value = float(np.log(self.fnull / (1 - self.fnull))) if link == "logit" else self.fnull
+        self.multi_output = bool(multi_output) and self.n_outputs == 2
+        if self.multi_output:
+            ev1 = self.expected_value
+            self.expected_value = np.array([-ev1 if link == "logit" else 1.0 - ev1, ev1])
         self._shared_cache: dict = {}
         self._device_plans: dict = {}
         self._device_calls = 0
@@ -290,8 +362,12 @@ class B200KernelExplainer:
             kw[i, :len(w)] = w
         return bits, kw
 
-    def shap_values(self, X, nsamples="auto", l1_reg="num_features(10)", mask_mode="per_row", masks=None, evaluator=EVAL_AUTO,
-                    random=None, silent=True, sampler="host", seed=0, **kwargs):
+    def shap_values(self, X, *args, **kwargs):
+        phi = self._shap_values_class1(X, *args, **kwargs)
+        return np.stack([-phi, phi], axis=-1) if self.multi_output else phi
+
+    def _shap_values_class1(self, X, nsamples="auto", l1_reg="num_features(10)", mask_mode="per_row", masks=None, evaluator=EVAL_AUTO,
+                            random=None, silent=True, sampler="host", seed=0, **kwargs):
         from . import sampler as _sampler
         num_features = 0
         if isinstance(l1_reg, str) and l1_reg.startswith("num_features("):

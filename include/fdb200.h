@@ -93,9 +93,10 @@ int fdb_transform_host(fdb_ctx* ctx, int dtype, int64_t n_rows, const void* x,
  * (explain_model.py:39) that ranks all-reduce across GPUs.
  * proba_cols = 1 writes proba[r] = p; proba_cols = 2 writes the predict_proba layout
  * proba[r][0] = 1 - p, proba[r][1] = p.  cls is uint8; abs_sum is 32 doubles on the device
- * (dev) / host (host).  A _dev call that asks for abs_sum uses per-context scratch: at most
- * one such launch per context may be in flight.  A non-finite abs_sum[k] means column k of
- * the input held a NaN or infinity.
+ * (dev) / host (host).  A _dev call that asks for abs_sum uses a per-context scratch set of
+ * its own (the _host entry points and every Kernel SHAP plan have theirs, so those may run
+ * at the same time): at most one such _dev launch per context may be in flight.  A
+ * non-finite abs_sum[k] means column k of the input held a NaN or infinity.
  * ------------------------------------------------------------------------------- */
 int fdb_linear_pass_dev(fdb_ctx* ctx, void* stream, int dtype, int64_t n_rows, const void* x,
                         const double* sub, const double* mul, double bias,
@@ -186,6 +187,17 @@ int fdb_kshap_explain_host(fdb_kshap_plan* plan, int64_t n_rows, const float* x,
 int fdb_linear_pass_noalloc(void* stream, int dtype, int64_t n_rows, const void* x,
                             const double* sub, const double* mul, double bias,
                             void* proba, int proba_cols, void* logit, void* phi, uint8_t* cls, double* abs_sum);
+
+/* ---------------------------------------------------------------------------------
+ * Measurement aid (no counterpart in the reference): instruction-pipe rates of this GPU,
+ * measured with small saturating kernels at the clock the device runs them at.  They are
+ * the denominators of the Kernel SHAP rooflines in bench.py (MEASURED_PEAKS.json has no
+ * SFU / FP32-issue figure).  out8: [0] ex2.approx results/s, [1] rcp.approx results/s,
+ * [2] independent FFMA results/s, [3] sigmoids/s of K2f's clamp-free quad loop on
+ * registers, [4] the same loop with its broadcast LDS.128 reads, [5] SM clock (Hz) during
+ * the FFMA probe, [6] SM count, [7] 0.  Synchronous; allocates 256 bytes while it runs.
+ * ------------------------------------------------------------------------------- */
+int fdb_probe_pipes(fdb_ctx* ctx, double* out8);
 
 #ifdef __cplusplus
 }

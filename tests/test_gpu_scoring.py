@@ -282,3 +282,38 @@ def test_serving_path_takes_unaligned_pinned_rows(params):
         _lib.check(_lib.lib.fdb_linear_pass_host(_lib.get_ctx(None), _lib.F64, n, _lib.np_ptr(view), None, _lib.dvec(params.coef),
                                                  float(params.intercept), _lib.np_ptr(p), 1, None, None, None, None))
         np.testing.assert_allclose(p, scoring.predict_proba(params, X)[:, 1], rtol=0, atol=1e-12)
+
+
+def test_host_and_device_calls_on_one_context_do_not_share_scratch(params):
+    """A _dev launch (torch stream) and a _host call of the same context run at the same time: each keeps its own
+    partial-sum scratch and arrival ticket, so both |phi| summaries stay right however they interleave."""
+    import threading
+
+    from fraud_detection_b200.device import FraudScorer
+    scorer = FraudScorer(params.coef, params.intercept, params.mean, params.scale)
+    Xd = synth.rows(3_000_000, seed=5).astype(np.float32)
+    Xh = synth.rows(9000, seed=6).astype(np.float32)
+    xd = torch.from_numpy(Xd).cuda()
+    want_d = scorer(xd, abs_sum=True).abs_sum.cpu().numpy()
+    want_h = scorer.score_host(Xh, abs_sum=True)["abs_sum"].copy()
+    stop = threading.Event()
+    bad = []
+
+    def host_loop():
+        while not stop.is_set():
+            got = scorer.score_host(Xh, abs_sum=True)["abs_sum"]
+            if not np.array_equal(got, want_h):
+                bad.append(got.copy())
+
+    th = threading.Thread(target=host_loop)
+    th.start()
+    try:
+        side = torch.cuda.Stream()
+        with torch.cuda.stream(side):
+            for _ in range(60):
+                got = scorer(xd, abs_sum=True).abs_sum.cpu().numpy()
+                assert np.array_equal(got, want_d)
+    finally:
+        stop.set()
+        th.join()
+    assert not bad

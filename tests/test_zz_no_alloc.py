@@ -103,3 +103,52 @@ def test_noalloc_rejects_batches_beyond_its_scratch(params):
     out = _call_noalloc(_lib, x[:0], np.zeros(30), params.coef, 0.0, int(torch.cuda.current_stream(dev).cuda_stream))
     torch.cuda.synchronize(dev)
     assert float(out["abs_sum"].abs().sum()) == 0.0
+
+
+def test_noalloc_matches_the_oracle(params):
+    """The same outputs against the CPU oracle (not only against the sibling entry point), float64, so a fault
+    shared by both CUDA entry points would still show."""
+    from fraud_detection_b200 import _lib
+    from oracle import linear_shap, scoring, synth
+
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    stream = int(torch.cuda.current_stream(dev).cuda_stream)
+    Xs = scoring.transform(params, synth.rows(5003, seed=9))
+    mu_bg, ev = linear_shap.explainer_state(params.coef, params.intercept, Xs[:100])
+    for _ in range(2):
+        got = _call_noalloc(_lib, torch.from_numpy(Xs).to(dev), mu_bg, params.coef, ev, stream)
+        torch.cuda.synchronize(dev)
+        phi_ref = linear_shap.shap_values(params.coef, mu_bg, Xs)
+        np.testing.assert_allclose(got["phi"].cpu().numpy(), phi_ref, rtol=0, atol=1e-12)
+        np.testing.assert_allclose(got["proba"].cpu().numpy(), scoring.predict_proba(params, Xs), rtol=0, atol=1e-12)
+        np.testing.assert_allclose(got["logit"].cpu().numpy(), scoring.decision_function(params, Xs), rtol=0, atol=1e-10)
+        assert np.array_equal(got["cls"].cpu().numpy(), scoring.predict(params, Xs).astype(np.uint8))
+        a = got["abs_sum"].cpu().numpy()
+        np.testing.assert_allclose(a[:30], np.abs(phi_ref).sum(0), rtol=1e-12)
+        assert a[30] == Xs.shape[0]
+
+
+def test_noalloc_without_column_sums_leaves_the_shared_array_alone(params):
+    """abs_sum == NULL is the variant that needs no scratch at all: the other outputs are unchanged, and a call that
+    does ask for the sums afterwards is not disturbed by it."""
+    from fraud_detection_b200 import _lib
+    from oracle import synth
+
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    stream = int(torch.cuda.current_stream(dev).cuda_stream)
+    x = torch.from_numpy(synth.rows(7001, seed=11)).to(dev, torch.float32)
+    sub, mul, bias = params.mean, params.coef / params.scale, params.intercept
+    full = _call_noalloc(_lib, x, sub, mul, bias, stream)
+    out = _buffers(x)
+    rc = _lib.lib.fdb_linear_pass_noalloc(stream, _lib.F32, x.shape[0], x.data_ptr(), _lib.dvec(sub), _lib.dvec(mul), float(bias),
+                                          out["proba"].data_ptr(), 2, out["logit"].data_ptr(), out["phi"].data_ptr(),
+                                          out["cls"].data_ptr(), None)
+    _lib.check(rc)
+    again = _call_noalloc(_lib, x, sub, mul, bias, stream)
+    torch.cuda.synchronize(dev)
+    for key in ("proba", "logit", "phi", "cls"):
+        assert torch.equal(out[key], full[key]), key
+    assert float(out["abs_sum"][0]) == -1.0                      # untouched: the caller's buffer was never passed
+    assert torch.equal(again["abs_sum"], full["abs_sum"])
