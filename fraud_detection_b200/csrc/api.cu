@@ -29,18 +29,6 @@ constexpr int64_t kSmallRows = 16384;            // serving-size batches go thro
 constexpr int64_t kDefaultChunkRows = 1 << 20;   // rows per pipeline chunk for large host batches
 constexpr int kScratchSets = FDB_PIPE_SLOTS + 1; // set 0: _dev callers; sets 1..: the host entry points (one per pipeline slot)
 
-struct DeviceGuard {
-    int prev = -1;
-    bool ok = true;
-    explicit DeviceGuard(int dev) {
-        if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
-        if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
-    }
-    ~DeviceGuard() {
-        if (prev >= 0) cudaSetDevice(prev);
-    }
-};
-
 size_t elem_size(int dtype) { return dtype == FDB_F64 ? 8 : 4; }
 
 void free_pipeline(fdb_ctx* ctx) {

@@ -35,6 +35,20 @@ void fdb_set_error(const char* fmt, ...);
 
 static inline bool fdb_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
+// Makes `dev` the current device for the lifetime of the object and restores the caller's device afterwards (a
+// process that drives several GPUs must not find its current device changed by a library call).
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; prev = -1; return; }
+        if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
 // ---- context --------------------------------------------------------------------------
 constexpr int FDB_MAX_DEVICES = 64;        // device indices a process may use
 constexpr int FDB_PIPE_SLOTS = 3;          // host pipeline depth (H2D / kernel / D2H overlap)

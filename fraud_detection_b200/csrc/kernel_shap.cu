@@ -118,17 +118,6 @@ __global__ void __launch_bounds__(32) kshap_wls_prepare(const uint32_t* __restri
     if (lane == 0) status[s] = singular ? 1 : 0;
 }
 
-// xw[m][j] = kw_m * x_mj (x = z_j - z_29) for the single set of a factored plan: the row-independent factor of X'W y
-__global__ void kshap_build_xw(const uint32_t* __restrict__ bits, const float* __restrict__ kw, int m_pad,
-                               float* __restrict__ xw) {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= m_pad * 32) return;
-    const int m = idx >> 5, j = idx & 31;
-    const uint32_t b = bits[m];
-    const float x = j < kNV ? (float)((b >> j) & 1u) - (float)((b >> 29) & 1u) : 0.f;
-    xw[idx] = kw[m] * x;
-}
-
 // ---------------------------------------------------------------------------------------
 // SIMT evaluator: one thread per (row, mask), plain fp32 FMAs and full-precision expf.
 // The GPU-side cross-check of K2 and the evaluator for shapes K2 does not take.
@@ -177,7 +166,7 @@ __global__ void __launch_bounds__(128) kshap_wls_solve(
     const float* __restrict__ ainv, const float* __restrict__ c2, const float* __restrict__ wcoef, float intercept,
     float fnull, int link, float* __restrict__ phi, double* __restrict__ abs_sum, int accumulate,
     int64_t total_rows, double* __restrict__ partials, unsigned int* __restrict__ ticket,
-    const float* __restrict__ gpart, int nparts) {
+    const float* __restrict__ gpart, int gslots, long long fx_units, int fx_grid, int fx_tiles) {
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const float lnull = link_apply(fnull, link);
@@ -196,10 +185,14 @@ __global__ void __launch_bounds__(128) kshap_wls_solve(
         const float* er = ey + (size_t)r * m_pad;
         float g;
         if (gpart != nullptr) {
-            // X'W y already accumulated by the factored evaluator: fold its per-(tile, warp) partials in a fixed order
-            const float* gp = gpart + (size_t)r * nparts * 32 + lane;
+            // X'W y already accumulated by the factored evaluator (fused GEMM, kshap_eval_fx.cu): one record per CTA that
+            // worked on this row's block of 128 rows.  Units are dealt to CTAs as contiguous ranges, so the CTAs of a
+            // row block are consecutive; fold their records in CTA order (deterministic).
+            const long long ub = (long long)(r >> 7) * fx_tiles;
+            const int nseg = (int)((((ub + fx_tiles) * fx_grid - 1) / fx_units) - (((ub + 1) * fx_grid - 1) / fx_units)) + 1;
+            const float* gp = gpart + (size_t)r * gslots * 32 + lane;
             g = 0.f;
-            for (int q = 0; q < nparts; ++q) g += gp[(size_t)q * 32];
+            for (int q = 0; q < nseg; ++q) g += gp[(size_t)q * 32];
         } else {
             // X'W y: every lane owns one coalition per step and keeps all 29 partial sums in registers
             // (x_mj * v = zp_j ? vp : 0 after folding the sign of the eliminated feature into vp / zp) ...
@@ -277,9 +270,14 @@ float f16_to_f32(uint16_t h) { return __half2float(__ushort_as_half(h)); }
 void free_plan(fdb_kshap_plan* p) {
     if (!p) return;
     cudaFree(p->d_bits); cudaFree(p->d_kw); cudaFree(p->d_P); cudaFree(p->d_wq); cudaFree(p->d_bimg); cudaFree(p->d_aimg);
-    cudaFree(p->d_ainv); cudaFree(p->d_c2); cudaFree(p->d_status); cudaFree(p->d_ey); cudaFree(p->d_x); cudaFree(p->d_phi);
-    cudaFree(p->d_set); cudaFree(p->d_abs); cudaFree(p->d_E); cudaFree(p->d_eoff); cudaFree(p->d_xw); cudaFree(p->d_gpart); cudaFree(p->d_gz); cudaFree(p->d_bv); cudaFree(p->d_s0);
+    cudaFree(p->d_ainv); cudaFree(p->d_c2); cudaFree(p->d_status); cudaFree(p->d_ey);
+    cudaFree(p->d_abs); cudaFree(p->d_E); cudaFree(p->d_eoff); cudaFree(p->d_fxtile); cudaFree(p->d_gpart); cudaFree(p->d_gz); cudaFree(p->d_bv); cudaFree(p->d_s0);
     cudaFree(p->d_partials); cudaFree(p->d_ticket);
+    for (int i = 0; i < 2; ++i) {
+        cudaFree(p->d_x2[i]); cudaFree(p->d_phi2[i]); cudaFree(p->d_set2[i]);
+        for (int e = 0; e < 3; ++e)
+            if (p->ev[i][e]) cudaEventDestroy(p->ev[i][e]);
+    }
     delete p;
 }
 
@@ -313,10 +311,6 @@ static int refresh_set_products(fdb_kshap_plan* p) {
         FDB_REQUIRE(st[s] == 0, FDB_ERR_ARG, "mask set %d gives a singular weighted least-squares system (X'WX); "
                     "use more samples or fewer features", s);
     if (p->n_sets == 1) {
-        if (!p->d_xw) FDB_CUDA(cudaMalloc((void**)&p->d_xw, (size_t)p->m_pad * 32 * 4));
-        if (!p->d_gpart) FDB_CUDA(cudaMalloc((void**)&p->d_gpart, (size_t)p->batch_rows * (p->m_pad / 32) * 32 * 4));
-        kshap_build_xw<<<(p->m_pad * 32 + 255) / 256, 256>>>(p->d_bits, p->d_kw, p->m_pad, p->d_xw);
-        FDB_CUDA(cudaGetLastError());
         cudaFree(p->d_E); cudaFree(p->d_eoff);
         p->d_E = nullptr; p->d_eoff = nullptr;
         int rc = fdb_kshap_build_factored(p, p->bg_host.data());
@@ -342,7 +336,8 @@ static int plan_create_impl(fdb_ctx* ctx, const double* coef, double intercept, 
     FDB_REQUIRE(n_bg >= 1 && n_bg <= FDB_KSHAP_MAX_BG, FDB_ERR_ARG, "background rows must be in [1, %d], got %d", FDB_KSHAP_MAX_BG, n_bg);
     FDB_REQUIRE(n_sets >= 1 && n_masks >= 1, FDB_ERR_ARG, "need at least one mask set and one mask");
     FDB_REQUIRE(link == 0 || link == 1, FDB_ERR_ARG, "link must be 0 (identity) or 1 (logit)");
-    if (cudaSetDevice(ctx->device) != cudaSuccess) { fdb_set_error("cannot select device %d", ctx->device); return FDB_ERR_CUDA; }
+    DeviceGuard guard(ctx->device);
+    FDB_REQUIRE(guard.ok, FDB_ERR_CUDA, "cannot select device %d", ctx->device);
     fdb_kshap_plan* p = new (std::nothrow) fdb_kshap_plan();
     FDB_REQUIRE(p != nullptr, FDB_ERR_NOMEM, "out of host memory");
     p->ctx = ctx;
@@ -413,12 +408,8 @@ static int plan_create_impl(fdb_ctx* ctx, const double* coef, double intercept, 
         TRY(cudaMalloc((void**)&p->d_ainv, (size_t)n_sets * kNV * 32 * 4));
         TRY(cudaMalloc((void**)&p->d_c2, (size_t)n_sets * 32 * 4));
         TRY(cudaMalloc((void**)&p->d_status, (size_t)n_sets * 4));
-        p->batch_rows = FDB_KSHAP_BATCH_ROWS;
-        TRY(cudaMalloc((void**)&p->d_ey, (size_t)p->batch_rows * p->m_pad * 4));
-        TRY(cudaMalloc((void**)&p->d_x, (size_t)p->batch_rows * FDB_F * 4));
-        TRY(cudaMalloc((void**)&p->d_phi, (size_t)p->batch_rows * FDB_F * 4));
-        TRY(cudaMalloc((void**)&p->d_set, (size_t)p->batch_rows * 4));
-        TRY(cudaMalloc((void**)&p->d_abs, 32 * 8));
+        p->batch_rows = FDB_KSHAP_BATCH_ROWS;          // the scratch between evaluate and solve is sized by the first calls (ensure_scratch)
+        TRY(cudaMalloc((void**)&p->d_abs, 2 * 32 * 8));
         TRY(cudaMalloc((void**)&p->d_partials, (size_t)FDB_MAX_GRID * 32 * sizeof(double)));
         TRY(cudaMalloc((void**)&p->d_ticket, sizeof(unsigned int)));
         TRY(cudaMemset(p->d_ticket, 0, sizeof(unsigned int)));
@@ -473,7 +464,8 @@ extern "C" int fdb_kshap_plan_resample(fdb_kshap_plan* p, uint64_t seed) {
     FDB_REQUIRE(p != nullptr, FDB_ERR_ARG, "plan is NULL");
     FDB_REQUIRE(p->sampled, FDB_ERR_STATE, "only plans made by fdb_kshap_plan_create_sampled can be resampled");
     std::lock_guard<std::mutex> lock(p->ctx->host_mu);
-    FDB_CUDA(cudaSetDevice(p->ctx->device));
+    DeviceGuard guard(p->ctx->device);
+    FDB_REQUIRE(guard.ok, FDB_ERR_CUDA, "cannot select device %d", p->ctx->device);
     FDB_CUDA(cudaDeviceSynchronize());
     int rc = fdb_kshap_sample_on_device(p, p->n_masks, (unsigned long long)seed);
     if (rc != FDB_OK) return rc;
@@ -483,7 +475,8 @@ extern "C" int fdb_kshap_plan_resample(fdb_kshap_plan* p, uint64_t seed) {
 extern "C" int fdb_kshap_plan_get_masks(const fdb_kshap_plan* p, int set, uint32_t* bits, float* kw) {
     FDB_REQUIRE(p && bits && kw, FDB_ERR_ARG, "NULL argument");
     FDB_REQUIRE(set >= 0 && set < p->n_sets, FDB_ERR_ARG, "set %d out of range", set);
-    FDB_CUDA(cudaSetDevice(p->ctx->device));
+    DeviceGuard guard(p->ctx->device);
+    FDB_REQUIRE(guard.ok, FDB_ERR_CUDA, "cannot select device %d", p->ctx->device);
     FDB_CUDA(cudaMemcpy(bits, p->d_bits + (size_t)set * p->m_pad, (size_t)p->n_masks * 4, cudaMemcpyDeviceToHost));
     FDB_CUDA(cudaMemcpy(kw, p->d_kw + (size_t)set * p->m_pad, (size_t)p->n_masks * 4, cudaMemcpyDeviceToHost));
     return FDB_OK;
@@ -491,7 +484,7 @@ extern "C" int fdb_kshap_plan_get_masks(const fdb_kshap_plan* p, int set, uint32
 
 extern "C" int fdb_kshap_plan_destroy(fdb_kshap_plan* p) {
     if (p) {
-        cudaSetDevice(p->ctx->device);
+        DeviceGuard guard(p->ctx->device);
         cudaDeviceSynchronize();
         free_plan(p);
     }
@@ -514,11 +507,31 @@ extern "C" int fdb_kshap_plan_set_num_features(fdb_kshap_plan* p, int k) {
     FDB_REQUIRE(p != nullptr, FDB_ERR_ARG, "plan is NULL");
     FDB_REQUIRE(k >= 0 && k <= 16, FDB_ERR_ARG, "num_features must be in [0, 16] (0 = no feature selection), got %d", k);
     if (k > 0) {
-        FDB_CUDA(cudaSetDevice(p->ctx->device));
+        DeviceGuard guard(p->ctx->device);
+        FDB_REQUIRE(guard.ok, FDB_ERR_CUDA, "cannot select device %d", p->ctx->device);
         int rc = fdb_kshap_prepare_lars(p);
         if (rc != FDB_OK) return rc;
     }
     p->num_features = k;
+    return FDB_OK;
+}
+
+// Scratch between evaluate and solve, grown on demand and never shrunk: coalition expectations (only when they go
+// through HBM: K2 / SIMT evaluators, ey_out, feature selection) and the factored evaluator's X'W y records.  Growing
+// frees the old buffer, which waits for the device - it happens on the first calls only.
+static int ensure_scratch(fdb_kshap_plan* p, size_t ey_floats, size_t gpart_floats) {
+    if (ey_floats > p->ey_cap) {
+        cudaFree(p->d_ey);
+        p->d_ey = nullptr; p->ey_cap = 0;
+        FDB_CUDA(cudaMalloc((void**)&p->d_ey, ey_floats * 4));
+        p->ey_cap = ey_floats;
+    }
+    if (gpart_floats > p->gpart_cap) {
+        cudaFree(p->d_gpart);
+        p->d_gpart = nullptr; p->gpart_cap = 0;
+        FDB_CUDA(cudaMalloc((void**)&p->d_gpart, gpart_floats * 4));
+        p->gpart_cap = gpart_floats;
+    }
     return FDB_OK;
 }
 
@@ -536,16 +549,41 @@ extern "C" int fdb_kshap_explain_dev(fdb_kshap_plan* p, void* stream, int64_t n_
         if (abs_sum) FDB_CUDA(cudaMemsetAsync(abs_sum, 0, 32 * sizeof(double), st));
         return FDB_OK;
     }
+    int cur = -1;
+    FDB_CUDA(cudaGetDevice(&cur));
+    FDB_REQUIRE(cur == p->ctx->device, FDB_ERR_STATE, "the plan lives on device %d but the current device is %d", p->ctx->device, cur);
     fdb_ctx* ctx = p->ctx;
-    for (int64_t r0 = 0; r0 < n_rows; r0 += p->batch_rows) {
-        const int nb = (int)((n_rows - r0) < p->batch_rows ? (n_rows - r0) : p->batch_rows);
+    const bool fx = evaluator == FDB_KSHAP_EVAL_FACTORED;
+    const bool need_ey = !fx || ey_out != nullptr || p->num_features > 0;
+    // rows per evaluate -> solve round: bounded by the ey scratch when expectations go through HBM; the factored path
+    // leaves only 256 B per row behind, so it takes large rounds (every CTA gets an equal share of the units)
+    int64_t batch = need_ey ? FDB_KSHAP_BATCH_ROWS : FDB_KSHAP_FX_BATCH_ROWS;
+    if (fx) {                                             // equal rounds, whole row blocks
+        const int64_t rounds = (n_rows + batch - 1) / batch;
+        batch = ((n_rows + rounds - 1) / rounds + 127) & ~int64_t(127);
+    }
+    {
+        const int64_t b0 = n_rows < batch ? n_rows : batch;
+        size_t gfl = 0;
+        if (fx) {
+            long long units; int grid, slots;
+            fdb_kshap_fx_geometry(p, (int)b0, &units, &grid, &slots);
+            gfl = (size_t)b0 * slots * 32;
+        }
+        int rc = ensure_scratch(p, need_ey ? (size_t)b0 * p->m_pad : 0, gfl);
+        if (rc != FDB_OK) return rc;
+    }
+    for (int64_t r0 = 0; r0 < n_rows; r0 += batch) {
+        const int nb = (int)((n_rows - r0) < batch ? (n_rows - r0) : batch);
         const float* xb = x + r0 * FDB_F;
         const int32_t* sb = set_idx ? set_idx + r0 : nullptr;
+        long long fx_units = 1; int fx_grid = 1, fx_slots = 1;
         if (evaluator == FDB_KSHAP_EVAL_TC) {
             int rc = fdb_kshap_launch_eval_tc(p, st, xb, r0, nb, sb, p->d_ey);
             if (rc != FDB_OK) return rc;
-        } else if (evaluator == FDB_KSHAP_EVAL_FACTORED) {
-            int rc = fdb_kshap_launch_eval_fx(p, st, xb, nb, (ey_out || p->num_features > 0) ? p->d_ey : nullptr);
+        } else if (fx) {
+            fdb_kshap_fx_geometry(p, nb, &fx_units, &fx_grid, &fx_slots);
+            int rc = fdb_kshap_launch_eval_fx(p, st, xb, nb, need_ey ? p->d_ey : nullptr, p->d_gpart);
             if (rc != FDB_OK) return rc;
         } else {
             dim3 grid(p->m_pad / 128, nb);
@@ -569,13 +607,15 @@ extern "C" int fdb_kshap_explain_dev(fdb_kshap_plan* p, void* stream, int64_t n_
         kshap_wls_solve<<<grid, 128, 0, st>>>(xb, r0, nb, sb, p->n_sets, p->d_bits, p->d_kw, p->m_pad, p->d_ey, p->d_ainv,
                                              p->d_c2, p->d_wq, (float)p->intercept, (float)p->fnull, p->link,
                                              phi + r0 * FDB_F, abs_sum, r0 > 0 ? 1 : 0, n_rows, p->d_partials,
-                                             p->d_ticket, evaluator == FDB_KSHAP_EVAL_FACTORED ? p->d_gpart : nullptr,
-                                             p->m_pad / 32);
+                                             p->d_ticket, fx ? p->d_gpart : nullptr, fx_slots, fx_units, fx_grid, p->m_pad / 128);
         FDB_CUDA(cudaGetLastError());
     }
     return FDB_OK;
 }
 
+// Host rows in, host phi out.  Batches of FDB_KSHAP_BATCH_ROWS rows go through two staging slots and three of the
+// context's streams: the copy-in of batch i + 1 and the copy-out of batch i - 1 overlap evaluate + solve of batch i
+// (the plan's own scratch serialises the compute, which is the long part).
 extern "C" int fdb_kshap_explain_host(fdb_kshap_plan* p, int64_t n_rows, const float* x, const int32_t* set_idx,
                                       int evaluator, float* phi, double* abs_sum) {
     FDB_REQUIRE(p != nullptr, FDB_ERR_ARG, "plan is NULL");
@@ -585,30 +625,83 @@ extern "C" int fdb_kshap_explain_host(fdb_kshap_plan* p, int64_t n_rows, const f
     if (n_rows == 0) return FDB_OK;
     fdb_ctx* ctx = p->ctx;
     std::lock_guard<std::mutex> lock(ctx->host_mu);
-    FDB_CUDA(cudaSetDevice(ctx->device));
-    cudaStream_t st = ctx->slot[0].stream;
-    for (int64_t r0 = 0; r0 < n_rows; r0 += p->batch_rows) {
-        const int64_t nb = (n_rows - r0) < p->batch_rows ? (n_rows - r0) : p->batch_rows;
-        FDB_CUDA(cudaMemcpyAsync(p->d_x, x + r0 * FDB_F, (size_t)nb * FDB_F * 4, cudaMemcpyHostToDevice, st));
-        if (set_idx) FDB_CUDA(cudaMemcpyAsync(p->d_set, set_idx + r0, (size_t)nb * 4, cudaMemcpyHostToDevice, st));
-        // default set mapping must see global row numbers: shift through an explicit index when needed
-        const int32_t* sidx = set_idx ? p->d_set : nullptr;
-        if (!set_idx && p->n_sets > 1 && r0 > 0) {
-            std::vector<int32_t> tmp((size_t)nb);
-            for (int64_t i = 0; i < nb; ++i) tmp[(size_t)i] = (int32_t)((r0 + i) % p->n_sets);
-            FDB_CUDA(cudaMemcpyAsync(p->d_set, tmp.data(), (size_t)nb * 4, cudaMemcpyHostToDevice, st));
-            FDB_CUDA(cudaStreamSynchronize(st));
-            sidx = p->d_set;
+    DeviceGuard guard(ctx->device);
+    FDB_REQUIRE(guard.ok, FDB_ERR_CUDA, "cannot select device %d", ctx->device);
+    const int64_t batch = FDB_KSHAP_BATCH_ROWS;
+    const int64_t n_batches = (n_rows + batch - 1) / batch;
+    const int64_t want = n_rows < batch ? n_rows : batch;
+    if (want > p->stage_rows) {
+        for (int i = 0; i < 2; ++i) {
+            cudaFree(p->d_x2[i]); cudaFree(p->d_phi2[i]); cudaFree(p->d_set2[i]);
+            p->d_x2[i] = p->d_phi2[i] = nullptr; p->d_set2[i] = nullptr;
         }
-        int rc = fdb_kshap_explain_dev(p, st, nb, p->d_x, sidx, evaluator, p->d_phi, nullptr, abs_sum ? p->d_abs : nullptr);
-        if (rc != FDB_OK) return rc;
-        FDB_CUDA(cudaMemcpyAsync(phi + r0 * FDB_F, p->d_phi, (size_t)nb * FDB_F * 4, cudaMemcpyDeviceToHost, st));
-        double habs[32];
-        if (abs_sum) FDB_CUDA(cudaMemcpyAsync(habs, p->d_abs, sizeof(habs), cudaMemcpyDeviceToHost, st));
-        FDB_CUDA(cudaStreamSynchronize(st));
-        if (abs_sum)
-            for (int k = 0; k < FDB_F; ++k) abs_sum[k] += habs[k];
+        p->stage_rows = 0;
+        const int slots = n_batches > 1 ? 2 : 1;
+        const int64_t rows = n_batches > 1 ? batch : want;
+        for (int i = 0; i < slots; ++i) {
+            FDB_CUDA(cudaMalloc((void**)&p->d_x2[i], (size_t)rows * FDB_F * 4));
+            FDB_CUDA(cudaMalloc((void**)&p->d_phi2[i], (size_t)rows * FDB_F * 4));
+            FDB_CUDA(cudaMalloc((void**)&p->d_set2[i], (size_t)rows * 4));
+        }
+        p->stage_rows = rows;
     }
-    if (abs_sum) abs_sum[FDB_F] = (double)n_rows;
+    if (n_batches > 1 && p->d_x2[1] == nullptr) {          // first multi-batch call after single-batch ones
+        FDB_CUDA(cudaMalloc((void**)&p->d_x2[1], (size_t)p->stage_rows * FDB_F * 4));
+        FDB_CUDA(cudaMalloc((void**)&p->d_phi2[1], (size_t)p->stage_rows * FDB_F * 4));
+        FDB_CUDA(cudaMalloc((void**)&p->d_set2[1], (size_t)p->stage_rows * 4));
+    }
+    for (int i = 0; i < 2; ++i)
+        for (int e = 0; e < 3; ++e)
+            if (!p->ev[i][e]) FDB_CUDA(cudaEventCreateWithFlags(&p->ev[i][e], cudaEventDisableTiming));
+    FDB_REQUIRE((size_t)n_batches * 32 * sizeof(double) <= ctx->h_stage_bytes, FDB_ERR_ARG, "too many rows for one call (%lld)", (long long)n_rows);
+    double* h_abs = static_cast<double*>(ctx->h_stage);          // pinned: per-batch |phi| sums land here
+    cudaStream_t s_in = ctx->slot[0].stream, s_c = ctx->slot[1].stream, s_out = ctx->slot[2].stream;
+    std::vector<int32_t> tmp;
+    int rc = FDB_OK;
+    cudaError_t e = cudaSuccess;
+    for (int64_t b = 0; b < n_batches && rc == FDB_OK && e == cudaSuccess; ++b) {
+        const int sl = (int)(b & 1);
+        const int64_t r0 = b * batch;
+        const int64_t nb = (n_rows - r0) < batch ? (n_rows - r0) : batch;
+        // copy-in: the slot's rows were last read by the compute of batch b - 2
+        if (b >= 2) e = cudaStreamWaitEvent(s_in, p->ev[sl][1], 0);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(p->d_x2[sl], x + r0 * FDB_F, (size_t)nb * FDB_F * 4, cudaMemcpyHostToDevice, s_in);
+        const int32_t* sidx = nullptr;
+        if (e == cudaSuccess && set_idx) {
+            e = cudaMemcpyAsync(p->d_set2[sl], set_idx + r0, (size_t)nb * 4, cudaMemcpyHostToDevice, s_in);
+            sidx = p->d_set2[sl];
+        } else if (e == cudaSuccess && p->n_sets > 1 && r0 > 0) {
+            // the default set mapping must see global row numbers: shift through an explicit index
+            tmp.resize((size_t)nb);
+            for (int64_t i = 0; i < nb; ++i) tmp[(size_t)i] = (int32_t)((r0 + i) % p->n_sets);
+            e = cudaMemcpyAsync(p->d_set2[sl], tmp.data(), (size_t)nb * 4, cudaMemcpyHostToDevice, s_in);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(s_in);          // tmp is reused by the next batch
+            sidx = p->d_set2[sl];
+        }
+        if (e == cudaSuccess) e = cudaEventRecord(p->ev[sl][0], s_in);
+        // evaluate + solve: needs the rows, and the slot's phi buffer back from the copy-out of batch b - 2
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(s_c, p->ev[sl][0], 0);
+        if (e == cudaSuccess && b >= 2) e = cudaStreamWaitEvent(s_c, p->ev[sl][2], 0);
+        if (e != cudaSuccess) break;
+        rc = fdb_kshap_explain_dev(p, s_c, nb, p->d_x2[sl], sidx, evaluator, p->d_phi2[sl], nullptr, abs_sum ? p->d_abs + 32 * sl : nullptr);
+        if (rc != FDB_OK) break;
+        e = cudaEventRecord(p->ev[sl][1], s_c);
+        // copy-out
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(s_out, p->ev[sl][1], 0);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(phi + r0 * FDB_F, p->d_phi2[sl], (size_t)nb * FDB_F * 4, cudaMemcpyDeviceToHost, s_out);
+        if (e == cudaSuccess && abs_sum) e = cudaMemcpyAsync(h_abs + b * 32, p->d_abs + 32 * sl, 32 * sizeof(double), cudaMemcpyDeviceToHost, s_out);
+        if (e == cudaSuccess) e = cudaEventRecord(p->ev[sl][2], s_out);
+    }
+    for (auto& s : ctx->slot) {
+        cudaError_t e2 = cudaStreamSynchronize(s.stream);
+        if (e == cudaSuccess) e = e2;
+    }
+    if (rc != FDB_OK) return rc;
+    FDB_CUDA(e);
+    if (abs_sum) {
+        for (int64_t b = 0; b < n_batches; ++b)
+            for (int k = 0; k < FDB_F; ++k) abs_sum[k] += h_abs[b * 32 + k];
+        abs_sum[FDB_F] = (double)n_rows;
+    }
     return FDB_OK;
 }

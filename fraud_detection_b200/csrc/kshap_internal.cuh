@@ -6,7 +6,9 @@
 #include "fdb_internal.cuh"
 
 #define FDB_KSHAP_MAX_BG 1024          // background rows the tensor-core evaluator keeps resident in smem
-#define FDB_KSHAP_BATCH_ROWS 32768     // explained rows per evaluate->solve round (bounds the ey / partial-sum scratch)
+#define FDB_KSHAP_BATCH_ROWS 32768     // explained rows per evaluate->solve round when coalition expectations go through HBM (bounds the ey scratch)
+#define FDB_KSHAP_FX_BATCH_ROWS 262144 // ... when the factored evaluator hands K3 the finished X'W y instead (256 B of scratch per row)
+#define FDB_FX_TILE_BYTES 9216         // per coalition tile of a single-set plan: x^T image (8192 B) + o_m[128] + kw_m[128]
 
 struct fdb_kshap_plan {
     fdb_ctx* ctx = nullptr;
@@ -30,15 +32,16 @@ struct fdb_kshap_plan {
     float* d_c2 = nullptr;             // [S][32]     X'W z29
     int* d_status = nullptr;           // [S] 1 = singular
     float* d_ey = nullptr;             // [batch_rows][m_pad] scratch between evaluate and solve
-    float* d_x = nullptr;              // host-API staging
-    float* d_phi = nullptr;
-    int32_t* d_set = nullptr;
-    double* d_abs = nullptr;
+    float* d_x2[2] = {nullptr, nullptr};     // host-API staging, two slots: copy-in, evaluate + solve and copy-out of
+    float* d_phi2[2] = {nullptr, nullptr};   //   consecutive batches overlap (fdb_kshap_explain_host)
+    int32_t* d_set2[2] = {nullptr, nullptr};
+    cudaEvent_t ev[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};   // per slot: rows in, phi ready, phi out
+    double* d_abs = nullptr;                 // [2][32]
     float* d_E = nullptr;              // factored evaluator (single set): [tile][chunk][128][cbs] 2^(e - o_m)
     float* d_eoff = nullptr;           // [m_pad] exponent centres o_m
     float fx_quad_logsum = 0.f;        // worst sum over a column quad of |log2 E| on one side of 0 (bounds the product of four denominators)
     float fx_half_spread = 0.f;        // largest half-spread (log2) of a coalition's background exponents around o_m
-    float* d_xw = nullptr;             // [m_pad][32] kw_m * x_mj
+    unsigned char* d_fxtile = nullptr; // factored evaluator: per tile, x^T image (B operand of the fused X'W y GEMM) + o_m + kw_m
     double* d_gz = nullptr;            // [S][30][32] Z'WZ, built on demand for l1_reg = num_features(k)
     double* d_bv = nullptr;            // [S][32]
     double* d_s0 = nullptr;            // [S]
@@ -46,7 +49,9 @@ struct fdb_kshap_plan {
     bool sampled = false;              // sets were drawn on the device and may be redrawn (fdb_kshap_plan_resample)
     int num_features = 0;              // 0 = plain WLS over all features; k = LARS selection of k features first
     uint32_t varying = 0x3FFFFFFFu;    // features that differ from the background for the rows of this plan (bit 29 always set)
-    float* d_gpart = nullptr;          // [batch_rows][m_pad/32][32] partial X'W y written by K2f, folded by K3
+    float* d_gpart = nullptr;          // [gpart_rows][slots][32] X'W y records written by K2f, folded by K3 (grown on demand)
+    size_t ey_cap = 0, gpart_cap = 0;  // floats the two scratch buffers hold
+    int64_t stage_rows = 0;            // rows the host-API staging buffers hold
     double* d_partials = nullptr;      // [FDB_MAX_GRID][32] per-CTA |phi| column sums of K3 / K3L (the plan's own: plans on
     unsigned int* d_ticket = nullptr;  //   different streams, and K1 calls on the same context, never share an arrival ticket)
 };
@@ -59,7 +64,8 @@ int fdb_kshap_launch_eval_tc(fdb_kshap_plan* p, cudaStream_t st, const float* x,
 
 // K2f: factored evaluator for single-set plans (kshap_eval_fx.cu).
 int fdb_kshap_build_factored(fdb_kshap_plan* pl, const double* bg_host);
-int fdb_kshap_launch_eval_fx(fdb_kshap_plan* pl, cudaStream_t st, const float* x, int n_rows, float* ey);
+int fdb_kshap_launch_eval_fx(fdb_kshap_plan* pl, cudaStream_t st, const float* x, int n_rows, float* ey, float* gpart);
+void fdb_kshap_fx_geometry(const fdb_kshap_plan* pl, int n_rows, long long* n_units, int* grid, int* slots);
 
 // Coalition expectations between evaluate and solve (d_ey).  Identity link: ey itself.  Logit link: an expectation
 // above 1/2 would lose its distance to 1 in float32 (1 - ey < 6e-8 already breaks logit(ey)), so the evaluators
