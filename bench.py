@@ -568,27 +568,28 @@ def bench_kernel_shap(args, torch, dist, device, rank, world, model, scaler, pro
         plan4.close()
         del x4, phi4
 
-    # the reference's behaviour: a different coalition set for every explained row, drawn on the device
+    # the reference's behaviour: a different coalition set for every explained row, drawn on the device.  Steady state of
+    # a row stream: two plans alternate on two CUDA streams (KernelShapStream), the sets of batch i + 1 are drawn and
+    # their X'WX inverted while batch i is evaluated and solved.
+    from fraud_detection_b200 import KernelShapStream
     pr = args.kshap_per_row
-    x2, phi2 = x[:pr].contiguous(), torch.empty((pr, 30), dtype=torch.float32, device=device)
-    KernelShapPlan.sampled(coef, intercept, bg, 64, nsamples, seed=0, device=device.index).close()   # warm the module
+    x2 = x[:pr].contiguous()
+    phis = [torch.empty((pr, 30), dtype=torch.float32, device=device) for _ in range(2)]
     sync()
     t0 = time.perf_counter()
-    plan2 = KernelShapPlan.sampled(coef, intercept, bg, pr, nsamples, seed=1 + rank, device=device.index)
+    stream = KernelShapStream(coef, intercept, bg, batch_rows=pr, nsamples=nsamples, seed=1 + 1000 * rank, device=device.index)
     torch.cuda.synchronize()
-    t_plan = time.perf_counter() - t0
-    ms2 = timed(lambda: plan2.explain_dev(x2, phi=phi2), steps)
-    # steady state of a row stream: the plan is kept, its sets are redrawn in place for every new batch of rows
-    n_stream = 6
-    for i in range(2):
-        plan2.resample(50 + i)
-        plan2.explain_dev(x2, phi=phi2)
+    t_plan = (time.perf_counter() - t0) / 2
+    ms2 = timed(lambda: stream.plans[0].explain_dev(x2, phi=phis[0]), steps)       # evaluate + solve only, sets kept
+    n_stream = 8
+    for i in range(4):
+        stream.explain(x2, phi=phis[i & 1])
+    stream.synchronize()
     sync()
     t0 = time.perf_counter()
     for i in range(n_stream):
-        plan2.resample(100 + n_stream * rank + i)
-        plan2.explain_dev(x2, phi=phi2)
-    torch.cuda.synchronize()
+        stream.explain(x2, phi=phis[i & 1])
+    stream.synchronize()
     t_stream = (time.perf_counter() - t0) / n_stream
     ts = torch.tensor([t_stream], dtype=torch.float64, device=device)
     if world > 1:
@@ -600,9 +601,10 @@ def bench_kernel_shap(args, torch, dist, device, rank, world, model, scaler, pro
                            "stream_ms_per_batch": t_stream * 1e3,
                            "evaluate_only_value": pr * world / (ms2 * 1e-3), "evaluate_only_ms": ms2,
                            "plan_ms": t_plan * 1e3,
-                           "note": "value = fdb_kshap_plan_resample (draw the sets, per-set (X'WX)^-1) + evaluate + solve per batch, wall "
-                                   "clock, fresh sets every batch; evaluate_only keeps the sets; plan_ms = first creation incl. allocation"}
-    plan2.close()
+                           "note": "value = per batch: draw the sets + per-set (X'WX)^-1 + evaluate + solve, two plans alternating on two "
+                                   "streams (KernelShapStream), wall clock over 8 batches, fresh sets every batch; evaluate_only keeps the "
+                                   "sets; plan_ms = creating one plan incl. allocation"}
+    stream.close()
 
     # Rooflines against pipe rates measured in this process (fdb_probe_pipes), nominal figures beside them.
     sms = torch.cuda.get_device_properties(device).multi_processor_count

@@ -12,6 +12,6 @@ serving classes do not pull torch into a gunicorn/Celery worker.
 
 from ._lib import FdbError, PinnedBuffer, get_ctx, host_near_gpu, lib  # noqa: F401
 from .estimators import B200LogisticRegression, B200StandardScaler, from_joblib, wrap  # noqa: F401
-from .explainers import B200KernelExplainer, B200LinearExplainer, KernelShapPlan  # noqa: F401
+from .explainers import B200KernelExplainer, B200LinearExplainer, KernelShapPlan, KernelShapStream  # noqa: F401
 
 __version__ = "0.1.0"

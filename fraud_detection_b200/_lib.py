@@ -56,6 +56,8 @@ _SIGS = {
     "fdb_kshap_plan_create_sampled": (_i, [_vp, _dp, C.c_double, _i, _vp, _i, _i, C.c_uint64, _i, C.POINTER(_vp)]),
     "fdb_kshap_plan_get_masks": (_i, [_vp, _i, _vp, _vp]),
     "fdb_kshap_plan_resample": (_i, [_vp, C.c_uint64]),
+    "fdb_kshap_plan_resample_dev": (_i, [_vp, _vp, C.c_uint64]),
+    "fdb_kshap_plan_status": (_i, [_vp, C.POINTER(C.c_int)]),
     "fdb_kshap_plan_destroy": (_i, [_vp]),
     "fdb_kshap_expected_value": (C.c_double, [_vp]),
     "fdb_kshap_plan_info": (_i, [_vp, C.POINTER(C.c_int)]),

@@ -67,7 +67,7 @@ __global__ void kshap_expand_masks(const uint32_t* __restrict__ bits, uint16_t* 
 // are lane k's column and travel by shuffle.  No shared memory, no barriers.
 __global__ void __launch_bounds__(32) kshap_wls_prepare(const uint32_t* __restrict__ bits, const float* __restrict__ kw,
                                                         int m_pad, float* __restrict__ ainv, float* __restrict__ c2out,
-                                                        int* __restrict__ status, uint32_t varying) {
+                                                        int* __restrict__ status, uint32_t varying, int* __restrict__ bad) {
     const int s = blockIdx.x;
     const int lane = threadIdx.x;
     const uint32_t* sb = bits + (size_t)s * m_pad;
@@ -115,7 +115,10 @@ __global__ void __launch_bounds__(32) kshap_wls_prepare(const uint32_t* __restri
 #pragma unroll
     for (int i = 0; i < kNV; ++i)
         ainv[((size_t)s * kNV + i) * 32 + lane] = (lane < kNV && !singular) ? (float)inv[i] : 0.f;
-    if (lane == 0) status[s] = singular ? 1 : 0;
+    if (lane == 0) {
+        status[s] = singular ? 1 : 0;
+        if (singular) atomicAdd(bad, 1);          // polled by fdb_kshap_plan_status; a singular set yields phi = 0 except the last feature
+    }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -272,7 +275,8 @@ void free_plan(fdb_kshap_plan* p) {
     cudaFree(p->d_bits); cudaFree(p->d_kw); cudaFree(p->d_P); cudaFree(p->d_wq); cudaFree(p->d_bimg); cudaFree(p->d_aimg);
     cudaFree(p->d_ainv); cudaFree(p->d_c2); cudaFree(p->d_status); cudaFree(p->d_ey);
     cudaFree(p->d_abs); cudaFree(p->d_E); cudaFree(p->d_eoff); cudaFree(p->d_fxtile); cudaFree(p->d_gpart); cudaFree(p->d_gz); cudaFree(p->d_bv); cudaFree(p->d_s0);
-    cudaFree(p->d_partials); cudaFree(p->d_ticket);
+    cudaFree(p->d_partials); cudaFree(p->d_ticket); cudaFree(p->d_bad);
+    fdb_kshap_sampler_free(p);
     for (int i = 0; i < 2; ++i) {
         cudaFree(p->d_x2[i]); cudaFree(p->d_phi2[i]); cudaFree(p->d_set2[i]);
         for (int e = 0; e < 3; ++e)
@@ -295,6 +299,15 @@ void fdb_kshap_split(double v, int fmt, int n, uint16_t* out) {
 
 // Everything derived from the coalition sets (d_bits / d_kw): operand tile images, per-set (X'WX)^-1 and, for a
 // single set, the factored evaluator's operands.  Run at plan creation and again after a resample.
+// Stream-ordered part of the refresh for plans with several sets: per-set (X'WX)^-1 (and the Z'WZ products when feature
+// selection is on), enqueued on `st` with no host synchronisation.  Singular sets are counted in d_bad.
+static int refresh_set_products_async(fdb_kshap_plan* p, cudaStream_t st) {
+    kshap_wls_prepare<<<p->n_sets, 32, 0, st>>>(p->d_bits, p->d_kw, p->m_pad, p->d_ainv, p->d_c2, p->d_status, p->varying, p->d_bad);
+    FDB_CUDA(cudaGetLastError());
+    if (p->d_gz) return fdb_kshap_refresh_lars(p, st);
+    return FDB_OK;
+}
+
 static int refresh_set_products(fdb_kshap_plan* p) {
     const size_t SM = (size_t)p->n_sets * p->m_pad;
     const uint16_t one = p->fmt == 0 ? 0x3C00 : 0x3F80;
@@ -302,9 +315,10 @@ static int refresh_set_products(fdb_kshap_plan* p) {
         kshap_expand_masks<<<(unsigned)((SM + 255) / 256), 256>>>(p->d_bits, p->d_aimg, (int64_t)SM, one);
         FDB_CUDA(cudaGetLastError());
     }
-    kshap_wls_prepare<<<p->n_sets, 32>>>(p->d_bits, p->d_kw, p->m_pad, p->d_ainv, p->d_c2, p->d_status, p->varying);
+    kshap_wls_prepare<<<p->n_sets, 32>>>(p->d_bits, p->d_kw, p->m_pad, p->d_ainv, p->d_c2, p->d_status, p->varying, p->d_bad);
     FDB_CUDA(cudaGetLastError());
     FDB_CUDA(cudaDeviceSynchronize());
+    FDB_CUDA(cudaMemset(p->d_bad, 0, sizeof(int)));
     std::vector<int> st(p->n_sets);
     FDB_CUDA(cudaMemcpy(st.data(), p->d_status, (size_t)p->n_sets * 4, cudaMemcpyDeviceToHost));
     for (int s = 0; s < p->n_sets; ++s)
@@ -413,12 +427,15 @@ static int plan_create_impl(fdb_ctx* ctx, const double* coef, double intercept, 
         TRY(cudaMalloc((void**)&p->d_partials, (size_t)FDB_MAX_GRID * 32 * sizeof(double)));
         TRY(cudaMalloc((void**)&p->d_ticket, sizeof(unsigned int)));
         TRY(cudaMemset(p->d_ticket, 0, sizeof(unsigned int)));
+        TRY(cudaMalloc((void**)&p->d_bad, sizeof(int)));
+        TRY(cudaMemset(p->d_bad, 0, sizeof(int)));
         if (bits) {
             TRY(cudaMemcpy(p->d_bits, hbits.data(), SM * 4, cudaMemcpyHostToDevice));
             TRY(cudaMemcpy(p->d_kw, hkw.data(), SM * 4, cudaMemcpyHostToDevice));
         } else {
-            rc = fdb_kshap_sample_on_device(p, n_masks, seed);
+            rc = fdb_kshap_sample_on_device(p, nullptr, n_masks, seed);
             if (rc != FDB_OK) break;
+            TRY(cudaDeviceSynchronize());
         }
         TRY(cudaMemcpy(p->d_P, P.data(), P.size() * 4, cudaMemcpyHostToDevice));
         TRY(cudaMemcpy(p->d_wq, wq, 32 * 4, cudaMemcpyHostToDevice));
@@ -467,9 +484,31 @@ extern "C" int fdb_kshap_plan_resample(fdb_kshap_plan* p, uint64_t seed) {
     DeviceGuard guard(p->ctx->device);
     FDB_REQUIRE(guard.ok, FDB_ERR_CUDA, "cannot select device %d", p->ctx->device);
     FDB_CUDA(cudaDeviceSynchronize());
-    int rc = fdb_kshap_sample_on_device(p, p->n_masks, (unsigned long long)seed);
+    int rc = fdb_kshap_sample_on_device(p, nullptr, p->n_masks, (unsigned long long)seed);
     if (rc != FDB_OK) return rc;
+    FDB_CUDA(cudaDeviceSynchronize());
     return refresh_set_products(p);
+}
+
+extern "C" int fdb_kshap_plan_resample_dev(fdb_kshap_plan* p, void* stream, uint64_t seed) {
+    FDB_REQUIRE(p != nullptr, FDB_ERR_ARG, "plan is NULL");
+    FDB_REQUIRE(p->sampled, FDB_ERR_STATE, "only plans made by fdb_kshap_plan_create_sampled can be resampled");
+    FDB_REQUIRE(p->n_sets > 1, FDB_ERR_STATE, "a single-set plan rebuilds the factored evaluator's operands on the host: use fdb_kshap_plan_resample");
+    int cur = -1;
+    FDB_CUDA(cudaGetDevice(&cur));
+    FDB_REQUIRE(cur == p->ctx->device, FDB_ERR_STATE, "the plan lives on device %d but the current device is %d", p->ctx->device, cur);
+    int rc = fdb_kshap_sample_on_device(p, (cudaStream_t)stream, p->n_masks, (unsigned long long)seed);
+    if (rc != FDB_OK) return rc;
+    return refresh_set_products_async(p, (cudaStream_t)stream);
+}
+
+extern "C" int fdb_kshap_plan_status(fdb_kshap_plan* p, int* n_singular) {
+    FDB_REQUIRE(p != nullptr && n_singular != nullptr, FDB_ERR_ARG, "NULL argument");
+    DeviceGuard guard(p->ctx->device);
+    FDB_REQUIRE(guard.ok, FDB_ERR_CUDA, "cannot select device %d", p->ctx->device);
+    FDB_CUDA(cudaMemcpy(n_singular, p->d_bad, sizeof(int), cudaMemcpyDeviceToHost));
+    FDB_CUDA(cudaMemset(p->d_bad, 0, sizeof(int)));
+    return FDB_OK;
 }
 
 extern "C" int fdb_kshap_plan_get_masks(const fdb_kshap_plan* p, int set, uint32_t* bits, float* kw) {

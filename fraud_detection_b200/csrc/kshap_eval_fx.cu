@@ -102,7 +102,13 @@ __device__ __forceinline__ float fx_from_h16(uint16_t h, int fmt) {
 //   the same reciprocal:  sum_quad g_i / d_i = ((g0 d1 + g1 d0) p23 + (g2 d3 + g3 d2) p01) / (p01 p23).  accc gathers
 //   them; with both sums the stored expectation is exact to float32 in both tails (fdb_kshap_encode_ey).
 #ifndef FDB_FX_QUAD_UNROLL
-#define FDB_FX_QUAD_UNROLL 2      // quads of one coalition in flight (x 4 interleaved coalitions)
+#define FDB_FX_QUAD_UNROLL 2      // quads of one coalition in flight (x 4 interleaved coalitions), multi-chunk backgrounds
+#endif
+#ifndef FDB_FX_QUAD_UNROLL_SINGLE
+#define FDB_FX_QUAD_UNROLL_SINGLE 3   // ... single-chunk backgrounds: no per-coalition partial sums in registers, room for three
+#endif                                //     (measured at config 3, ms per 100k rows: 1 -> 2.97, 2 -> 2.91, 3 -> 2.77, 4 -> 2.83)
+#ifndef FDB_FX_PREFETCH_MULTI
+#define FDB_FX_PREFETCH_MULTI 0   // multi-chunk backgrounds: fetch the next group's exponents from TMEM ahead of the sums (costs 4 registers)
 #endif
 #define FDB_FX_PRAGMA(x) _Pragma(#x)
 #define FDB_FX_UNROLL(n) FDB_FX_PRAGMA(unroll n)
@@ -120,13 +126,13 @@ __device__ __forceinline__ void fx_scales(const float (&t)[4], float (&a)[4], fl
 
 // sums of this chunk are gathered apart and added to the running totals once: with ~1000 background rows a
 // single float32 chain drifts by 1e-5 on saturated coalitions (every term 1, every add rounded the same way)
-template <int MODE>
+template <int MODE, int UNROLL>
 __device__ __forceinline__ void chunk_sum4(const float* __restrict__ e0, int cbs, int nquads, int ntail,
                                            const float (&a)[4], const float (&b)[4], float (&sum)[4]) {
     constexpr float kClamp = MODE == kFxClampedPairs ? 4.611686018427388e18f : 1073741824.f;
 #pragma unroll
     for (int mm = 0; mm < 4; ++mm) sum[mm] = 0.f;
-FDB_FX_UNROLL(FDB_FX_QUAD_UNROLL)
+#pragma unroll UNROLL
     for (int q = 0; q < nquads; ++q) {
 #pragma unroll
         for (int mm = 0; mm < 4; ++mm) {
@@ -466,7 +472,7 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
                     if (g4 < 7) load_t(g4 + 1, rr);
                     fx_scales<MODE>(t4, a, b);
                     if (MODE == kFxBalancedLogit) chunk_sum4_logit(eb + (size_t)g4 * 4 * cbs, cbs, cbw >> 2, cbw & 3, a, b, S, C);
-                    else chunk_sum4<MODE>(eb + (size_t)g4 * 4 * cbs, cbs, cbw >> 2, cbw & 3, a, b, S);
+                    else chunk_sum4<MODE, FDB_FX_QUAD_UNROLL_SINGLE>(eb + (size_t)g4 * 4 * cbs, cbs, cbw >> 2, cbw & 3, a, b, S);
                     if (g4 == 0) before_first_store();
                     fx_finish4<MODE>(S, C, b, kwp[g4], p.inv_bg, p.lnull, a2 + 2 * g4, st);
                     if (eyd != nullptr) eyd[g4] = make_float4(st[0], st[1], st[2], st[3]);
@@ -488,20 +494,21 @@ __global__ void __launch_bounds__(kFxThreads, 1) kshap_eval_fx_kernel(const FxPa
                     ptx::mbar_wait(&bars->e_full[es], (j >> 1) & 1);
                     const float* eb = reinterpret_cast<const float*>(sE + es * kEStageBytes) + (size_t)cg * 32 * cbs;
                     uint32_t rr[4];
-                    load_t(0, rr);
+                    if (FDB_FX_PREFETCH_MULTI) load_t(0, rr);
 #pragma unroll
                     for (int g4 = 0; g4 < 8; ++g4) {
                         float t4[4], a[4], b[4], S[4], C[4];
+                        if (!FDB_FX_PREFETCH_MULTI) load_t(g4, rr);
                         ptx::tmem_ld_wait();
                         exps(rr, g4, t4);
-                        if (g4 < 7) load_t(g4 + 1, rr);
+                        if (FDB_FX_PREFETCH_MULTI && g4 < 7) load_t(g4 + 1, rr);
                         fx_scales<MODE>(t4, a, b);
                         if (MODE == kFxBalancedLogit) {
                             chunk_sum4_logit(eb + (size_t)g4 * 4 * cbs, cbs, cbw >> 2, cbw & 3, a, b, S, C);
 #pragma unroll
                             for (int mm = 0; mm < 4; ++mm) partc[MODE == kFxBalancedLogit ? 4 * g4 + mm : 0] += C[mm];
                         } else {
-                            chunk_sum4<MODE>(eb + (size_t)g4 * 4 * cbs, cbs, cbw >> 2, cbw & 3, a, b, S);
+                            chunk_sum4<MODE, FDB_FX_QUAD_UNROLL>(eb + (size_t)g4 * 4 * cbs, cbs, cbw >> 2, cbw & 3, a, b, S);
                         }
 #pragma unroll
                         for (int mm = 0; mm < 4; ++mm) part[4 * g4 + mm] += S[mm];

@@ -52,6 +52,8 @@ struct fdb_kshap_plan {
     float* d_gpart = nullptr;          // [gpart_rows][slots][32] X'W y records written by K2f, folded by K3 (grown on demand)
     size_t ey_cap = 0, gpart_cap = 0;  // floats the two scratch buffers hold
     int64_t stage_rows = 0;            // rows the host-API staging buffers hold
+    void* sampler_state = nullptr;     // device-sampled plans: the uploaded sampling schedule (kshap_sampler.cu)
+    int* d_bad = nullptr;              // number of coalition sets whose X'WX came out singular since the last check (resample_dev)
     double* d_partials = nullptr;      // [FDB_MAX_GRID][32] per-CTA |phi| column sums of K3 / K3L (the plan's own: plans on
     unsigned int* d_ticket = nullptr;  //   different streams, and K1 calls on the same context, never share an arrival ticket)
 };
@@ -154,9 +156,11 @@ __device__ __forceinline__ void fdb_kshap_weighted_gram_row(const uint32_t* __re
 
 // l1_reg = "num_features(k)": LARS selection + reduced WLS (kshap_lars.cu)
 int fdb_kshap_prepare_lars(fdb_kshap_plan* p);
+int fdb_kshap_refresh_lars(fdb_kshap_plan* p, cudaStream_t st);
 int fdb_kshap_launch_lars_solve(fdb_kshap_plan* p, cudaStream_t st, const float* x, int64_t row_offset, int n_rows,
                                 const int32_t* set_idx, float* phi, double* abs_sum, int accumulate, int64_t total_rows);
 
 // on-device coalition sampler (kshap_sampler.cu)
 int fdb_kshap_resolve_nsamples(int nsamples);
-int fdb_kshap_sample_on_device(fdb_kshap_plan* pl, int nsamples, unsigned long long seed);
+int fdb_kshap_sample_on_device(fdb_kshap_plan* pl, cudaStream_t stream, int nsamples, unsigned long long seed);
+void fdb_kshap_sampler_free(fdb_kshap_plan* pl);

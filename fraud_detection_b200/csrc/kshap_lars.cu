@@ -340,6 +340,14 @@ int fdb_kshap_prepare_lars(fdb_kshap_plan* p) {
     return FDB_OK;
 }
 
+// after a resample: the same products for the new sets, stream-ordered, buffers kept
+int fdb_kshap_refresh_lars(fdb_kshap_plan* p, cudaStream_t st) {
+    if (p->d_gz == nullptr) return FDB_OK;
+    kshap_gram_prepare<<<p->n_sets, 32, 0, st>>>(p->d_bits, p->d_kw, p->m_pad, p->d_gz, p->d_bv, p->d_s0, p->varying);
+    FDB_CUDA(cudaGetLastError());
+    return FDB_OK;
+}
+
 int fdb_kshap_launch_lars_solve(fdb_kshap_plan* p, cudaStream_t st, const float* x, int64_t row_offset, int n_rows,
                                 const int32_t* set_idx, float* phi, double* abs_sum, int accumulate, int64_t total_rows) {
     int grid = (n_rows + 3) / 4;

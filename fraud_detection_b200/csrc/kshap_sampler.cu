@@ -21,6 +21,7 @@
 #include <curand_kernel.h>
 #include <math.h>
 
+#include <new>
 #include <vector>
 
 #include "kshap_internal.cuh"
@@ -195,8 +196,27 @@ int fdb_kshap_resolve_nsamples(int nsamples) {
     return (long long)nsamples > cap ? (int)cap : nsamples;
 }
 
-// Fills plan->d_bits / d_kw for all sets.  nsamples must already be resolved; M is fixed at 30 features.
-int fdb_kshap_sample_on_device(fdb_kshap_plan* pl, int nsamples, unsigned long long seed) {
+// The sampling schedule (enumerated block, size distribution) depends only on nsamples: it is worked out and uploaded
+// ONCE per plan and kept (plan->sampler_state), so that redrawing the sets is a single kernel launch with no
+// allocation, copy or host synchronisation.
+namespace {
+struct SamplerState {
+    SamplerParams sp;
+    uint32_t* d_fb = nullptr;
+    float* d_fw = nullptr;
+};
+}  // namespace
+
+void fdb_kshap_sampler_free(fdb_kshap_plan* pl) {
+    SamplerState* st = static_cast<SamplerState*>(pl->sampler_state);
+    if (!st) return;
+    cudaFree(st->d_fb);
+    cudaFree(st->d_fw);
+    delete st;
+    pl->sampler_state = nullptr;
+}
+
+static int sampler_prepare(fdb_kshap_plan* pl, int nsamples) {
     FDB_REQUIRE(nsamples >= 64 && nsamples <= 4096, FDB_ERR_ARG,
                 "the on-device sampler supports 64 <= nsamples <= 4096 (got %d); use host-drawn masks otherwise", nsamples);
     const int M = FDB_F;
@@ -235,10 +255,12 @@ int fdb_kshap_sample_on_device(fdb_kshap_plan* pl, int nsamples, unsigned long l
             break;
         }
     }
-    SamplerParams sp;
+    SamplerState* st = new (std::nothrow) SamplerState();
+    FDB_REQUIRE(st != nullptr, FDB_ERR_NOMEM, "out of host memory");
+    SamplerParams& sp = st->sp;
     sp.bits = pl->d_bits; sp.kw = pl->d_kw; sp.m_pad = pl->m_pad; sp.nsamples = nsamples;
     sp.n_fixed = (int)fb.size();
-    sp.n_sizes = n_sizes - n_full; sp.first_size = n_full + 1; sp.n_paired = n_paired; sp.seed = seed;
+    sp.n_sizes = n_sizes - n_full; sp.first_size = n_full + 1; sp.n_paired = n_paired; sp.seed = 0ULL;
     sp.fixed_w = 0.f;
     double weight_left = 0.0, csum = 0.0, tot = 0.0;
     std::vector<double> pr;
@@ -249,27 +271,40 @@ int fdb_kshap_sample_on_device(fdb_kshap_plan* pl, int nsamples, unsigned long l
         pr.push_back(v);
         tot += v;
     }
+    for (int i = 0; i < kMaxSizes; ++i) sp.cdf[i] = 1.0f;
     for (size_t i = 0; i < pr.size() && i < (size_t)kMaxSizes; ++i) {
         csum += pr[i] / tot;
         sp.cdf[i] = (float)csum;
     }
     sp.weight_left = (float)weight_left;
-    uint32_t* d_fb = nullptr;
-    float* d_fw = nullptr;
-    FDB_CUDA(cudaMalloc((void**)&d_fb, (fb.size() + 1) * 4));
-    cudaError_t e = cudaMalloc((void**)&d_fw, (fw.size() + 1) * 4);
-    if (e == cudaSuccess && !fb.empty()) e = cudaMemcpy(d_fb, fb.data(), fb.size() * 4, cudaMemcpyHostToDevice);
-    if (e == cudaSuccess && !fw.empty()) e = cudaMemcpy(d_fw, fw.data(), fw.size() * 4, cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) {
-        sp.fixed_bits = d_fb;
-        sp.fixed_kw = d_fw;
-        if (nsamples <= 2048) kshap_sample_sets<2048, 21, 2048><<<pl->n_sets, 32>>>(sp);
-        else kshap_sample_sets<4096, 20, 4096><<<pl->n_sets, 32>>>(sp);
-        e = cudaGetLastError();
+    cudaError_t e = cudaMalloc((void**)&st->d_fb, (fb.size() + 1) * 4);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&st->d_fw, (fw.size() + 1) * 4);
+    if (e == cudaSuccess && !fb.empty()) e = cudaMemcpy(st->d_fb, fb.data(), fb.size() * 4, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && !fw.empty()) e = cudaMemcpy(st->d_fw, fw.data(), fw.size() * 4, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        cudaFree(st->d_fb); cudaFree(st->d_fw);
+        delete st;
+        FDB_CUDA(e);
     }
-    if (e == cudaSuccess) e = cudaDeviceSynchronize();
-    cudaFree(d_fb);
-    cudaFree(d_fw);
-    FDB_CUDA(e);
+    sp.fixed_bits = st->d_fb;
+    sp.fixed_kw = st->d_fw;
+    pl->sampler_state = st;
+    return FDB_OK;
+}
+
+// Fills plan->d_bits / d_kw for all sets: one kernel on `stream`, no synchronisation.  nsamples must already be
+// resolved (and stay the same for the life of the plan); M is fixed at 30 features.
+int fdb_kshap_sample_on_device(fdb_kshap_plan* pl, cudaStream_t stream, int nsamples, unsigned long long seed) {
+    if (pl->sampler_state == nullptr) {
+        int rc = sampler_prepare(pl, nsamples);
+        if (rc != FDB_OK) return rc;
+    }
+    SamplerState* st = static_cast<SamplerState*>(pl->sampler_state);
+    FDB_REQUIRE(st->sp.nsamples == nsamples, FDB_ERR_STATE, "the plan was created for nsamples = %d", st->sp.nsamples);
+    SamplerParams sp = st->sp;
+    sp.seed = seed;
+    if (nsamples <= 2048) kshap_sample_sets<2048, 21, 2048><<<pl->n_sets, 32, 0, stream>>>(sp);
+    else kshap_sample_sets<4096, 20, 4096><<<pl->n_sets, 32, 0, stream>>>(sp);
+    FDB_CUDA(cudaGetLastError());
     return FDB_OK;
 }

@@ -241,9 +241,24 @@ class KernelShapPlan:
         self.n_sets, self.n_masks = info["n_sets"], info["n_masks"]
         return self
 
-    def resample(self, seed: int) -> None:
-        """Redraw all coalition sets of a device-sampled plan in place (fresh coalitions for the next rows)."""
-        _lib.check(_lib.lib.fdb_kshap_plan_resample(self._h, int(seed) & 0xFFFFFFFFFFFFFFFF))
+    def resample(self, seed: int, stream=None) -> None:
+        """Redraw all coalition sets of a device-sampled plan in place (fresh coalitions for the next rows).
+        ``stream`` (a raw ``cudaStream_t`` value, or ``"current"`` for torch's current stream): enqueue the redraw there
+        with no host synchronisation (plans with more than one set; see ``KernelShapStream``)."""
+        if stream is None:
+            _lib.check(_lib.lib.fdb_kshap_plan_resample(self._h, int(seed) & 0xFFFFFFFFFFFFFFFF))
+            return
+        if stream == "current":
+            import torch
+            stream = int(torch.cuda.current_stream().cuda_stream)
+        _lib.check(_lib.lib.fdb_kshap_plan_resample_dev(self._h, int(stream), int(seed) & 0xFFFFFFFFFFFFFFFF))
+
+    def singular_sets(self) -> int:
+        """Coalition sets whose X'WX came out singular since the last call (stream-ordered redraws cannot raise)."""
+        import ctypes as C
+        n = C.c_int(0)
+        _lib.check(_lib.lib.fdb_kshap_plan_status(self._h, C.byref(n)))
+        return int(n.value)
 
     def masks(self, set_index: int = 0):
         """(bits uint32 (n_masks,), kernel weights float32 (n_masks,)) of one coalition set, copied from the device."""
@@ -293,6 +308,61 @@ class KernelShapPlan:
             self.close()
         except Exception:
             pass
+
+
+class KernelShapStream:
+    """Explains a STREAM of row batches with a fresh coalition set per row - what ``shap.KernelExplainer`` does - at
+    full device rate: two device-sampled plans alternate on two CUDA streams, so the sets of batch i + 1 are drawn (and
+    their X'WX inverted) while batch i is evaluated and solved.  Device tensors in and out; ``explain`` returns as soon
+    as the work is enqueued, ``synchronize`` waits for everything and raises if a set was singular."""
+
+    def __init__(self, coef, intercept, background, batch_rows: int = 32768, nsamples="auto", seed: int = 0, link="identity",
+                 device=None, num_features: int = 0):
+        import torch
+        self.device = torch.device("cuda", torch.cuda.current_device() if device is None else int(device))
+        self.batch_rows = int(batch_rows)
+        self.plans = [KernelShapPlan.sampled(coef, intercept, background, self.batch_rows, nsamples, seed + i, link, self.device.index)
+                      for i in range(2)]
+        for p in self.plans:
+            if num_features:
+                p.set_num_features(num_features)
+        self.streams = [torch.cuda.Stream(self.device) for _ in range(2)]
+        self.expected_value = self.plans[0].expected_value
+        self._seed = int(seed) + 2
+        self._i = 0
+        self._fresh = [True, True]          # the sets drawn at creation serve each plan's first batch
+
+    def explain(self, x, phi=None, evaluator=EVAL_AUTO, abs_sum=None):
+        """x: (n <= batch_rows, 30) float32 CUDA tensor.  Enqueues redraw + evaluate + solve; returns phi (same stream
+        semantics as torch: use ``synchronize`` or the returned tensor on ``stream_of_last`` before reading it)."""
+        import torch
+        if x.shape[0] > self.batch_rows:
+            raise ValueError(f"at most {self.batch_rows} rows per batch")
+        k = self._i & 1
+        plan, st = self.plans[k], self.streams[k]
+        st.wait_stream(torch.cuda.current_stream(self.device))      # x was produced on the caller's stream
+        with torch.cuda.stream(st):
+            if not self._fresh[k]:
+                plan.resample(self._seed, stream=int(st.cuda_stream))
+                self._seed += 1
+            self._fresh[k] = False
+            phi = plan.explain_dev(x, evaluator=evaluator, phi=phi, abs_sum=abs_sum, stream=int(st.cuda_stream))
+        self._i += 1
+        self.stream_of_last = st
+        return phi
+
+    def synchronize(self):
+        import torch
+        for st in self.streams:
+            st.synchronize()
+        bad = sum(p.singular_sets() for p in self.plans)
+        if bad:
+            raise ValueError(f"{bad} coalition sets gave a singular weighted least-squares system (X'WX); use more samples")
+        torch.cuda.current_stream(self.device).wait_stream(self.streams[0])
+
+    def close(self):
+        for p in self.plans:
+            p.close()
 
 
 class B200KernelExplainer:

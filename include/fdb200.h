@@ -158,6 +158,13 @@ int fdb_kshap_plan_get_masks(const fdb_kshap_plan* plan, int set, uint32_t* bits
 /* Redraw every coalition set of a sampled plan in place (no allocation of the large buffers): fresh coalitions for
  * the next batch of rows, as the reference draws them per explain() call. */
 int fdb_kshap_plan_resample(fdb_kshap_plan* plan, uint64_t seed);
+/* The same for plans with more than one set, ENQUEUED on a stream (void* = cudaStream_t) with no host synchronisation:
+ * two kernels (draw the sets, per-set (X'WX)^-1), so that a row stream can alternate two plans on two streams and draw
+ * the sets of batch i + 1 while batch i is being explained.  A set whose X'WX turns out singular (practically impossible
+ * at >= 256 samples over 30 features) cannot raise here: its rows get phi = 0 except for the last feature, and
+ * fdb_kshap_plan_status reports (and clears) how many such sets were seen since the last call. */
+int fdb_kshap_plan_resample_dev(fdb_kshap_plan* plan, void* stream, uint64_t seed);
+int fdb_kshap_plan_status(fdb_kshap_plan* plan, int* n_singular);
 int fdb_kshap_plan_destroy(fdb_kshap_plan* plan);
 double fdb_kshap_expected_value(const fdb_kshap_plan* plan);
 int fdb_kshap_plan_info(const fdb_kshap_plan* plan, int* info8);
