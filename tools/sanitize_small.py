@@ -37,3 +37,16 @@ plan.explain_dev(xr[:8])
 plan.close()
 torch.cuda.synchronize()
 print("sanitize_small: done")
+# stream-ordered redraw and the multi-chunk factored path (n_bg > 128)
+from fraud_detection_b200 import KernelShapStream  # noqa: E402
+st = KernelShapStream(prm.coef, prm.intercept, bg, batch_rows=16, nsamples=256, seed=2)
+for i in range(3):
+    st.explain(xr[:16])
+st.synchronize()
+st.close()
+bits, kw = sampler.sample_coalitions(30, 200, np.random.RandomState(1))
+plan = KernelShapPlan(prm.coef, prm.intercept, scoring.transform(prm, synth.rows(40, seed=44)), bits, kw, link="logit")
+plan.explain_dev(xr[:150], evaluator=2)
+plan.close()
+torch.cuda.synchronize()
+print("sanitize_small: stream + logit done")
