@@ -44,9 +44,9 @@ UNIT = "rows/s"
 BYTES_PER_ROW = 244           # 120 B x in + 4 B proba + 120 B phi
 FALLBACK_HBM_GBS = 6650.0     # B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
 # dram__bytes_read.sum + dram__bytes_write.sum of linear_pass_tma_kernel<float,0,1> from ONE `ncu --set full` capture
-# (not re-measured by this run): 2e7 rows, 2.400650 GB read + 2.436800 GB written; scaled to the launch's row count
-NCU_TRAFFIC_SOURCE = "profiles/r01/ncu_k1_tma.txt"
-NCU_TRAFFIC_BYTES_PER_ROW = (2.400650e9 + 2.436800e9) / 2.0e7
+# (not re-measured by this run): 2e7 rows, 2.400175 GB read + 2.436786 GB written; scaled to the launch's row count
+NCU_TRAFFIC_SOURCE = "profiles/r02/ncu_k1_tma.txt"
+NCU_TRAFFIC_BYTES_PER_ROW = (2.400175e9 + 2.436786e9) / 2.0e7
 CONFIG1_ROWS = 284_807
 CONFIG5_BATCHES = (1, 64, 4096)
 FEATURE_NAMES = ["Time"] + [f"V{i}" for i in range(1, 29)] + ["Amount"]

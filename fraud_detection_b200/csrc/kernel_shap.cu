@@ -451,6 +451,15 @@ static int plan_create_impl(fdb_ctx* ctx, const double* coef, double intercept, 
         p->sampled = bits == nullptr;
         rc = refresh_set_products(p);
     }
+    // A plan must have at least one fast evaluator that can run: the tensor-core one keeps the whole background
+    // resident in shared memory (192 B per row in the bf16 x 3 format that large-magnitude rows need), the factored one
+    // exists for single-set plans only.  Say so here, not at the first explain call.
+    if (rc == FDB_OK && fdb_kshap_tc_smem_bytes(p) > 227 * 1024 && !(p->n_sets == 1 && p->d_E != nullptr)) {
+        fdb_set_error("a background of %d rows in the %s operand format needs %zu bytes of shared memory per SM (limit %d): "
+                      "use at most %d background rows for this model", n_bg, p->fmt == 0 ? "f16 x 2" : "bf16 x 3",
+                      fdb_kshap_tc_smem_bytes(p), 227 * 1024, p->fmt == 0 ? FDB_KSHAP_MAX_BG : 800);
+        rc = FDB_ERR_ARG;
+    }
     if (rc != FDB_OK) { free_plan(p); return rc; }
     *out = p;
     return FDB_OK;

@@ -400,6 +400,11 @@ __global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcPa
 
 }  // namespace
 
+// shared memory one CTA of the tensor-core evaluator needs for this plan (resident B image + A / Bq stages + barriers)
+size_t fdb_kshap_tc_smem_bytes(const fdb_kshap_plan* pl) {
+    return (size_t)pl->nsplit * pl->nb_pad * 64 + kPipes * kAStages * (kATileBytes + kBqBytes) + sizeof(TcBars) + 64;
+}
+
 int fdb_kshap_launch_eval_tc(fdb_kshap_plan* pl, cudaStream_t st, const float* x, int64_t row_offset, int n_rows,
                              const int32_t* set_idx, float* ey) {
     TcParams p;
@@ -409,7 +414,7 @@ int fdb_kshap_launch_eval_tc(fdb_kshap_plan* pl, cudaStream_t st, const float* x
     p.n_chunks = (pl->nb_pad + kBufCols - 1) / kBufCols;
     p.chunk_cols = kBufCols;
     p.inv_bg = 1.0f / (float)pl->n_bg;
-    const size_t smem = (size_t)pl->nsplit * pl->nb_pad * 64 + kPipes * kAStages * (kATileBytes + kBqBytes) + sizeof(TcBars) + 64;
+    const size_t smem = fdb_kshap_tc_smem_bytes(pl);
     FDB_REQUIRE(smem <= 227 * 1024, FDB_ERR_ARG, "background of %d rows with %d operand splits needs %zu bytes of shared memory",
                 pl->n_bg, pl->nsplit, smem);
     static size_t configured[FDB_MAX_DEVICES] = {};        // function attributes are per device

@@ -64,6 +64,8 @@ void fdb_kshap_split(double v, int fmt, int n, uint16_t* out);
 int fdb_kshap_launch_eval_tc(fdb_kshap_plan* p, cudaStream_t st, const float* x, int64_t row_offset, int n_rows,
                              const int32_t* set_idx, float* ey);
 
+size_t fdb_kshap_tc_smem_bytes(const fdb_kshap_plan* pl);
+
 // K2f: factored evaluator for single-set plans (kshap_eval_fx.cu).
 int fdb_kshap_build_factored(fdb_kshap_plan* pl, const double* bg_host);
 int fdb_kshap_launch_eval_fx(fdb_kshap_plan* pl, cudaStream_t st, const float* x, int n_rows, float* ey, float* gpart);

@@ -112,7 +112,8 @@ int fdb_linear_pass_host(fdb_ctx* ctx, int dtype, int64_t n_rows, const void* x,
  * shap==0.49.1 is pinned at requirements.txt:21, the reference holds no call site).
  *
  * A plan fixes the model (coef, intercept in the space of the rows being explained), the
- * background (n_bg x 30, host doubles, at most 1024 rows) and one or more coalition mask
+ * background (n_bg x 30, host doubles, at most 1024 rows; at most 800 when some |log2e * coef * bg| reaches 16384 - the
+ * bf16 operand format - and the plan has several coalition sets: creation fails with FDB_ERR_ARG beyond that) and one or more coalition mask
  * sets: bits[s][m] has bit k set when feature k takes the explained row's value, kw[s][m]
  * is the Shapley-kernel weight (maskMatrix / kernelWeights of the reference run).  With
  * n_sets == 1 all rows share the set; otherwise row r uses set set_idx[r] (or r mod n_sets

@@ -755,6 +755,12 @@ def test_wide_background_limits(params, monkeypatch):
     phi, _, _ = _run(plan, X, FX, want_ey=False)
     np.testing.assert_allclose(phi.sum(1) + plan.expected_value, f(X), atol=1e-5)
     plan.close()
+    # several coalition sets have no other fast evaluator: such a plan is refused when it is created, not at the first call
+    Z2, kw2, _ = ks.sample_coalitions(30, 256, np.random.RandomState(82))
+    with pytest.raises(ValueError, match="shared memory"):
+        _plan(params, bg, [(Z, kw), (Z2, kw2)])
+    small = _plan(params, bg[:800], [(Z, kw), (Z2, kw2)])          # 800 rows is the documented limit of that format
+    small.close()
 
 
 @pytest.mark.parametrize("rows,nsamples", [(1, 100), (1, 128), (2, 129), (3, 2048)])
