@@ -77,6 +77,10 @@ struct fdb_ctx {
     fdb_pipe_slot slot[FDB_PIPE_SLOTS];
     void* h_stage = nullptr;               // pinned staging for small (serving) batches
     size_t h_stage_bytes = 0;
+    void* h_out[FDB_PIPE_SLOTS] = {};      // pinned landing buffers for phi chunks bound for PAGEABLE caller memory
+    size_t h_out_bytes = 0;                // size of each
+    void* h_in[FDB_PIPE_SLOTS] = {};       // pinned take-off buffers for row chunks coming from PAGEABLE caller memory
+    size_t h_in_bytes = 0;
 };
 
 // ---- kernel launchers (device pointers, no synchronisation) ---------------------------
