@@ -75,9 +75,12 @@ __global__ void __launch_bounds__(32) kshap_wls_prepare(const uint32_t* __restri
     // x_i x_j = zp_i zp_j with zp = z29 ? ~z : z (x_i = z_i - z_29 = z29 ? -zp_i : zp_i);  c2 = X'W z29 = -sum w zp z29
     double a[kNV];
     double c2;
-    fdb_kshap_weighted_gram_row<kNV>(
-        sb, sk, m_pad, lane, [](uint32_t b) { return ((b >> 29) & 1u) ? ~b : b; },
-        [](uint32_t b) { return ((b >> 29) & 1u) != 0u; }, a, c2);
+    __shared__ float s_tile[2 * 32 * 33];
+    auto word = [](uint32_t b) { return ((b >> 29) & 1u) ? ~b : b; };
+    auto flag = [](uint32_t b) { return ((b >> 29) & 1u) != 0u; };
+    // draw-count weights (sampled sets, shap's own sets) take the tensor-core Gram; anything else the exact generic path
+    if (!fdb_kshap_weighted_gram_row_mma<kNV>(sb, sk, m_pad, lane, word, flag, s_tile, a, c2))
+        fdb_kshap_weighted_gram_row<kNV>(sb, sk, m_pad, lane, word, flag, a, c2);
     c2out[(size_t)s * 32 + lane] = lane < kNV ? (float)(-c2) : 0.f;
     double inv[kNV];
 #pragma unroll

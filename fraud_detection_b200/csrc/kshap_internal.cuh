@@ -3,6 +3,8 @@
 
 #include <vector>
 
+#include <cuda_fp16.h>
+
 #include "fdb_internal.cuh"
 
 #define FDB_KSHAP_MAX_BG 1024          // background rows the tensor-core evaluator keeps resident in smem
@@ -153,6 +155,126 @@ __device__ __forceinline__ void fdb_kshap_weighted_gram_row(const uint32_t* __re
 #pragma unroll
     for (int j = 0; j < NF; ++j) a[j] += wd * (double)cnt[j];
     c += wd * (double)cflag;
+}
+#endif
+
+// The same Gram row for sets whose weights are DRAW COUNTS - every weight an integer multiple (<= 2048) of the smallest
+// one, except one class of equal weights among the first 64 coalitions (the enumerated block of a sampled set): what
+// the on-device sampler and shap's own sampler produce.  Then  G = w0 E + wmin R  with integer matrices
+// E = sum_{enumerated} v v',  R = sum_m count_m v_m v_m',  and both are small GEMMs  V' diag(count) V  that run on the
+// tensor cores (mma.sync m16n8k16, f16 operands holding 0 / 1 / count - exact - and fp32 accumulation of integers below
+// 2^24 - exact).  A thread builds its operand fragments straight from four coalition words per k-step: after one shift
+// the bits of its four feature rows sit in the four bytes of a word, a byte permute pairs them with the neighbouring
+// coalition, one multiply turns the pair into two halves.  ~4.4 instructions per coalition for the warp against ~14 for
+// the bit-sliced counting plus the predicated float64 path (which stays as the fallback for arbitrary weights: the
+// function returns false and leaves a / c untouched).  The flag column rides along as feature NF.
+// tile: 2 x 32 x 33 floats of shared memory owned by this warp.
+#ifdef __CUDACC__
+__device__ __forceinline__ void fdb_mma_m16n8k16(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                                 uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+template <int NF, typename WordFn, typename FlagFn>
+__device__ __forceinline__ bool fdb_kshap_weighted_gram_row_mma(const uint32_t* __restrict__ sb, const float* __restrict__ sk,
+                                                                int m_pad, int lane, WordFn word, FlagFn flag, float* tile,
+                                                                double (&a)[NF], double& c) {
+    static_assert(NF < 31, "the flag column needs a bit of its own");
+    const uint32_t full = 0xffffffffu;
+    float wmin = 3.0e38f;
+#pragma unroll 4
+    for (int m = lane; m < m_pad; m += 32) {
+        const float w = __ldg(sk + m);
+        if (w > 0.f) wmin = fminf(wmin, w);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) wmin = fminf(wmin, __shfl_xor_sync(full, wmin, o));
+    if (!(wmin < 3.0e38f)) return false;
+    const float w0 = __ldg(sk);
+    const bool has_enum = w0 > 0.f && w0 != wmin && m_pad >= 64;
+    const float inv_wmin = 1.0f / wmin;
+    const int g = lane >> 2, t = lane & 3;
+    float acc[2][4][4];
+    bool bad = false;
+    auto zero_acc = [&]() {
+#pragma unroll
+        for (int r = 0; r < 2; ++r)
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) acc[r][q][i] = 0.f;
+    };
+    // one k-step: 16 coalitions starting at m0; `enumerated` selects which weights count (see above)
+    auto kstep = [&](int m0, bool enumerated) {
+        const uint2 bab = __ldg(reinterpret_cast<const uint2*>(sb + m0 + 2 * t));
+        const uint2 bcd = __ldg(reinterpret_cast<const uint2*>(sb + m0 + 2 * t + 8));
+        const float2 wab = __ldg(reinterpret_cast<const float2*>(sk + m0 + 2 * t));
+        const float2 wcd = __ldg(reinterpret_cast<const float2*>(sk + m0 + 2 * t + 8));
+        const uint32_t bw[4] = {bab.x, bab.y, bcd.x, bcd.y};
+        const float ww[4] = {wab.x, wab.y, wcd.x, wcd.y};
+        uint32_t mb[4];
+        float cnt[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t v = (word(bw[i]) & ((1u << NF) - 1u)) | (flag(bw[i]) ? (1u << NF) : 0u);
+            mb[i] = (v >> g) & 0x01010101u;                  // features g, g + 8, g + 16, g + 24 in bytes 0..3
+            const bool in_enum = has_enum && m0 < 64 && ww[i] == w0;
+            if (enumerated) {
+                cnt[i] = in_enum ? 1.0f : 0.0f;
+            } else {
+                const float q = ww[i] * inv_wmin, rq = rintf(q);
+                if (!in_enum && (fabsf(q - rq) > 1e-3f * fmaxf(rq, 1.0f) || rq > 2048.f)) bad = true;
+                cnt[i] = in_enum ? 0.0f : rq;
+            }
+        }
+        const __half2 hab2 = __floats2half2_rn(cnt[0], cnt[1]), hcd2 = __floats2half2_rn(cnt[2], cnt[3]);
+        const uint32_t hab = *reinterpret_cast<const uint32_t*>(&hab2), hcd = *reinterpret_cast<const uint32_t*>(&hcd2);
+        uint32_t aab[4], acd[4], bab4[4], bcd4[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const uint32_t sel = (uint32_t)r | ((uint32_t)r << 4) | ((uint32_t)(4 + r) << 8) | ((uint32_t)(4 + r) << 12);
+            const uint32_t sab = __byte_perm(mb[0], mb[1], sel) & 0x00010001u;       // bit of coalition a | bit of coalition b << 16
+            const uint32_t scd = __byte_perm(mb[2], mb[3], sel) & 0x00010001u;
+            aab[r] = sab * 0x3C00u;                                                  // two halves, 0 or 1.0
+            acd[r] = scd * 0x3C00u;
+            bab4[r] = (sab * 0xFFFFu) & hab;                                         // two halves, 0 or count
+            bcd4[r] = (scd * 0xFFFFu) & hcd;
+        }
+#pragma unroll
+        for (int rt = 0; rt < 2; ++rt)
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                fdb_mma_m16n8k16(acc[rt][q], aab[2 * rt], aab[2 * rt + 1], acd[2 * rt], acd[2 * rt + 1], bab4[q], bcd4[q]);
+    };
+    // accumulators -> this warp's shared-memory tile (row = feature i, column = feature j)
+    auto dump = [&](float* tl) {
+#pragma unroll
+        for (int rt = 0; rt < 2; ++rt)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                tl[(16 * rt + g) * 33 + 8 * q + 2 * t] = acc[rt][q][0];
+                tl[(16 * rt + g) * 33 + 8 * q + 2 * t + 1] = acc[rt][q][1];
+                tl[(16 * rt + g + 8) * 33 + 8 * q + 2 * t] = acc[rt][q][2];
+                tl[(16 * rt + g + 8) * 33 + 8 * q + 2 * t + 1] = acc[rt][q][3];
+            }
+    };
+    zero_acc();
+    if (has_enum)
+        for (int m0 = 0; m0 < 64; m0 += 16) kstep(m0, true);
+    dump(tile);
+    zero_acc();
+#pragma unroll 2
+    for (int m0 = 0; m0 < m_pad; m0 += 16) kstep(m0, false);
+    dump(tile + 32 * 33);
+    __syncwarp();
+    if (__any_sync(full, bad)) return false;
+    const double dw0 = has_enum ? (double)w0 : 0.0, dwm = (double)wmin;
+#pragma unroll
+    for (int j = 0; j < NF; ++j) a[j] = dw0 * (double)tile[lane * 33 + j] + dwm * (double)tile[(32 + lane) * 33 + j];
+    c = dw0 * (double)tile[lane * 33 + NF] + dwm * (double)tile[(32 + lane) * 33 + NF];
+    return true;
 }
 #endif
 
