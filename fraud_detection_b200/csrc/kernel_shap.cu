@@ -616,10 +616,13 @@ extern "C" int fdb_kshap_explain_dev(fdb_kshap_plan* p, void* stream, int64_t n_
     {
         const int64_t b0 = n_rows < batch ? n_rows : batch;
         size_t gfl = 0;
-        if (fx) {
+        if (fx) {                                         // the last round may be shorter and need more records per row
             long long units; int grid, slots;
             fdb_kshap_fx_geometry(p, (int)b0, &units, &grid, &slots);
             gfl = (size_t)b0 * slots * 32;
+            const int64_t last = n_rows - ((n_rows - 1) / batch) * batch;
+            fdb_kshap_fx_geometry(p, (int)last, &units, &grid, &slots);
+            if ((size_t)last * slots * 32 > gfl) gfl = (size_t)last * slots * 32;
         }
         int rc = ensure_scratch(p, need_ey ? (size_t)b0 * p->m_pad : 0, gfl);
         if (rc != FDB_OK) return rc;

@@ -106,3 +106,36 @@ def test_config3_full_size_properties(params):
         got = phi[r].cpu().numpy().astype(np.float64)
         assert np.all(np.abs(got - ref) <= 1e-4 * np.abs(ref).max() + 1e-9), r
     plan.close()
+
+
+def test_factored_evaluator_over_several_rounds(params):
+    """More rows than one round of the factored evaluator takes (262,144): the rounds share the plan's scratch and the
+    |phi| summary accumulates over them.  Checked against the tensor-core evaluator (its own, shorter rounds), additivity
+    on every row, and two rows per round against the oracle."""
+    from fraud_detection_b200 import KernelShapPlan, sampler
+    n, nsamples, n_bg = 262_144 + 70_001, 256, 20
+    bg = scoring.transform(params, synth.rows(n_bg, seed=43))
+    X = scoring.transform(params, synth.rows(n, seed=7)).astype(np.float32)
+    bits, kw = sampler.sample_coalitions(30, nsamples, np.random.RandomState(5))
+    plan = KernelShapPlan(params.coef, params.intercept, bg, bits, kw)
+    x = torch.from_numpy(X).cuda()
+    sums = [torch.zeros(32, dtype=torch.float64, device="cuda") for _ in range(2)]
+    phi_fx = plan.explain_dev(x, evaluator=2, abs_sum=sums[0])
+    phi_tc = plan.explain_dev(x, evaluator=0, abs_sum=sums[1])
+    torch.cuda.synchronize()
+    f = lambda A: scoring.predict_proba(params, A)[:, 1]  # noqa: E731
+    fnull = float(f(bg).mean())
+    assert float((phi_fx - phi_tc).abs().max()) < 2e-5
+    fx = torch.sigmoid(x.double() @ torch.from_numpy(params.coef).cuda() + params.intercept)
+    assert float((phi_fx.double().sum(1) + fnull - fx).abs().max()) < 1e-5
+    a, b = sums[0].cpu().numpy(), sums[1].cpu().numpy()
+    assert a[30] == n and b[30] == n
+    np.testing.assert_allclose(a[:30], phi_fx.double().abs().sum(0).cpu().numpy(), rtol=1e-9)
+    np.testing.assert_allclose(a[:30], b[:30], rtol=1e-4)
+    Z = sampler.bits_to_masks(bits)
+    for r in (0, 131_071, 166_100, n - 1):
+        xr = X[r].astype(np.float64)
+        ref = ks.solve(Z, kw, ks.evaluate(f, xr, bg, Z), float(f(xr[None])[0]), fnull)
+        got = phi_fx[r].cpu().numpy()
+        assert np.all(np.abs(got - ref) <= 1e-4 * np.abs(ref).max() + 1e-8)
+    plan.close()
