@@ -31,26 +31,52 @@ _HOST_SCAN_ELEMS = 1 << 20
 
 
 def _feature_names_of(X):
+    """String column labels of a DataFrame as an object array, else None (sklearn ignores non-string labels:
+    api/app.py:184 passes ints).  ``inferred_type`` is cached by pandas and ``to_numpy`` avoids the 50 us that
+    ``list(columns)`` costs on an Arrow-backed string Index - this runs on every serving request."""
     cols = getattr(X, "columns", None)
     if cols is None:
         return None
-    names = list(cols)
-    if len(names) and all(isinstance(c, str) for c in names):
-        return np.asarray(names, dtype=object)
-    return None   # sklearn ignores non-string column labels (api/app.py:184 passes ints)
+    kind = getattr(cols, "inferred_type", None)
+    if kind is None:                                   # not a pandas Index: the generic route
+        names = list(cols)
+        if len(names) and all(isinstance(c, str) for c in names):
+            return np.asarray(names, dtype=object)
+        return None
+    if kind != "string" or len(cols) == 0:
+        return None
+    return cols.to_numpy(dtype=object)
+
+
+def _names_match_fast(X, est) -> bool:
+    """True when X carries exactly the fitted feature names (one C-level Index comparison, the serving hot path)."""
+    cols = getattr(X, "columns", None)
+    fitted = getattr(est, "feature_names_in_", None)
+    if cols is None or fitted is None or not hasattr(cols, "equals"):
+        return False
+    fi = getattr(est, "_fitted_index", None)
+    if fi is None:
+        import pandas as pd
+        fi = est._fitted_index = pd.Index(fitted)
+    return bool(cols.equals(fi))
 
 
 def _rows(X, est, *, allow_nan: bool = False):
     """sklearn-style validation -> C-contiguous float32/float64 (N, 30) host array."""
     name = type(est).sk_name
-    fitted = getattr(est, "feature_names_in_", None)
-    given = _feature_names_of(X)
-    if fitted is not None and given is None:
-        warnings.warn(f"X does not have valid feature names, but {name} was fitted with feature names", UserWarning)
-    elif fitted is None and given is not None:
-        warnings.warn(f"X has feature names, but {name} was fitted without feature names", UserWarning)
-    elif fitted is not None and given is not None and (len(fitted) != len(given) or np.any(fitted != given)):
-        raise ValueError("The feature names should match those that were passed during fit.")
+    if not _names_match_fast(X, est):
+        fitted = getattr(est, "feature_names_in_", None)
+        cols = getattr(X, "columns", None)
+        if fitted is None and getattr(cols, "inferred_type", None) is not None:
+            given = True if (cols.inferred_type == "string" and len(cols)) else None      # only "has names?" matters here
+        else:
+            given = _feature_names_of(X)
+        if fitted is not None and given is None:
+            warnings.warn(f"X does not have valid feature names, but {name} was fitted with feature names", UserWarning)
+        elif fitted is None and given is not None:
+            warnings.warn(f"X has feature names, but {name} was fitted without feature names", UserWarning)
+        elif fitted is not None and given is not None and (len(fitted) != len(given) or np.any(fitted != given)):
+            raise ValueError("The feature names should match those that were passed during fit.")
     if hasattr(X, "to_numpy"):
         X = X.to_numpy()
     A = np.asarray(X)
