@@ -179,8 +179,18 @@ __device__ __forceinline__ void sigmoid_and_complement_sums16(const uint32_t (&r
 }
 
 // smem carve-up (dynamic): [B image][A stages x pipes][Bq stages x pipes][barriers]
+// FDB_K2_MAXREG: cap on registers per thread.  At 64 the CTA leaves a quarter of the register file (and 130 KB of shared
+// memory) free, so the coalition sampler of the NEXT batch (other stream, 51 registers, 16 KB per set) can run beside it.
+#ifndef FDB_K2_MAXREG
+#define FDB_K2_MAXREG 0
+#endif
+#if FDB_K2_MAXREG > 0
+#define FDB_K2_REGCAP __maxnreg__(FDB_K2_MAXREG)
+#else
+#define FDB_K2_REGCAP __launch_bounds__(kThreadsTc, 1)
+#endif
 template <bool FROM_BITS, bool WIDE>
-__global__ void __launch_bounds__(kThreadsTc, 1) kshap_eval_tc_kernel(const TcParams p) {
+__global__ void FDB_K2_REGCAP kshap_eval_tc_kernel(const TcParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     const uint32_t b_bytes = (uint32_t)p.nsplit * p.nb_pad * 64;
     unsigned char* sB = smem;
