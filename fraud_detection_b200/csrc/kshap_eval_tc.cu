@@ -37,13 +37,20 @@
 
 namespace {
 
-constexpr int kPipes = 4;
+#ifndef FDB_K2_PIPES
+#define FDB_K2_PIPES 4
+#endif
+#ifndef FDB_K2_BUF_COLS
+#define FDB_K2_BUF_COLS 64
+#endif
+constexpr int kPipes = FDB_K2_PIPES;
 constexpr int kThreadsTc = (2 * kPipes + 4 * kPipes) * 32;   // 768
 constexpr int kATileBytes = 128 * 32 * 2;     // 8192
 constexpr int kBqBytes = 3 * 512;             // 3 splits x (4 k-chunks x 8 identical rows x 16 B)
 constexpr int kAStages = 2;
-constexpr int kPipeCols = 128;                // TMEM columns per pipeline ...
-constexpr int kBufCols = 64;                  // ... used as two accumulator buffers: the MMA of background chunk c + 1 runs while chunk c is read
+constexpr int kBufCols = FDB_K2_BUF_COLS;     // TMEM columns of one accumulator buffer (a background chunk)
+constexpr int kPipeCols = 2 * kBufCols;       // per pipeline: two buffers, the MMA of background chunk c + 1 runs while chunk c is read
+static_assert(kPipes * kPipeCols <= 512 && kBufCols % 16 == 0, "TMEM holds 512 columns");
 constexpr uint32_t kLbo = 128;                // K-direction core-matrix stride (bytes)
 constexpr uint32_t kSbo = 512;                // 8-row-group stride (bytes)
 
