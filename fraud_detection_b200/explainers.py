@@ -412,6 +412,7 @@ class B200KernelExplainer:
             ev1 = self.expected_value
             self.expected_value = np.array([-ev1 if link == "logit" else 1.0 - ev1, ev1])
         self._shared_cache: dict = {}
+        self._shared_plans: dict = {}
         self._device_plans: dict = {}
         self._device_calls = 0
 
@@ -514,6 +515,20 @@ class B200KernelExplainer:
             sets = [shared_set(N_FEATURES)]
         else:
             sets = [host_sets[int(r)] for r in rows]
+        if masks is None and mask_mode == "shared":
+            # the shared set is cached per (nsamples, random source): keep its plan too, so that repeated calls (a served
+            # explainer) pay neither the upload nor the factored evaluator's set-up again
+            key = ("shared", nsamples, id(random))
+            plan = self._shared_plans.get(key)
+            if plan is None:
+                for old in self._shared_plans.values():
+                    old.close()
+                self._shared_plans.clear()
+                bits, kw = self._pad_sets(sets)
+                plan = self._shared_plans[key] = KernelShapPlan(self.coef, self.intercept, self.data, bits, kw, self.link, self.device)
+            plan.set_num_features(num_features)
+            out[rows] = plan.explain_host(Xr, None, evaluator)
+            return out[0] if single else out
         bits, kw = self._pad_sets(sets)
         plan = KernelShapPlan(self.coef, self.intercept, self.data, bits, kw, self.link, self.device)
         try:

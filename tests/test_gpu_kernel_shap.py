@@ -262,8 +262,16 @@ def test_explainer_class_matches_oracle_with_same_seed(params):
     one = expl.shap_values(X[0], nsamples=2048, random=np.random.RandomState(7), l1_reg=False)
     assert one.shape == (30,)
     np.testing.assert_allclose(one, phi[0], atol=1e-6)      # one set -> factored evaluator, five sets -> general one
-    shared = expl.shap_values(X, nsamples=2048, mask_mode="shared", random=np.random.RandomState(8), l1_reg=False)
+    rs8 = np.random.RandomState(8)
+    shared = expl.shap_values(X, nsamples=2048, mask_mode="shared", random=rs8, l1_reg=False)
     np.testing.assert_allclose(shared.sum(1) + expl.expected_value, f(X), atol=1e-5)
+    # the shared set and its plan are kept: the same call again reuses both and returns the same attributions,
+    # with or without feature selection in between
+    plan_before = next(iter(expl._shared_plans.values()))
+    expl.shap_values(X[:2], nsamples=2048, mask_mode="shared", random=rs8, l1_reg="num_features(5)")
+    again = expl.shap_values(X, nsamples=2048, mask_mode="shared", random=rs8, l1_reg=False)
+    assert next(iter(expl._shared_plans.values())) is plan_before and len(expl._shared_plans) == 1
+    np.testing.assert_array_equal(again, shared)
     with pytest.raises(NotImplementedError):
         expl.shap_values(X, l1_reg="aic")
 

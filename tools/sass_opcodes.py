@@ -13,7 +13,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 lib = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "fraud_detection_b200", "libfdb200.so")
-OPS = ["UTCHMMA", "UTCQMMA", "LDTM", "STTM", "UBLKCP", "UTMALDG", "UTCBAR", "SYNCS", "MUFU.EX2", "MUFU.RCP", "MUFU.LG2",
+OPS = ["UTCHMMA", "UTCQMMA", "HMMA", "LDTM", "STTM", "UBLKCP", "UTMALDG", "UTCBAR", "SYNCS", "MUFU.EX2", "MUFU.RCP", "MUFU.LG2",
        "FFMA", "FFMA2", "FMUL", "FADD", "DFMA", "LDS", "STS", "LDG", "STG", "LDL", "STL", "SHFL", "REDUX", "ATOM", "RED"]
 sass = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True, check=True).stdout
 counts, order, cur = {}, [], None
