@@ -626,6 +626,7 @@ def bench_kernel_shap(args, torch, dist, device, rank, world, model, scaler, pro
                      "peak_nominal": 128.0 * sms * nominal_hz / 3.5 / 1e12,
                      "inner_loop_alone": probes["k2f_quad_lds_sigmoids_per_s"] / 1e12,
                      "frac_of_inner_loop_alone": k2f_rate / probes["k2f_quad_lds_sigmoids_per_s"],
+                     "inner_loop_alone_16_warps": probes["k2f_quad_16warps_sigmoids_per_s"] / 1e12,
                      "config4_achieved": None if sig4_rate is None else sig4_rate / 1e12,
                      "config4_frac": None if sig4_rate is None else sig4_rate / (issue_meas / 3.5)},
     }

@@ -118,9 +118,9 @@ def probe_pipes(device: int | None = None) -> dict:
     """Measured instruction-pipe rates of the device (fdb_probe_pipes): the Kernel SHAP roofline denominators."""
     out = (C.c_double * 8)()
     check(lib.fdb_probe_pipes(get_ctx(device), out))
-    keys = ("ex2_per_s", "rcp_per_s", "ffma_per_s", "k2f_quad_regs_sigmoids_per_s", "k2f_quad_lds_sigmoids_per_s",
-            "sm_clock_hz", "sm_count")
-    return dict(zip(keys, list(out)[:7]))
+    v = list(out)
+    return {"ex2_per_s": v[0], "rcp_per_s": v[1], "ffma_per_s": v[2], "k2f_quad_16warps_sigmoids_per_s": v[3],
+            "k2f_quad_lds_sigmoids_per_s": v[4], "sm_count": v[6]}
 
 
 # ------------------------------------------------------------------ small helpers

@@ -5,9 +5,10 @@
 //   [0] ex2.approx.ftz.f32 results per second            (MUFU.EX2, the SFU line of the north star)
 //   [1] rcp.approx.ftz.f32 results per second            (MUFU.RCP)
 //   [2] independent FFMA results per second              (FP32 FMA pipe = warp-instruction issue rate x 32)
-//   [3] sigmoids per second of K2f's clamp-free quad loop with its operands in registers (no shared-memory reads)
-//   [4] the same loop reading E as broadcast LDS.128 from shared memory, 64 resident warps per SM
-//   [5] SM clock in Hz seen by the probe (clock64 ticks / elapsed time of probe [2])
+//   [3] sigmoids per second of K2f's clamp-free quad loop (E read as broadcast LDS.128) at 16 resident warps per SM -
+//       the occupancy the evaluator's 16 compute warps give it
+//   [4] the same loop at 64 resident warps per SM
+//   [5] 0 (reserved)
 // Every probe keeps 8 independent dependency chains per thread and 64 warps per SM, so the pipes, not latencies, set
 // the rate.  No counterpart in the reference; a measurement aid only.
 
@@ -136,19 +137,14 @@ extern "C" int fdb_probe_pipes(fdb_ctx* ctx, double* out8) {
         bool ok = true;
         ok = ok && timed([&] { probe_ex2<<<grid, kProbeThreads>>>(sink, it_mufu); }, (double)kChains * it_mufu, &out8[0]);
         ok = ok && timed([&] { probe_rcp<<<grid, kProbeThreads>>>(sink, it_mufu); }, (double)kChains * it_mufu, &out8[1]);
-        double fma_rate = 0.0;
-        float ms_fma = 0.f;
+        ok = ok && timed([&] { probe_ffma<<<grid, kProbeThreads>>>(sink, it_fma, 0.999f, 0.001f, clocks); }, (double)kChains * it_fma, &out8[2]);
+        out8[5] = 0.0;
         {
-            // one more timed launch of the FFMA probe whose clock64 span gives the SM clock under load
-            ok = ok && timed([&] { probe_ffma<<<grid, kProbeThreads>>>(sink, it_fma, 0.999f, 0.001f, clocks); }, (double)kChains * it_fma, &fma_rate);
-            out8[2] = fma_rate;
-            long long ticks = 0;
-            if (ok && cudaMemcpy(&ticks, clocks, sizeof(ticks), cudaMemcpyDeviceToHost) != cudaSuccess) ok = false;
-            // the timed span of one CTA's loop: FFMA rate per SM per clock = threads_per_sm * chains * iters / ticks
-            ms_fma = (float)(threads * kChains * it_fma / fma_rate * 1e3);
-            out8[5] = ticks > 0 ? (double)ticks / (ms_fma * 1e-3) : 0.0;
+            // the quad loop at the evaluator's own occupancy: one CTA of 512 threads per SM
+            double r16 = 0.0;
+            ok = ok && timed([&] { probe_quad<true><<<ctx->sm_count, 512>>>(sink, it_quad); }, 32.0 * it_quad, &r16);
+            out8[3] = r16 * (512.0 * ctx->sm_count) / threads;          // `timed` multiplies by the full-grid thread count
         }
-        ok = ok && timed([&] { probe_quad<false><<<grid, kProbeThreads>>>(sink, it_quad); }, 32.0 * it_quad, &out8[3]);
         ok = ok && timed([&] { probe_quad<true><<<grid, kProbeThreads>>>(sink, it_quad); }, 32.0 * it_quad, &out8[4]);
         out8[6] = (double)ctx->sm_count;
         out8[7] = 0.0;

@@ -201,9 +201,9 @@ int fdb_linear_pass_noalloc(void* stream, int dtype, int64_t n_rows, const void*
  * measured with small saturating kernels at the clock the device runs them at.  They are
  * the denominators of the Kernel SHAP rooflines in bench.py (MEASURED_PEAKS.json has no
  * SFU / FP32-issue figure).  out8: [0] ex2.approx results/s, [1] rcp.approx results/s,
- * [2] independent FFMA results/s, [3] sigmoids/s of K2f's clamp-free quad loop on
- * registers, [4] the same loop with its broadcast LDS.128 reads, [5] SM clock (Hz) during
- * the FFMA probe, [6] SM count, [7] 0.  Synchronous; allocates 256 bytes while it runs.
+ * [2] independent FFMA results/s, [3] sigmoids/s of K2f's clamp-free quad loop (broadcast
+ * LDS.128 reads included) at 16 resident warps per SM, [4] the same at 64 warps per SM,
+ * [5] 0, [6] SM count, [7] 0.  Synchronous; allocates 256 bytes while it runs.
  * ------------------------------------------------------------------------------- */
 int fdb_probe_pipes(fdb_ctx* ctx, double* out8);
 

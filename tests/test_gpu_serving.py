@@ -104,3 +104,17 @@ def test_paired_predict_calls_share_one_pass(params):
         np.testing.assert_allclose(model.predict_proba(Xs2), model_sk.predict_proba(Xs2), atol=1e-12)
         X32 = Xs.astype(np.float32)                   # same values, other dtype -> its own pass and dtype rules
         np.testing.assert_allclose(model.predict_proba(X32), model_sk.predict_proba(X32), atol=1e-5)
+
+
+def test_pipe_probes_report_plausible_rates():
+    """fdb_probe_pipes (the measured denominators of the Kernel SHAP rooflines): on a B200 the SFU does 16 results per
+    clock per SM, the FP32 pipe 128, and K2f's quad loop cannot beat the issue bound of 3.5 slots per sigmoid."""
+    from fraud_detection_b200 import _lib
+    p = _lib.probe_pipes(0)
+    sms = p["sm_count"]
+    assert sms >= 100
+    per_clk = lambda rate, ghz: rate / (sms * ghz * 1e9)  # noqa: E731
+    assert 10.0 < per_clk(p["ex2_per_s"], 1.965) < 17.0 and 10.0 < per_clk(p["rcp_per_s"], 1.965) < 17.0
+    assert 90.0 < per_clk(p["ffma_per_s"], 1.965) < 130.0
+    bound = p["ffma_per_s"] / 3.5
+    assert 0.3 * bound < p["k2f_quad_16warps_sigmoids_per_s"] <= p["k2f_quad_lds_sigmoids_per_s"] * 1.05 < 1.1 * bound
