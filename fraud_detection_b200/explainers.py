@@ -341,6 +341,9 @@ class KernelShapStream:
         k = self._i & 1
         plan, st = self.plans[k], self.streams[k]
         st.wait_stream(torch.cuda.current_stream(self.device))      # x was produced on the caller's stream
+        x.record_stream(st)                                          # ... and must outlive the work queued on this one
+        if phi is not None:
+            phi.record_stream(st)
         with torch.cuda.stream(st):
             if not self._fresh[k]:
                 plan.resample(self._seed, stream=int(st.cuda_stream))
