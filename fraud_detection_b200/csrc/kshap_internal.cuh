@@ -206,14 +206,9 @@ __device__ __forceinline__ bool fdb_kshap_weighted_gram_row_mma(const uint32_t* 
 #pragma unroll
                 for (int i = 0; i < 4; ++i) acc[r][q][i] = 0.f;
     };
-    // one k-step: 16 coalitions starting at m0; `enumerated` selects which weights count (see above)
-    auto kstep = [&](int m0, bool enumerated) {
-        const uint2 bab = __ldg(reinterpret_cast<const uint2*>(sb + m0 + 2 * t));
-        const uint2 bcd = __ldg(reinterpret_cast<const uint2*>(sb + m0 + 2 * t + 8));
-        const float2 wab = __ldg(reinterpret_cast<const float2*>(sk + m0 + 2 * t));
-        const float2 wcd = __ldg(reinterpret_cast<const float2*>(sk + m0 + 2 * t + 8));
-        const uint32_t bw[4] = {bab.x, bab.y, bcd.x, bcd.y};
-        const float ww[4] = {wab.x, wab.y, wcd.x, wcd.y};
+    // one k-step: 16 coalitions (this thread's four: words bw, weights ww) starting at m0; `enumerated` selects which
+    // weights count (see above)
+    auto kstep = [&](int m0, bool enumerated, const uint32_t (&bw)[4], const float (&ww)[4]) {
         uint32_t mb[4];
         float cnt[4];
 #pragma unroll
@@ -248,6 +243,14 @@ __device__ __forceinline__ bool fdb_kshap_weighted_gram_row_mma(const uint32_t* 
             for (int q = 0; q < 4; ++q)
                 fdb_mma_m16n8k16(acc[rt][q], aab[2 * rt], aab[2 * rt + 1], acd[2 * rt], acd[2 * rt + 1], bab4[q], bcd4[q]);
     };
+    auto load4 = [&](int m0, uint32_t (&bw)[4], float (&ww)[4]) {
+        const uint2 bab = __ldg(reinterpret_cast<const uint2*>(sb + m0 + 2 * t));
+        const uint2 bcd = __ldg(reinterpret_cast<const uint2*>(sb + m0 + 2 * t + 8));
+        const float2 wab = __ldg(reinterpret_cast<const float2*>(sk + m0 + 2 * t));
+        const float2 wcd = __ldg(reinterpret_cast<const float2*>(sk + m0 + 2 * t + 8));
+        bw[0] = bab.x; bw[1] = bab.y; bw[2] = bcd.x; bw[3] = bcd.y;
+        ww[0] = wab.x; ww[1] = wab.y; ww[2] = wcd.x; ww[3] = wcd.y;
+    };
     // accumulators -> this warp's shared-memory tile (row = feature i, column = feature j)
     auto dump = [&](float* tl) {
 #pragma unroll
@@ -262,11 +265,24 @@ __device__ __forceinline__ bool fdb_kshap_weighted_gram_row_mma(const uint32_t* 
     };
     zero_acc();
     if (has_enum)
-        for (int m0 = 0; m0 < 64; m0 += 16) kstep(m0, true);
+        for (int m0 = 0; m0 < 64; m0 += 16) {
+            uint32_t bw[4];
+            float ww[4];
+            load4(m0, bw, ww);
+            kstep(m0, true, bw, ww);
+        }
     dump(tile);
     zero_acc();
-#pragma unroll 2
-    for (int m0 = 0; m0 < m_pad; m0 += 16) kstep(m0, false);
+    // 64 coalitions per trip (m_pad is a multiple of 128): the loads of four k-steps are issued together, ahead of the
+    // fragment arithmetic, so a warp keeps 16 loads in flight instead of stalling on four per k-step
+    for (int m1 = 0; m1 < m_pad; m1 += 64) {
+        uint32_t bw[4][4];
+        float ww[4][4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) load4(m1 + 16 * q, bw[q], ww[q]);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) kstep(m1 + 16 * q, false, bw[q], ww[q]);
+    }
     dump(tile + 32 * 33);
     __syncwarp();
     if (__any_sync(full, bad)) return false;
