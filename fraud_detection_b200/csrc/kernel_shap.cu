@@ -278,6 +278,7 @@ void free_plan(fdb_kshap_plan* p) {
     cudaFree(p->d_bits); cudaFree(p->d_kw); cudaFree(p->d_P); cudaFree(p->d_wq); cudaFree(p->d_bimg); cudaFree(p->d_aimg);
     cudaFree(p->d_ainv); cudaFree(p->d_c2); cudaFree(p->d_status); cudaFree(p->d_ey);
     cudaFree(p->d_abs); cudaFree(p->d_E); cudaFree(p->d_eoff); cudaFree(p->d_fxtile); cudaFree(p->d_gpart); cudaFree(p->d_gz); cudaFree(p->d_bv); cudaFree(p->d_s0);
+    fdb_kshap_free_lasso(p);
     cudaFree(p->d_partials); cudaFree(p->d_ticket); cudaFree(p->d_bad);
     fdb_kshap_sampler_free(p);
     for (int i = 0; i < 2; ++i) {
@@ -307,7 +308,11 @@ void fdb_kshap_split(double v, int fmt, int n, uint16_t* out) {
 static int refresh_set_products_async(fdb_kshap_plan* p, cudaStream_t st) {
     kshap_wls_prepare<<<p->n_sets, 32, 0, st>>>(p->d_bits, p->d_kw, p->m_pad, p->d_ainv, p->d_c2, p->d_status, p->varying, p->d_bad);
     FDB_CUDA(cudaGetLastError());
-    if (p->d_gz) return fdb_kshap_refresh_lars(p, st);
+    if (p->d_gz) {
+        int rc = fdb_kshap_refresh_lars(p, st);
+        if (rc != FDB_OK) return rc;
+        return fdb_kshap_refresh_lasso(p, st);
+    }
     return FDB_OK;
 }
 
@@ -338,6 +343,12 @@ static int refresh_set_products(fdb_kshap_plan* p) {
         p->d_gz = nullptr; p->d_bv = nullptr; p->d_s0 = nullptr;
         int rc = fdb_kshap_prepare_lars(p);
         if (rc != FDB_OK) return rc;
+        if (p->d_lg) {
+            const int scale = p->lasso_scaled;
+            fdb_kshap_free_lasso(p);
+            rc = fdb_kshap_prepare_lasso(p, scale);
+            if (rc != FDB_OK) return rc;
+        }
     }
     return FDB_OK;
 }
@@ -564,6 +575,28 @@ extern "C" int fdb_kshap_plan_set_num_features(fdb_kshap_plan* p, int k) {
         if (rc != FDB_OK) return rc;
     }
     p->num_features = k;
+    p->l1_mode = k > 0 ? FDB_KSHAP_L1_NUM_FEATURES : FDB_KSHAP_L1_NONE;
+    return FDB_OK;
+}
+
+extern "C" int fdb_kshap_plan_set_l1(fdb_kshap_plan* p, int mode, double param) {
+    FDB_REQUIRE(p != nullptr, FDB_ERR_ARG, "plan is NULL");
+    FDB_REQUIRE(mode >= FDB_KSHAP_L1_NONE && mode <= FDB_KSHAP_L1_ALPHA, FDB_ERR_ARG, "unknown l1 mode %d", mode);
+    if (mode == FDB_KSHAP_L1_NONE) return fdb_kshap_plan_set_num_features(p, 0);
+    if (mode == FDB_KSHAP_L1_NUM_FEATURES) {
+        FDB_REQUIRE(param >= 1.0 && param <= 16.0 && param == (double)(int)param, FDB_ERR_ARG,
+                    "num_features(k) needs an integer 1 <= k <= 16, got %g", param);
+        return fdb_kshap_plan_set_num_features(p, (int)param);
+    }
+    if (mode == FDB_KSHAP_L1_ALPHA)
+        FDB_REQUIRE(param > 0.0 && param < 1e300, FDB_ERR_ARG, "the Lasso penalty must be a positive finite number, got %g", param);
+    DeviceGuard guard(p->ctx->device);
+    FDB_REQUIRE(guard.ok, FDB_ERR_CUDA, "cannot select device %d", p->ctx->device);
+    int rc = fdb_kshap_prepare_lasso(p, mode == FDB_KSHAP_L1_ALPHA ? 0 : 1);
+    if (rc != FDB_OK) return rc;
+    p->num_features = 0;
+    p->l1_mode = mode;
+    p->l1_alpha = mode == FDB_KSHAP_L1_ALPHA ? param : 0.0;
     return FDB_OK;
 }
 
@@ -605,7 +638,7 @@ extern "C" int fdb_kshap_explain_dev(fdb_kshap_plan* p, void* stream, int64_t n_
     FDB_REQUIRE(cur == p->ctx->device, FDB_ERR_STATE, "the plan lives on device %d but the current device is %d", p->ctx->device, cur);
     fdb_ctx* ctx = p->ctx;
     const bool fx = evaluator == FDB_KSHAP_EVAL_FACTORED;
-    const bool need_ey = !fx || ey_out != nullptr || p->num_features > 0;
+    const bool need_ey = !fx || ey_out != nullptr || p->l1_mode != FDB_KSHAP_L1_NONE;
     // rows per evaluate -> solve round: bounded by the ey scratch when expectations go through HBM; the factored path
     // leaves only 256 B per row behind, so it takes large rounds (every CTA gets an equal share of the units)
     int64_t batch = need_ey ? FDB_KSHAP_BATCH_ROWS : FDB_KSHAP_FX_BATCH_ROWS;
@@ -650,8 +683,13 @@ extern "C" int fdb_kshap_explain_dev(fdb_kshap_plan* p, void* stream, int64_t n_
                                                                                  p->link);
             FDB_CUDA(cudaGetLastError());
         }
-        if (p->num_features > 0) {
+        if (p->l1_mode == FDB_KSHAP_L1_NUM_FEATURES) {
             int rc = fdb_kshap_launch_lars_solve(p, st, xb, r0, nb, sb, phi + r0 * FDB_F, abs_sum, r0 > 0 ? 1 : 0, n_rows);
+            if (rc != FDB_OK) return rc;
+            continue;
+        }
+        if (p->l1_mode != FDB_KSHAP_L1_NONE) {
+            int rc = fdb_kshap_launch_lasso_solve(p, st, xb, r0, nb, sb, phi + r0 * FDB_F, abs_sum, r0 > 0 ? 1 : 0, n_rows);
             if (rc != FDB_OK) return rc;
             continue;
         }

@@ -50,6 +50,12 @@ struct fdb_kshap_plan {
     std::vector<double> bg_host;       // background rows (host copy, for rebuilding set-dependent operands)
     bool sampled = false;              // sets were drawn on the device and may be redrawn (fdb_kshap_plan_resample)
     int num_features = 0;              // 0 = plain WLS over all features; k = LARS selection of k features first
+    int l1_mode = 0;                   // FDB_KSHAP_L1_*: which feature selection runs before the WLS
+    double l1_alpha = 0.0;             // FDB_KSHAP_L1_ALPHA: the Lasso penalty
+    double* d_lg = nullptr;            // [S][30][32] centred (scaled) Gram of the augmented system (kshap_lasso.cu)
+    double* d_lginv = nullptr;         // [S][30][32] its inverse
+    double* d_lvec = nullptr;          // [S][96] column sums, 1 / sd, Q, n
+    int lasso_scaled = -1;             // which variant d_lg holds: 1 unit-variance columns (criteria), 0 centred only (alpha)
     uint32_t varying = 0x3FFFFFFFu;    // features that differ from the background for the rows of this plan (bit 29 always set)
     float* d_gpart = nullptr;          // [gpart_rows][slots][32] X'W y records written by K2f, folded by K3 (grown on demand)
     size_t ey_cap = 0, gpart_cap = 0;  // floats the two scratch buffers hold
@@ -297,6 +303,12 @@ __device__ __forceinline__ bool fdb_kshap_weighted_gram_row_mma(const uint32_t* 
 // l1_reg = "num_features(k)": LARS selection + reduced WLS (kshap_lars.cu)
 int fdb_kshap_prepare_lars(fdb_kshap_plan* p);
 int fdb_kshap_refresh_lars(fdb_kshap_plan* p, cudaStream_t st);
+// l1_reg = "aic" | "bic" | alpha: LARS-lasso path / coordinate descent selection + reduced WLS (kshap_lasso.cu)
+int fdb_kshap_prepare_lasso(fdb_kshap_plan* p, int scale);
+int fdb_kshap_refresh_lasso(fdb_kshap_plan* p, cudaStream_t st);
+void fdb_kshap_free_lasso(fdb_kshap_plan* p);
+int fdb_kshap_launch_lasso_solve(fdb_kshap_plan* p, cudaStream_t st, const float* x, int64_t row_offset, int n_rows,
+                                 const int32_t* set_idx, float* phi, double* abs_sum, int accumulate, int64_t total_rows);
 int fdb_kshap_launch_lars_solve(fdb_kshap_plan* p, cudaStream_t st, const float* x, int64_t row_offset, int n_rows,
                                 const int32_t* set_idx, float* phi, double* abs_sum, int accumulate, int64_t total_rows);
 

@@ -1,0 +1,591 @@
+// Kernel SHAP solve with shap's adaptive feature selection:  l1_reg = "aic" | "bic" | "auto" | <alpha>.
+//
+// Reference (oracle/kernel_shap.py::solve, restating shap/explainers/_kernel.py::solve [recalled]):
+//   X_aug = sqrt(w_aug) * [Z; Z - 1],  y_aug = sqrt(w_aug) * [e; e - d],  w_aug = [kw (M - s); kw s]      (2 n_masks rows)
+//   "aic" / "bic":  sel = nonzero(make_pipeline(StandardScaler(with_mean=False), LassoLarsIC(criterion)).fit(X_aug, y_aug).coef_)
+//   alpha        :  sel = nonzero(Lasso(alpha).fit(X_aug, y_aug).coef_)
+//   "auto"       :  "aic" when nsamples / (2^M - 2) < 0.2, no selection otherwise (decided by the caller)
+//   then the additivity-constrained WLS over `sel` only, every other feature gets phi = 0.
+// sklearn's part (1.7.2 pinned by the reference, 1.9.0 in this image; sklearn/linear_model/_least_angle.py):
+//   LassoLarsIC.fit centres X and y, walks lars_path(method="lasso") to alpha = 0, and keeps the path point that minimises
+//   n log(2 pi s2) + RSS / s2 + factor * df   (factor 2 | log n,  df = #|coef| > eps,  s2 = RSS_ols / (n - M - 1));
+//   Lasso.fit centres X and y and runs cyclic coordinate descent on (1 / 2n) |y - Xw|^2 + alpha |w|_1 to a duality gap.
+//
+// The kernel never forms the 2 n_masks x M matrix.  Per coalition set (kshap_lasso_prepare, on top of the Z'WZ products of
+// kshap_lars.cu): column sums and variances of X_aug, the centred (and for the criteria unit-variance) Gram
+//   G_ij = (A_ij - n mu_i mu_j) / (sd_i sd_j),   A = X_aug'X_aug = M Gz_ij - B_i - B_j + S0,   mu_j = (R_j - Q) / n,
+//   R_j = sum_m (sqrt(kw (M - s)) + sqrt(kw s)) z_mj,   Q = sum_m sqrt(kw s),   sd_j^2 = A_jj / n - mu_j^2
+// and its inverse.  Per explained row ONE pass over the coalition expectations gives T_j = sum kw z_mj e_m,
+// E2 = sum kw e^2 and P1 = sum (sqrt(kw (M - s)) + sqrt(kw s)) e, from which
+//   X'y_j = (M T_j - d B_j - sum T + d S0 - (R_j - Q) (P1 - d Q) / n) / sd_j,   y'y = M E2 - 2 d sum T + d^2 S0 - (P1 - d Q)^2 / n.
+// The LARS-lasso walk (adds, sign-change drops with a refactorisation of the active block, RSS and support recorded at
+// every path point), the criterion, the coordinate descent and the reduced WLS all run in float64, one warp per row,
+// lane j = feature j (tests/lasso_gram_model.py is the same algorithm in numpy, checked against sklearn on the CPU).
+
+#include <float.h>
+#include <math.h>
+
+#include "kshap_internal.cuh"
+
+namespace {
+
+constexpr int kMaxPath = 96;          // path points kept per row (sklearn: max_iter = 500; 30 features need ~31 + drops)
+constexpr int kVecStride = 96;        // per set: [0..31] column sums c_j, [32..63] 1 / sd_j, [64] Q, [65] n
+
+__device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+__device__ __forceinline__ double shfl_xor_d(double v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
+__device__ __forceinline__ double warp_min(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmin(v, shfl_xor_d(v, o));
+    return v;
+}
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, shfl_xor_d(v, o));
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += shfl_xor_d(v, o);
+    return v;
+}
+__device__ __forceinline__ double min_pos(double v) { return v > 0.0 ? v : DBL_MAX; }
+
+// lanes own coalitions and hold 32 per-feature partial sums each; afterwards lane j holds the total of feature j in v[0]
+__device__ __forceinline__ void transpose_reduce(double (&v)[32], int lane) {
+#pragma unroll
+    for (int half = 16; half >= 1; half >>= 1) {
+        const bool up = (lane & half) != 0;
+#pragma unroll
+        for (int i = 0; i < half; ++i) {
+            const double send = up ? v[i] : v[i + half];
+            const double keep = up ? v[i + half] : v[i];
+            v[i] = keep + shfl_xor_d(send, half);
+        }
+    }
+}
+
+struct LassoScratch {
+    double L[FDB_F][FDB_F + 1];       // Cholesky factor of the active Gram block; afterwards the reduced WLS system [A | rhs]
+    double ls[FDB_F];                 // equiangular direction, by active position; afterwards the WLS solution
+    double sgn[FDB_F];
+    int act[FDB_F];
+    double rss[kMaxPath + 1];
+    uint32_t nz[kMaxPath + 1];
+};
+
+// Per coalition set: centred (scale != 0: unit-variance) Gram of the augmented matrix, its inverse, column sums, 1 / sd.
+__global__ void __launch_bounds__(32) kshap_lasso_prepare(const uint32_t* __restrict__ bits, const float* __restrict__ kw,
+                                                          int m_pad, const double* __restrict__ gz, const double* __restrict__ bv,
+                                                          const double* __restrict__ s0, double* __restrict__ lg,
+                                                          double* __restrict__ lginv, double* __restrict__ lvec,
+                                                          uint32_t varying, int scale) {
+    const int s = blockIdx.x, lane = threadIdx.x;
+    const uint32_t* sb = bits + (size_t)s * m_pad;
+    const float* sk = kw + (size_t)s * m_pad;
+    const double Mf = (double)__popc(varying);
+    const bool is_var = (varying >> lane) & 1u;
+    double g[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) g[j] = 0.0;
+    double qacc = 0.0, cnt = 0.0;
+    for (int m = lane; m < m_pad; m += 32) {
+        const double w = (double)sk[m];
+        if (!(w > 0.0)) continue;
+        const uint32_t b = sb[m] & varying;
+        const double sc = (double)__popc(b);
+        const double q = sqrt(w * sc);
+        const double r = sqrt(w * (Mf - sc)) + q;
+        qacc += q;
+        cnt += 1.0;
+#pragma unroll
+        for (int j = 0; j < FDB_F; ++j) g[j] += ((b >> j) & 1u) ? r : 0.0;
+    }
+    transpose_reduce(g, lane);
+    const double Q = warp_sum(qacc);
+    const double n = 2.0 * warp_sum(cnt);
+    const double* G0 = gz + (size_t)s * FDB_F * 32;
+    const double Bj = bv[(size_t)s * 32 + lane];
+    const double S0 = s0[s];
+    const double c = is_var ? g[0] - Q : 0.0;
+    const double mu = c / n;
+    const double ajj = is_var ? Mf * G0[lane * 32 + lane] - 2.0 * Bj + S0 : 0.0;
+    const double var = ajj / n - mu * mu;
+    double isd = 1.0;
+    if (scale && is_var && var > 10.0 * DBL_EPSILON) isd = 1.0 / sqrt(var);       // StandardScaler: near-constant columns keep scale 1
+    // a[i] = G[i][lane]
+    double a[FDB_F], inv[FDB_F];
+#pragma unroll
+    for (int i = 0; i < FDB_F; ++i) {
+        const double mu_i = shfl_d(mu, i), isd_i = shfl_d(isd, i), B_i = shfl_d(Bj, i);
+        const bool var_i = (varying >> i) & 1u;
+        double v = 0.0;
+        if (lane < FDB_F) {
+            if (var_i && is_var) v = (Mf * G0[i * 32 + lane] - B_i - Bj + S0 - n * mu_i * mu) * isd_i * isd;
+            else v = (i == lane) ? 1.0 : 0.0;                                      // features outside `varying` never enter
+        }
+        a[i] = v;
+        inv[i] = (i == lane) ? 1.0 : 0.0;
+        if (lane < FDB_F) lg[((size_t)s * FDB_F + i) * 32 + lane] = v;
+    }
+    // Gauss-Jordan without pivoting (G is symmetric positive definite for any set the WLS itself can use)
+    bool singular = false;
+#pragma unroll
+    for (int k = 0; k < FDB_F; ++k) {
+        const double pk = shfl_d(a[k], k);
+        if (!(fabs(pk) > 1e-300)) { singular = true; break; }
+        const double r = 1.0 / pk;
+        const double ak = a[k] * r, ik = inv[k] * r;
+#pragma unroll
+        for (int i = 0; i < FDB_F; ++i) {
+            const double f = shfl_d(a[i], k);
+            if (i != k) {
+                a[i] = fma(-f, ak, a[i]);
+                inv[i] = fma(-f, ik, inv[i]);
+            }
+        }
+        a[k] = ak;
+        inv[k] = ik;
+    }
+    if (lane < FDB_F) {
+#pragma unroll
+        for (int i = 0; i < FDB_F; ++i) lginv[((size_t)s * FDB_F + i) * 32 + lane] = singular ? 0.0 : inv[i];
+    }
+    double* V = lvec + (size_t)s * kVecStride;
+    V[lane] = c;
+    V[32 + lane] = isd;
+    V[64 + lane] = lane == 0 ? Q : (lane == 1 ? n : 0.0);
+}
+
+// ---- warp-parallel dense pieces over the n x n lower-triangular factor in shared memory (lane i = row / position i)
+
+// forward substitution  L w = t  (t: lane i holds t_i); returns w_i in lane i.  `doff` is added to the diagonal.
+__device__ __forceinline__ double trsv_lower(const LassoScratch& S, int n, double t, int lane, double doff) {
+    double w = 0.0;
+    for (int a = 0; a < n; ++a) {
+        const double wa = shfl_d(t, a) / (S.L[a][a] + doff);
+        if (lane == a) w = wa;
+        if (lane > a && lane < n) t -= S.L[lane][a] * wa;
+    }
+    return w;
+}
+// backward substitution  L' x = t
+__device__ __forceinline__ double trsv_lower_t(const LassoScratch& S, int n, double t, int lane, double doff) {
+    double x = 0.0;
+    for (int a = n - 1; a >= 0; --a) {
+        const double xa = shfl_d(t, a) / (S.L[a][a] + doff);
+        if (lane == a) x = xa;
+        if (lane < a) t -= S.L[a][lane] * xa;
+    }
+    return x;
+}
+// Cholesky factor of G[act, act] from scratch (after a drop): lane i owns row i
+__device__ __forceinline__ void chol_rebuild(LassoScratch& S, int n, const double* __restrict__ G, int lane) {
+    const int fi = lane < n ? S.act[lane] : 0;
+    for (int k = 0; k < n; ++k) {
+        double sv = 0.0;
+        if (lane >= k && lane < n) {
+            sv = G[S.act[k] * 32 + fi];
+            for (int b = 0; b < k; ++b) sv -= S.L[lane][b] * S.L[k][b];
+        }
+        const double dk = fmax(sqrt(fabs(shfl_d(sv, k))), DBL_EPSILON);
+        if (lane == k) S.L[k][k] = dk;
+        else if (lane > k && lane < n) S.L[lane][k] = sv / dk;
+        __syncwarp();
+    }
+}
+
+struct RowProducts {
+    double xy;      // lane j: centred (scaled) X'y of feature j, 0 outside `varying`
+    double yy;      // centred y'y
+    double T;       // lane j: sum_m kw z_mj e_m
+    double d;       // link(f(x)) - link(fnull)
+};
+
+// LARS-lasso walk on (G, X'y); records RSS and support of every path point in S.rss / S.nz; returns the point count - 1
+__device__ int lasso_path(LassoScratch& S, const double* __restrict__ G, const RowProducts& R, double n_aug, bool is_var,
+                          int n_var, int lane) {
+    const double eps = DBL_EPSILON, tiny32 = (double)FLT_MIN, eq_tol = (double)FLT_EPSILON;
+    double Cov = is_var ? R.xy : 0.0;
+    bool inactive = is_var;
+    double coef = 0.0;
+    int my_a = -1;                           // position of this lane's feature in the active list
+    int n_active = 0, n_iter = 0;
+    bool drop = false;
+    double prev_alpha = DBL_MAX;
+    if (lane == 0) { S.rss[0] = R.yy; S.nz[0] = 0u; }
+    while (true) {
+        double best = inactive ? fabs(Cov) : -1.0;
+        int bidx = lane;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const double ob = shfl_xor_d(best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bidx, o);
+            if (ob > best || (ob == best && oi < bidx)) { best = ob; bidx = oi; }
+        }
+        const double C = best >= 0.0 ? best : 0.0;
+        const double alpha = C / n_aug;
+        if (alpha <= eq_tol) break;
+        if (n_iter >= kMaxPath || n_active >= n_var) break;
+        if (!drop) {
+            // append feature bidx to the factorisation: L[n][:n] = L^-1 G[act, bidx], L[n][n] = sqrt(G_bb - |.|^2)
+            const int n = n_active;
+            const double t = lane < n ? G[bidx * 32 + S.act[lane]] : 0.0;
+            const double w = trsv_lower(S, n, t, lane, 0.0);
+            const double v = warp_sum(lane < n ? w * w : 0.0);
+            const double diag = fmax(sqrt(fabs(G[bidx * 32 + bidx] - v)), eps);
+            if (diag < 1e-7) {                                       // sklearn: degenerate regressor, zero its Cov and go on
+                if (lane == bidx) Cov = 0.0;
+                continue;
+            }
+            if (lane < n) S.L[n][lane] = w;
+            const double csig = shfl_d(Cov, bidx);
+            if (lane == 0) {
+                S.L[n][n] = diag;
+                S.act[n] = bidx;
+                S.sgn[n] = csig > 0.0 ? 1.0 : (csig < 0.0 ? -1.0 : 0.0);
+            }
+            if (lane == bidx) { inactive = false; coef = 0.0; my_a = n; }
+            ++n_active;
+            __syncwarp();
+        }
+        if (n_iter > 0 && prev_alpha < alpha) break;                 // alpha no longer decreasing: numerical end of the path
+        // equiangular direction: (L L') ls = sign, scaled by AA = 1 / sqrt(ls . sign)
+        const int n = n_active;
+        const double sg = lane < n ? S.sgn[lane] : 0.0;
+        double lsv = 0.0, AA = 0.0, doff = 0.0;
+        for (int attempt = 0;; ++attempt) {
+            lsv = trsv_lower_t(S, n, trsv_lower(S, n, sg, lane, doff), lane, doff);
+            if (attempt == 0 && n == 1 && shfl_d(lsv, 0) == 0.0) { lsv = lane == 0 ? 1.0 : 0.0; AA = 1.0; break; }
+            double tmp = warp_sum(lane < n ? lsv * sg : 0.0);
+            if (attempt > 0) tmp = fmax(tmp, eps);
+            AA = 1.0 / sqrt(tmp);
+            if (isfinite(AA) || attempt > 60) { lsv *= AA; break; }
+            doff += ldexp(eps, attempt);
+        }
+        if (lane < n) S.ls[lane] = lsv;
+        __syncwarp();
+        double corr = 0.0;
+        if (inactive) {
+            for (int a = 0; a < n; ++a) corr += G[S.act[a] * 32 + lane] * S.ls[a];
+            corr = rint(corr * 1e15) / 1e15;                         // np.around(..., decimals=15)
+        }
+        const double g1 = warp_min(inactive ? min_pos((C - Cov) / (AA - corr + tiny32)) : DBL_MAX);
+        const double g2 = warp_min(inactive ? min_pos((C + Cov) / (AA + corr + tiny32)) : DBL_MAX);
+        double gamma = fmin(fmin(g1, g2), C / AA);
+        const double my_ls = my_a >= 0 ? S.ls[my_a] : 0.0;
+        const double zz = my_a >= 0 ? min_pos(-coef / (my_ls + tiny32)) : DBL_MAX;
+        const double z_pos = warp_min(zz);
+        drop = false;
+        bool leaving = false;
+        if (z_pos < gamma) {
+            leaving = my_a >= 0 && zz == z_pos;
+            gamma = z_pos;
+            drop = true;
+        }
+        ++n_iter;
+        if (my_a >= 0) coef += gamma * my_ls;
+        if (inactive) Cov -= gamma * corr;
+        prev_alpha = alpha;
+        // path point n_iter: q = G coef, RSS = y'y - 2 coef.X'y + coef.q, support = |coef| > eps
+        double q = 0.0;
+        for (int a = 0; a < n; ++a) {
+            const int f = S.act[a];
+            q += G[f * 32 + lane] * shfl_d(coef, f);
+        }
+        const double rss = R.yy - warp_sum(coef * (2.0 * R.xy - q));
+        const uint32_t nz = __ballot_sync(0xffffffffu, fabs(coef) > eps);
+        if (lane == 0) { S.rss[n_iter] = rss; S.nz[n_iter] = nz; }
+        if (drop) {
+            // the coefficient that reached zero leaves: Cov from scratch, list compacted, factor rebuilt
+            if (leaving) { Cov = R.xy - q; coef = 0.0; inactive = true; }
+            const uint32_t out = __ballot_sync(0xffffffffu, leaving);
+            __syncwarp();
+            if (lane == 0) {
+                int k = 0;
+                for (int a = 0; a < n; ++a)
+                    if (!((out >> S.act[a]) & 1u)) { S.act[k] = S.act[a]; S.sgn[k] = S.sgn[a]; ++k; }
+            }
+            n_active = n - __popc(out);
+            __syncwarp();
+            my_a = -1;
+            for (int a = 0; a < n_active; ++a)
+                if (S.act[a] == lane) my_a = a;
+            chol_rebuild(S, n_active, G, lane);
+            if (n_active == 0) drop = false;
+        }
+        __syncwarp();
+    }
+    return n_iter;
+}
+
+// Lasso(alpha) support: cyclic coordinate descent on the Gram form from w = 0 with sklearn's stopping rule
+// (largest update / largest coefficient < tol, then duality gap < tol * y'y; tol = 1e-4, max_iter = 1000).
+__device__ uint32_t lasso_cd_support(const double* __restrict__ G, const RowProducts& R, double lam, bool is_var, int lane) {
+    const double tol = 1e-4;
+    const double gjj = lane < FDB_F ? G[lane * 32 + lane] : 1.0;
+    double w = 0.0, q = 0.0;                 // lane j: w_j and (G w)_j
+    for (int it = 0; it < 1000; ++it) {
+        double w_max = 0.0, d_w_max = 0.0;
+        for (int j = 0; j < FDB_F; ++j) {
+            const double wj = shfl_d(w, j), dj = shfl_d(gjj, j);
+            const double t = shfl_d(R.xy - q, j) + dj * wj;
+            const bool var_j = __shfl_sync(0xffffffffu, (int)is_var, j) != 0;
+            if (!var_j || dj == 0.0) continue;
+            const double mag = fabs(t) - lam;
+            const double nw = mag > 0.0 ? copysign(mag, t) / dj : 0.0;
+            const double dw = nw - wj;
+            if (dw != 0.0) {
+                if (lane < FDB_F) q += G[j * 32 + lane] * dw;
+                if (lane == j) w = nw;
+            }
+            d_w_max = fmax(d_w_max, fabs(dw));
+            w_max = fmax(w_max, fabs(nw));
+        }
+        if (w_max == 0.0 || d_w_max / w_max < tol || it == 999) {
+            const double dual = warp_max(is_var ? fabs(R.xy - q) : 0.0);
+            const double wxy = warp_sum(w * R.xy), wq = warp_sum(w * q), l1 = warp_sum(fabs(w));
+            const double r2 = R.yy - 2.0 * wxy + wq;
+            double cst = 1.0, gap = r2;
+            if (dual > lam) { cst = lam / dual; gap = 0.5 * (r2 + r2 * cst * cst); }
+            gap += lam * l1 - cst * (R.yy - wxy);
+            if (gap < tol * R.yy) break;
+        }
+    }
+    return __ballot_sync(0xffffffffu, w != 0.0) & 0x3FFFFFFFu;
+}
+
+struct Coef30 { double w[FDB_F]; };
+
+// MODE 0: information criterion (factor = 2 for AIC, log n for BIC, chosen by `bic`); MODE 1: Lasso(alpha)
+template <int MODE>
+__global__ void __launch_bounds__(128) kshap_lasso_solve(
+    const float* __restrict__ x, int64_t row_offset, int n_rows, const int32_t* __restrict__ set_idx, int n_sets,
+    const uint32_t* __restrict__ bits, const float* __restrict__ kw, int m_pad, const float* __restrict__ ey,
+    const double* __restrict__ gz, const double* __restrict__ bv, const double* __restrict__ s0v,
+    const double* __restrict__ lg, const double* __restrict__ lginv, const double* __restrict__ lvec,
+    const Coef30 wc, double intercept, double fnull, int link, int bic, double alpha_l1,
+    float* __restrict__ phi, double* __restrict__ abs_sum, int accumulate, int64_t total_rows,
+    double* __restrict__ partials, unsigned int* __restrict__ ticket, uint32_t varying) {
+    __shared__ LassoScratch scr[4];
+    __shared__ float s_tab[32];                                   // sqrt(M - s) + sqrt(s) by coalition size
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const bool is_var = (varying >> lane) & 1u;
+    const int n_var = __popc(varying);
+    const double Mf = (double)n_var;
+    if (threadIdx.x < 32) s_tab[lane] = lane <= n_var ? (float)(sqrt(Mf - (double)lane) + sqrt((double)lane)) : 0.f;
+    __syncthreads();
+    LassoScratch& S = scr[warp];
+    const double lnull = link == 1 ? log(fnull / (1.0 - fnull)) : fnull;
+    double wk = 0.0;
+#pragma unroll
+    for (int j = 0; j < FDB_F; ++j)
+        if (j == lane) wk = wc.w[j];
+    double abs_acc = 0.0;
+
+    for (int r = blockIdx.x * 4 + warp; r < n_rows; r += gridDim.x * 4) {
+        const int s = set_idx ? set_idx[r] : (n_sets == 1 ? 0 : (int)((row_offset + r) % n_sets));
+        const double zl = warp_sum(lane < FDB_F ? wk * (double)x[(size_t)r * FDB_F + lane] : 0.0) + intercept;
+        RowProducts R;
+        R.d = (link == 1 ? zl : 1.0 / (1.0 + exp(-zl))) - lnull;
+        // ---- one pass over the row's coalition expectations: T_j, E2 = sum kw e^2, P1 = sum r_m e  (float64 sums)
+        const uint32_t* sb = bits + (size_t)s * m_pad;
+        const float* sk = kw + (size_t)s * m_pad;
+        const float* er = ey + (size_t)r * m_pad;
+        double e2 = 0.0, p1 = 0.0;
+        {
+            double gj[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) gj[j] = 0.0;
+            for (int m0 = 0; m0 < m_pad; m0 += 32) {
+                const uint32_t b = sb[m0 + lane] & varying;
+                const float kwv = sk[m0 + lane];
+                if (kwv != 0.f) {                                   // lanes diverge only on the padding of the last words
+                    const double e = (double)fdb_kshap_link(er[m0 + lane], link) - lnull;
+                    const double v = (double)kwv * e;
+                    e2 = fma(v, e, e2);
+                    p1 = fma((double)(sqrtf(kwv) * s_tab[__popc(b)]), e, p1);
+#pragma unroll
+                    for (int j = 0; j < FDB_F; ++j) gj[j] += ((b >> j) & 1u) ? v : 0.0;
+                }
+            }
+            transpose_reduce(gj, lane);
+            R.T = is_var ? gj[0] : 0.0;
+        }
+        const double E2 = warp_sum(e2), P1 = warp_sum(p1), Tsum = warp_sum(R.T);
+        const double* G = lg + (size_t)s * FDB_F * 32;
+        const double* V = lvec + (size_t)s * kVecStride;
+        const double Bj = bv[(size_t)s * 32 + lane], S0 = s0v[s];
+        const double cj = V[lane], isd = V[32 + lane], Q = V[64], n_aug = V[65];
+        const double ysum = P1 - R.d * Q;
+        R.xy = is_var ? (Mf * R.T - R.d * Bj - Tsum + R.d * S0 - cj * ysum / n_aug) * isd : 0.0;
+        R.yy = Mf * E2 - 2.0 * R.d * Tsum + R.d * R.d * S0 - ysum * ysum / n_aug;
+
+        uint32_t sel;
+        if (MODE == 0) {
+            // noise variance of LassoLarsIC: OLS residual / (n - M - 1), RSS_ols = y'y - X'y . G^-1 X'y
+            const double* Gi = lginv + (size_t)s * FDB_F * 32;
+            double u = 0.0;
+            for (int i = 0; i < FDB_F; ++i) u += (lane < FDB_F ? Gi[i * 32 + lane] : 0.0) * shfl_d(R.xy, i);
+            const double sigma2 = (R.yy - warp_sum(R.xy * u)) / (n_aug - Mf - 1.0);
+            const int n_pts = lasso_path(S, G, R, n_aug, is_var, n_var, lane);
+            __syncwarp();
+            const double factor = bic ? log(n_aug) : 2.0;
+            double best = DBL_MAX;
+            int bk = n_pts;                                         // no usable noise estimate: keep the end of the path
+            if (sigma2 > 0.0) {
+                for (int k = lane; k <= n_pts; k += 32) {
+                    const double c = S.rss[k] / sigma2 + factor * (double)__popc(S.nz[k]);
+                    if (c < best) { best = c; bk = k; }
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    const double ob = shfl_xor_d(best, o);
+                    const int ok = __shfl_xor_sync(0xffffffffu, bk, o);
+                    if (ob < best || (ob == best && ok < bk)) { best = ob; bk = ok; }
+                }
+            }
+            sel = S.nz[bk] & varying;
+        } else {
+            sel = lasso_cd_support(G, R, alpha_l1 * n_aug, is_var, lane) & varying;
+        }
+        __syncwarp();
+
+        // ---- additivity-constrained WLS over the selected features (ascending; the last one is eliminated)
+        const int n_sel = __popc(sel);
+        double p = 0.0;
+        if (n_sel == 1) {
+            if ((sel >> lane) & 1u) p = R.d;
+        } else if (n_sel > 1) {
+            const int kk = n_sel - 1;
+            const int l = 31 - __clz(sel);
+            const double* Gz = gz + (size_t)s * FDB_F * 32;
+            const int pos = __popc(sel & ((1u << lane) - 1u));       // position of feature `lane` in the selection
+            if (((sel >> lane) & 1u) && lane != l) S.act[pos] = lane;
+            __syncwarp();
+            const double Tl = shfl_d(R.T, l);
+            double rhs = 0.0;
+            if (lane < kk) {
+                const int ia = S.act[lane];
+                for (int b = 0; b < kk; ++b) {
+                    const int ib = S.act[b];
+                    S.L[lane][b] = Gz[ia * 32 + ib] - Gz[ia * 32 + l] - Gz[l * 32 + ib] + Gz[l * 32 + l];
+                }
+            }
+            for (int a = 0; a < kk; ++a) {
+                const double t = shfl_d(R.T, S.act[a]);
+                if (lane == a) rhs = t - Tl - R.d * (Gz[S.act[a] * 32 + l] - Gz[l * 32 + l]);
+            }
+            __syncwarp();
+            // elimination without pivoting (X'WX is symmetric positive definite), lane = row
+            for (int c = 0; c < kk; ++c) {
+                const double piv = S.L[c][c];
+                const double rc = shfl_d(rhs, c);
+                if (lane > c && lane < kk) {
+                    const double f = S.L[lane][c] / piv;
+                    for (int q = c + 1; q < kk; ++q) S.L[lane][q] -= f * S.L[c][q];
+                    rhs -= f * rc;
+                }
+                __syncwarp();
+            }
+            double sol = 0.0;
+            for (int c = kk - 1; c >= 0; --c) {
+                const double xc = shfl_d(rhs, c) / S.L[c][c];
+                if (lane == c) sol = xc;
+                if (lane < c) rhs -= S.L[lane][c] * xc;
+            }
+            if (lane < kk) S.ls[lane] = sol;
+            const double sumw = warp_sum(lane < kk ? sol : 0.0);
+            __syncwarp();
+            if ((sel >> lane) & 1u) p = lane == l ? R.d - sumw : S.ls[pos];
+            __syncwarp();
+        }
+        if (fabs(p) < 1e-10) p = 0.0;
+        if (lane < FDB_F) phi[(size_t)r * FDB_F + lane] = (float)p;
+        abs_acc += fabs(p);
+    }
+    if (abs_sum == nullptr) return;
+    __shared__ double s_acc[4][32];
+    __shared__ bool s_last;
+    s_acc[warp][lane] = abs_acc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        partials[(size_t)blockIdx.x * 32 + lane] = s_acc[0][lane] + s_acc[1][lane] + s_acc[2][lane] + s_acc[3][lane];
+        __threadfence();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+    __syncthreads();
+    if (s_last && threadIdx.x < 32) {
+        __threadfence();
+        double tot = 0.0;
+        if (lane < FDB_F) {
+            for (unsigned b = 0; b < gridDim.x; ++b) tot += __ldcg(partials + (size_t)b * 32 + lane);
+            if (accumulate) tot += abs_sum[lane];
+        } else if (lane == FDB_F) {
+            tot = (double)total_rows;
+        }
+        abs_sum[lane] = tot;
+        if (lane == 0) *ticket = 0u;
+    }
+}
+
+}  // namespace
+
+static int launch_prepare(fdb_kshap_plan* p, cudaStream_t st) {
+    kshap_lasso_prepare<<<p->n_sets, 32, 0, st>>>(p->d_bits, p->d_kw, p->m_pad, p->d_gz, p->d_bv, p->d_s0, p->d_lg, p->d_lginv,
+                                                   p->d_lvec, p->varying, p->lasso_scaled);
+    FDB_CUDA(cudaGetLastError());
+    return FDB_OK;
+}
+
+// scale = 1: unit-variance columns (the StandardScaler step in front of LassoLarsIC); 0: plain centring (Lasso(alpha))
+int fdb_kshap_prepare_lasso(fdb_kshap_plan* p, int scale) {
+    int rc = fdb_kshap_prepare_lars(p);                       // Z'WZ, B, S0
+    if (rc != FDB_OK) return rc;
+    if (p->d_lg != nullptr && p->lasso_scaled == scale) return FDB_OK;
+    if (p->d_lg == nullptr) {
+        FDB_CUDA(cudaMalloc((void**)&p->d_lg, (size_t)p->n_sets * FDB_F * 32 * 8));
+        FDB_CUDA(cudaMalloc((void**)&p->d_lginv, (size_t)p->n_sets * FDB_F * 32 * 8));
+        FDB_CUDA(cudaMalloc((void**)&p->d_lvec, (size_t)p->n_sets * kVecStride * 8));
+    }
+    p->lasso_scaled = scale;
+    rc = launch_prepare(p, 0);
+    if (rc != FDB_OK) return rc;
+    FDB_CUDA(cudaDeviceSynchronize());
+    return FDB_OK;
+}
+
+// after a resample (stream-ordered, after fdb_kshap_refresh_lars on the same stream)
+int fdb_kshap_refresh_lasso(fdb_kshap_plan* p, cudaStream_t st) {
+    if (p->d_lg == nullptr) return FDB_OK;
+    return launch_prepare(p, st);
+}
+
+void fdb_kshap_free_lasso(fdb_kshap_plan* p) {
+    cudaFree(p->d_lg); cudaFree(p->d_lginv); cudaFree(p->d_lvec);
+    p->d_lg = nullptr; p->d_lginv = nullptr; p->d_lvec = nullptr;
+    p->lasso_scaled = -1;
+}
+
+int fdb_kshap_launch_lasso_solve(fdb_kshap_plan* p, cudaStream_t st, const float* x, int64_t row_offset, int n_rows,
+                                 const int32_t* set_idx, float* phi, double* abs_sum, int accumulate, int64_t total_rows) {
+    int grid = (n_rows + 3) / 4;
+    const int cap = p->ctx->sm_count * 8;
+    if (grid > cap) grid = cap;
+    Coef30 wc;
+    for (int j = 0; j < FDB_F; ++j) wc.w[j] = p->coef[j];
+    if (p->l1_mode == FDB_KSHAP_L1_ALPHA)
+        kshap_lasso_solve<1><<<grid, 128, 0, st>>>(x, row_offset, n_rows, set_idx, p->n_sets, p->d_bits, p->d_kw, p->m_pad, p->d_ey,
+                                                  p->d_gz, p->d_bv, p->d_s0, p->d_lg, p->d_lginv, p->d_lvec, wc, p->intercept,
+                                                  p->fnull, p->link, 0, p->l1_alpha, phi, abs_sum, accumulate, total_rows,
+                                                  p->d_partials, p->d_ticket, p->varying);
+    else
+        kshap_lasso_solve<0><<<grid, 128, 0, st>>>(x, row_offset, n_rows, set_idx, p->n_sets, p->d_bits, p->d_kw, p->m_pad, p->d_ey,
+                                                  p->d_gz, p->d_bv, p->d_s0, p->d_lg, p->d_lginv, p->d_lvec, wc, p->intercept,
+                                                  p->fnull, p->link, p->l1_mode == FDB_KSHAP_L1_BIC ? 1 : 0, 0.0, phi, abs_sum,
+                                                  accumulate, total_rows, p->d_partials, p->d_ticket, p->varying);
+    FDB_CUDA(cudaGetLastError());
+    return FDB_OK;
+}

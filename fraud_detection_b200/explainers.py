@@ -131,6 +131,45 @@ class B200LinearExplainer:
 # Kernel SHAP
 # =========================================================================================
 EVAL_AUTO, EVAL_TC, EVAL_SIMT, EVAL_FACTORED = -1, 0, 1, 2
+L1_NONE, L1_NUM_FEATURES, L1_AIC, L1_BIC, L1_ALPHA = 0, 1, 2, 3, 4
+
+
+class _L1Spec:
+    """``l1_reg`` of ``KernelExplainer.shap_values`` [recalled from shap/explainers/_kernel.py::solve]:
+    ``False`` / 0 no selection; ``"num_features(k)"`` LARS; ``"aic"`` / ``"bic"`` LassoLarsIC; a float Lasso(alpha);
+    ``"auto"`` AIC when the coalitions cover less than 20 % of the 2^M - 2 possible ones, nothing otherwise."""
+
+    def __init__(self, l1_reg):
+        self.auto = False
+        self.mode, self.param = L1_NONE, 0.0
+        if isinstance(l1_reg, str):
+            if l1_reg.startswith("num_features("):
+                k = int(l1_reg[len("num_features("):-1])
+                if not 1 <= k <= 16:
+                    raise ValueError("num_features(k) is supported for 1 <= k <= 16")
+                self.mode, self.param = L1_NUM_FEATURES, float(k)
+            elif l1_reg == "auto":
+                self.auto = True
+            elif l1_reg in ("aic", "bic"):
+                self.mode = L1_AIC if l1_reg == "aic" else L1_BIC
+            else:
+                raise ValueError(f"l1_reg must be False, 'auto', 'aic', 'bic', 'num_features(k)' or a float, got {l1_reg!r}")
+        elif l1_reg is False or l1_reg is None or l1_reg == 0:
+            pass
+        else:
+            alpha = float(l1_reg)
+            if not (alpha > 0.0 and np.isfinite(alpha)):
+                raise ValueError(f"a numeric l1_reg is the Lasso penalty and must be positive, got {l1_reg!r}")
+            self.mode, self.param = L1_ALPHA, alpha
+
+    def resolve(self, m_feat: int, nsamples):
+        """(mode, param) for rows with ``m_feat`` varying features explained with ``nsamples`` coalitions."""
+        if not self.auto:
+            return self.mode, self.param
+        from . import sampler as _sampler
+        max_samples = 2 ** m_feat - 2 if m_feat <= 30 else 2 ** 30
+        n = _sampler.resolve_nsamples(m_feat, nsamples)
+        return (L1_AIC, 0.0) if n / float(max_samples) < 0.2 else (L1_NONE, 0.0)
 _LINKS = {"identity": 0, "logit": 1}
 
 
@@ -271,6 +310,12 @@ class KernelShapPlan:
         """``l1_reg="num_features(k)"``: LARS-select k features per row before the constrained WLS (0 = off)."""
         _lib.check(_lib.lib.fdb_kshap_plan_set_num_features(self._h, int(k)))
 
+    def set_l1(self, mode: int, param: float = 0.0) -> None:
+        """Feature selection before the constrained WLS (``l1_reg`` of ``KernelExplainer.shap_values``): ``L1_NONE``,
+        ``L1_NUM_FEATURES`` (param = k), ``L1_AIC`` / ``L1_BIC`` (LassoLarsIC on the standardised augmented system) or
+        ``L1_ALPHA`` (param = the Lasso penalty)."""
+        _lib.check(_lib.lib.fdb_kshap_plan_set_l1(self._h, int(mode), float(param)))
+
     def info(self) -> dict:
         import ctypes as C
         arr = (C.c_int * 8)()
@@ -317,14 +362,16 @@ class KernelShapStream:
     as the work is enqueued, ``synchronize`` waits for everything and raises if a set was singular."""
 
     def __init__(self, coef, intercept, background, batch_rows: int = 32768, nsamples="auto", seed: int = 0, link="identity",
-                 device=None, num_features: int = 0):
+                 device=None, num_features: int = 0, l1_reg=None):
         import torch
         self.device = torch.device("cuda", torch.cuda.current_device() if device is None else int(device))
         self.batch_rows = int(batch_rows)
         self.plans = [KernelShapPlan.sampled(coef, intercept, background, self.batch_rows, nsamples, seed + i, link, self.device.index)
                       for i in range(2)]
         for p in self.plans:
-            if num_features:
+            if l1_reg is not None:                     # any l1_reg value of KernelExplainer.shap_values
+                p.set_l1(*_L1Spec(l1_reg).resolve(N_FEATURES, nsamples))
+            elif num_features:
                 p.set_num_features(num_features)
         self.streams = [torch.cuda.Stream(self.device) for _ in range(2)]
         self.expected_value = self.plans[0].expected_value
@@ -383,7 +430,10 @@ class B200KernelExplainer:
     not bitwise equivalent to shap; ~5 orders of magnitude faster than the Python sampler).
     ``l1_reg`` defaults to ``"num_features(10)"`` like the pinned shap release [recalled]: LARS feature selection on
     the augmented system, then WLS over the 10 selected features, the other 20 get 0.  ``l1_reg=False`` is the
-    plain WLS over all features (BASELINE.json's parity configuration).  Both run on the GPU.
+    plain WLS over all features (BASELINE.json's parity configuration).  ``"aic"`` / ``"bic"`` (LassoLarsIC on the
+    standardised augmented system), a float (``Lasso(alpha)``) and ``"auto"`` (AIC when fewer than 20 % of the 2^M - 2
+    coalitions are evaluated, else no selection - the pre-0.45 default [recalled]) are the other values shap accepts.
+    Every mode selects and solves on the GPU (K3L, ``csrc/kshap_lars.cu`` / ``csrc/kshap_lasso.cu``).
     """
 
     def __init__(self, model, data, link="identity", device=None, keep_index=False, multi_output=False, **kwargs):
@@ -443,14 +493,7 @@ class B200KernelExplainer:
     def _shap_values_class1(self, X, nsamples="auto", l1_reg="num_features(10)", mask_mode="per_row", masks=None, evaluator=EVAL_AUTO,
                             random=None, silent=True, sampler="host", seed=0, **kwargs):
         from . import sampler as _sampler
-        num_features = 0
-        if isinstance(l1_reg, str) and l1_reg.startswith("num_features("):
-            num_features = int(l1_reg[len("num_features("):-1])
-            if not 1 <= num_features <= 16:
-                raise ValueError("num_features(k) is supported for 1 <= k <= 16")
-        elif l1_reg not in (False, 0):
-            raise NotImplementedError("l1_reg must be False/0 (plain constrained WLS) or 'num_features(k)'; "
-                                      "'auto'/'aic'/'bic'/a Lasso alpha are not available on the B200 path")
+        l1 = _L1Spec(l1_reg)
         A, single = _plain_rows(X)
         A64 = A.astype(np.float64, copy=False)
         varying = self._varying(A64)
@@ -485,7 +528,7 @@ class B200KernelExplainer:
 
         if len(part):
             self._explain_partial(A, varying, part, host_sets if mask_mode == "per_row" else None, shared_set,
-                                  num_features, evaluator, out)
+                                  l1, nsamples, evaluator, out)
         if len(rows) == 0:
             return out[0] if single else out
         Xr = np.ascontiguousarray(A[rows], dtype=np.float32)
@@ -505,7 +548,7 @@ class B200KernelExplainer:
                 self._device_plans[key] = plan
             else:
                 plan.resample(call_seed)
-            plan.set_num_features(num_features)
+            plan.set_l1(*l1.resolve(N_FEATURES, nsamples))
             out[rows] = plan.explain_host(Xr, None, evaluator)
             return out[0] if single else out
         if masks is not None:
@@ -529,14 +572,13 @@ class B200KernelExplainer:
                 self._shared_plans.clear()
                 bits, kw = self._pad_sets(sets)
                 plan = self._shared_plans[key] = KernelShapPlan(self.coef, self.intercept, self.data, bits, kw, self.link, self.device)
-            plan.set_num_features(num_features)
+            plan.set_l1(*l1.resolve(N_FEATURES, nsamples))
             out[rows] = plan.explain_host(Xr, None, evaluator)
             return out[0] if single else out
         bits, kw = self._pad_sets(sets)
         plan = KernelShapPlan(self.coef, self.intercept, self.data, bits, kw, self.link, self.device)
         try:
-            if num_features:
-                plan.set_num_features(num_features)
+            plan.set_l1(*l1.resolve(N_FEATURES, nsamples if masks is None else sets[0][0].shape[0]))
             phi = plan.explain_host(Xr, None, evaluator)
         finally:
             plan.close()
@@ -564,7 +606,7 @@ class B200KernelExplainer:
             out |= ((b >> np.uint32(j)) & np.uint32(1)) << np.uint32(pz)
         return out
 
-    def _explain_partial(self, A, varying, part, host_sets, shared_set, num_features, evaluator, out):
+    def _explain_partial(self, A, varying, part, host_sets, shared_set, l1, nsamples, evaluator, out):
         """Rows where 2..29 features differ from the background (shap: M = len(varyingInds) < 30): coalitions are
         drawn over the M varying features, the others get phi = 0.  Rows are grouped by their varying pattern;
         per group the feature axis is permuted so that the last varying feature - the one the additivity
@@ -580,8 +622,7 @@ class B200KernelExplainer:
             plan = KernelShapPlan(self.coef[perm], self.intercept, self.data[:, perm], bits, kw, self.link, self.device,
                                   varying_mask=vmask)
             try:
-                if num_features:
-                    plan.set_num_features(num_features)
+                plan.set_l1(*l1.resolve(len(v), nsamples))
                 phi = plan.explain_host(np.ascontiguousarray(A[grp][:, perm], dtype=np.float32), None, evaluator)
             finally:
                 plan.close()

@@ -173,6 +173,17 @@ int fdb_kshap_plan_info(const fdb_kshap_plan* plan, int* info8);
  * augmented system (sklearn lars_path semantics, float64) and solves the constrained WLS over them only;
  * k = 0 (default) is l1_reg=False.  k <= 16. */
 int fdb_kshap_plan_set_num_features(fdb_kshap_plan* plan, int k);
+/* The other l1_reg values of KernelExplainer.shap_values (shap/explainers/_kernel.py::solve [recalled]):
+ *   FDB_KSHAP_L1_NONE          l1_reg=False / 0                       param ignored
+ *   FDB_KSHAP_L1_NUM_FEATURES  "num_features(k)"                      param = k (same as fdb_kshap_plan_set_num_features)
+ *   FDB_KSHAP_L1_AIC / _BIC    "aic" / "bic": make_pipeline(StandardScaler(with_mean=False), LassoLarsIC(criterion)) on
+ *                              the augmented system; the features with a nonzero coefficient at the criterion's minimum
+ *                              along the LARS-lasso path are kept           param ignored
+ *   FDB_KSHAP_L1_ALPHA         a float: Lasso(alpha=param) on the augmented system, nonzero coefficients are kept
+ * "auto" is the caller's decision (AIC when nsamples / (2^M - 2) < 0.2, none otherwise).  Selection runs per explained
+ * row on the device in float64 (csrc/kshap_lasso.cu); the constrained WLS is then solved over the kept features. */
+enum { FDB_KSHAP_L1_NONE = 0, FDB_KSHAP_L1_NUM_FEATURES = 1, FDB_KSHAP_L1_AIC = 2, FDB_KSHAP_L1_BIC = 3, FDB_KSHAP_L1_ALPHA = 4 };
+int fdb_kshap_plan_set_l1(fdb_kshap_plan* plan, int mode, double param);
 int fdb_kshap_explain_dev(fdb_kshap_plan* plan, void* stream, int64_t n_rows, const float* x,
                           const int32_t* set_idx, int evaluator, float* phi, float* ey_out, double* abs_sum);
 int fdb_kshap_explain_host(fdb_kshap_plan* plan, int64_t n_rows, const float* x, const int32_t* set_idx,

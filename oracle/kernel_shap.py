@@ -185,15 +185,23 @@ def evaluate(f, x: np.ndarray, background: np.ndarray, Z: np.ndarray,
 
 # ------------------------------------------------------------------ steps 7-8: solve
 def solve(Z: np.ndarray, kw: np.ndarray, ey: np.ndarray, fx: float, fnull: float,
-          link: str = "identity", l1_reg=False) -> np.ndarray:
-    """Constrained weighted least squares of ``KernelExplainer.solve``."""
+          link: str = "identity", l1_reg=False, fraction_evaluated: float = 0.0,
+          ic_standardize: bool = True) -> np.ndarray:
+    """Constrained weighted least squares of ``KernelExplainer.solve``.
+
+    ``l1_reg`` [recalled]: ``"num_features(k)"`` -> ``lars_path(max_iter=k)``; ``"aic"`` / ``"bic"`` ->
+    ``make_pipeline(StandardScaler(with_mean=False), LassoLarsIC(criterion=c))`` (the scaler step replaced the
+    ``normalize=False`` argument sklearn 1.2 deprecated; ``ic_standardize=False`` restates the older plain
+    ``LassoLarsIC``); ``"auto"`` -> ``"aic"`` when ``fraction_evaluated`` (= nsamples / (2^M - 2)) is below 0.2, no
+    selection otherwise; a float -> ``Lasso(alpha=l1_reg)``; ``False`` / 0 -> no selection.
+    """
     lf = LINKS[link]
     M = Z.shape[1]
     eyAdj = lf(ey) - lf(fnull)
     d = lf(fx) - lf(fnull)
     s = np.sum(Z, 1)
     nonzero_inds = np.arange(M)
-    if l1_reg not in ["auto", False, 0]:
+    if (l1_reg not in ["auto", False, 0]) or (fraction_evaluated < 0.2 and l1_reg == "auto"):
         w_aug = np.hstack((kw * (M - s), kw * s))
         w_sqrt_aug = np.sqrt(w_aug)
         eyAdj_aug = np.hstack((eyAdj, eyAdj - d))
@@ -203,9 +211,16 @@ def solve(Z: np.ndarray, kw: np.ndarray, ey: np.ndarray, fx: float, fnull: float
             from sklearn.linear_model import lars_path
             r = int(l1_reg[len("num_features("):-1])
             nonzero_inds = lars_path(mask_aug, eyAdj_aug, max_iter=r)[1]
-        elif l1_reg in ("bic", "aic"):
+        elif l1_reg in ("auto", "bic", "aic"):
             from sklearn.linear_model import LassoLarsIC
-            nonzero_inds = np.nonzero(LassoLarsIC(criterion=l1_reg).fit(mask_aug, eyAdj_aug).coef_)[0]
+            from sklearn.pipeline import make_pipeline
+            from sklearn.preprocessing import StandardScaler
+            c = "aic" if l1_reg == "auto" else l1_reg
+            if ic_standardize:
+                model = make_pipeline(StandardScaler(with_mean=False), LassoLarsIC(criterion=c)).fit(mask_aug, eyAdj_aug)[1]
+            else:
+                model = LassoLarsIC(criterion=c).fit(mask_aug, eyAdj_aug)
+            nonzero_inds = np.nonzero(model.coef_)[0]
         else:
             from sklearn.linear_model import Lasso
             nonzero_inds = np.nonzero(Lasso(alpha=l1_reg).fit(mask_aug, eyAdj_aug).coef_)[0]
@@ -261,10 +276,14 @@ def explain_row(f, x, background, nsamples="auto", l1_reg=False, link="identity"
         if masks is None:
             Z, kw, info = sample_coalitions(M, nsamples, random=random)
             parts["info"] = info
+            n_used, max_samples = resolve_nsamples(M, nsamples)
         else:
             Z, kw = masks
+            n_used, max_samples = len(Z), resolve_nsamples(M, len(Z))[1]
+        # explain(): self.solve(self.nsamples / self.max_samples, d), max_samples = 2^M - 2 for M <= 30 else 2^30 [recalled]
+        fraction = n_used / float(max_samples)
         ey = evaluate(f, x, background, Z, varying)
-        phi[varying] = solve(Z, kw, ey, fx, fnull, link=link, l1_reg=l1_reg)
+        phi[varying] = solve(Z, kw, ey, fx, fnull, link=link, l1_reg=l1_reg, fraction_evaluated=fraction)
         parts.update(Z=Z, kw=kw, ey=ey)
     return (phi, parts) if return_parts else phi
 
