@@ -69,6 +69,7 @@ struct LassoScratch {
     double L[FDB_F][FDB_F + 1];       // Cholesky factor of the active Gram block; afterwards the reduced WLS system [A | rhs]
     double ls[FDB_F];                 // equiangular direction, by active position; afterwards the WLS solution
     double sgn[FDB_F];
+    double dinv[FDB_F];               // 1 / L[a][a]
     int act[FDB_F];
     double rss[kMaxPath + 1];
     uint32_t nz[kMaxPath + 1];
@@ -159,11 +160,13 @@ __global__ void __launch_bounds__(32) kshap_lasso_prepare(const uint32_t* __rest
 
 // ---- warp-parallel dense pieces over the n x n lower-triangular factor in shared memory (lane i = row / position i)
 
-// forward substitution  L w = t  (t: lane i holds t_i); returns w_i in lane i.  `doff` is added to the diagonal.
+// forward substitution  L w = t  (t: lane i holds t_i); returns w_i in lane i.  `doff` (the ill-conditioned retry of
+// sklearn: L.diag += 2^i eps) is added to the diagonal; the regular case multiplies by the stored reciprocals.
 __device__ __forceinline__ double trsv_lower(const LassoScratch& S, int n, double t, int lane, double doff) {
     double w = 0.0;
     for (int a = 0; a < n; ++a) {
-        const double wa = shfl_d(t, a) / (S.L[a][a] + doff);
+        const double ta = shfl_d(t, a);
+        const double wa = doff == 0.0 ? ta * S.dinv[a] : ta / (S.L[a][a] + doff);
         if (lane == a) w = wa;
         if (lane > a && lane < n) t -= S.L[lane][a] * wa;
     }
@@ -173,7 +176,8 @@ __device__ __forceinline__ double trsv_lower(const LassoScratch& S, int n, doubl
 __device__ __forceinline__ double trsv_lower_t(const LassoScratch& S, int n, double t, int lane, double doff) {
     double x = 0.0;
     for (int a = n - 1; a >= 0; --a) {
-        const double xa = shfl_d(t, a) / (S.L[a][a] + doff);
+        const double ta = shfl_d(t, a);
+        const double xa = doff == 0.0 ? ta * S.dinv[a] : ta / (S.L[a][a] + doff);
         if (lane == a) x = xa;
         if (lane < a) t -= S.L[a][lane] * xa;
     }
@@ -189,7 +193,7 @@ __device__ __forceinline__ void chol_rebuild(LassoScratch& S, int n, const doubl
             for (int b = 0; b < k; ++b) sv -= S.L[lane][b] * S.L[k][b];
         }
         const double dk = fmax(sqrt(fabs(shfl_d(sv, k))), DBL_EPSILON);
-        if (lane == k) S.L[k][k] = dk;
+        if (lane == k) { S.L[k][k] = dk; S.dinv[k] = 1.0 / dk; }
         else if (lane > k && lane < n) S.L[lane][k] = sv / dk;
         __syncwarp();
     }
@@ -213,6 +217,7 @@ __device__ int lasso_path(LassoScratch& S, const double* __restrict__ G, const R
     int n_active = 0, n_iter = 0;
     bool drop = false;
     double prev_alpha = DBL_MAX;
+    double yv = 0.0;                         // lane a: (L^-1 sign)_a, extended by one entry per added feature
     if (lane == 0) { S.rss[0] = R.yy; S.nz[0] = 0u; }
     while (true) {
         double best = inactive ? fabs(Cov) : -1.0;
@@ -240,10 +245,14 @@ __device__ int lasso_path(LassoScratch& S, const double* __restrict__ G, const R
             }
             if (lane < n) S.L[n][lane] = w;
             const double csig = shfl_d(Cov, bidx);
+            const double sg_n = csig > 0.0 ? 1.0 : (csig < 0.0 ? -1.0 : 0.0);
+            const double y_n = (sg_n - warp_sum(lane < n ? w * yv : 0.0)) / diag;
+            if (lane == n) yv = y_n;
             if (lane == 0) {
                 S.L[n][n] = diag;
+                S.dinv[n] = 1.0 / diag;
                 S.act[n] = bidx;
-                S.sgn[n] = csig > 0.0 ? 1.0 : (csig < 0.0 ? -1.0 : 0.0);
+                S.sgn[n] = sg_n;
             }
             if (lane == bidx) { inactive = false; coef = 0.0; my_a = n; }
             ++n_active;
@@ -255,7 +264,7 @@ __device__ int lasso_path(LassoScratch& S, const double* __restrict__ G, const R
         const double sg = lane < n ? S.sgn[lane] : 0.0;
         double lsv = 0.0, AA = 0.0, doff = 0.0;
         for (int attempt = 0;; ++attempt) {
-            lsv = trsv_lower_t(S, n, trsv_lower(S, n, sg, lane, doff), lane, doff);
+            lsv = trsv_lower_t(S, n, attempt == 0 ? yv : trsv_lower(S, n, sg, lane, doff), lane, doff);
             if (attempt == 0 && n == 1 && shfl_d(lsv, 0) == 0.0) { lsv = lane == 0 ? 1.0 : 0.0; AA = 1.0; break; }
             double tmp = warp_sum(lane < n ? lsv * sg : 0.0);
             if (attempt > 0) tmp = fmax(tmp, eps);
@@ -312,6 +321,7 @@ __device__ int lasso_path(LassoScratch& S, const double* __restrict__ G, const R
             for (int a = 0; a < n_active; ++a)
                 if (S.act[a] == lane) my_a = a;
             chol_rebuild(S, n_active, G, lane);
+            yv = trsv_lower(S, n_active, lane < n_active ? S.sgn[lane] : 0.0, lane, 0.0);
             if (n_active == 0) drop = false;
         }
         __syncwarp();
