@@ -504,6 +504,15 @@ def bench_kernel_shap(args, torch, dist, device, rank, world, model, scaler, pro
 
     ms = timed(step_auto, steps)
     ms_tc = timed(lambda: plan.explain_dev(x, evaluator=0, phi=phi, abs_sum=abs_sum), steps)   # general tcgen05 evaluator (K2) + K3
+    # the other l1_reg values of KernelExplainer.shap_values (shap's own default is "num_features(10)" [recalled]):
+    # evaluate (K2f, expectations through HBM) + selection + reduced WLS, all on the device
+    l1_modes = {}
+    for name, mode, param in (("num_features(10)", 1, 10.0), ("aic", 2, 0.0), ("bic", 3, 0.0), ("alpha=1e-4", 4, 1e-4)):
+        plan.set_l1(mode, param)
+        ms_l1 = timed(step_auto, 3)
+        l1_modes[name] = {"value": rows * world / (ms_l1 * 1e-3), "unit": "explained rows/s", "ms_per_step": ms_l1,
+                          "features_kept_per_row": float((phi != 0).sum(1).float().mean().item())}
+    plan.set_l1(0, 0.0)
     sig = rows * len(bits) * n_bg
     out = {
         "workload": f"config3: Kernel SHAP nsamples={nsamples}, {n_bg}-row background, {rows} explained rows per GPU, "
@@ -512,7 +521,8 @@ def bench_kernel_shap(args, torch, dist, device, rank, world, model, scaler, pro
         "mode": "ONE shared coalition set for all rows (throughput mode; compare with cpu_baseline.shared_set)",
         "sigmoids_per_s": sig * world / (ms * 1e-3),
         "evaluator": "K2f factored (single coalition set: one exponential per (row, coalition), E[m][b] precomputed) + K3",
-        "gpu_launches_per_step": 2 * -(-rows // 32768),
+        "gpu_launches_per_step": 2 * -(-rows // 262144),      # K2f + K3 per round of up to 262,144 rows
+        "l1_reg_modes": l1_modes,
         "general_evaluator": {"evaluator": "K2 tcgen05 per-element sigmoid (any plan, the per-row-set path) + K3",
                               "value": rows * world / (ms_tc * 1e-3), "unit": "explained rows/s", "ms_per_step": ms_tc,
                               "sigmoids_per_s": sig * world / (ms_tc * 1e-3)},

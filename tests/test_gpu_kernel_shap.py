@@ -272,8 +272,13 @@ def test_explainer_class_matches_oracle_with_same_seed(params):
     again = expl.shap_values(X, nsamples=2048, mask_mode="shared", random=rs8, l1_reg=False)
     assert next(iter(expl._shared_plans.values())) is plan_before and len(expl._shared_plans) == 1
     np.testing.assert_array_equal(again, shared)
-    with pytest.raises(NotImplementedError):
-        expl.shap_values(X, l1_reg="aic")
+    # every l1_reg value shap accepts runs (tests/test_gpu_kernel_shap_l1.py holds the parity cases); the cached plan is reused
+    aic = expl.shap_values(X, nsamples=2048, mask_mode="shared", random=rs8, l1_reg="aic")
+    np.testing.assert_allclose(aic.sum(1) + expl.expected_value, f(X), atol=1e-5)
+    assert next(iter(expl._shared_plans.values())) is plan_before
+    np.testing.assert_array_equal(expl.shap_values(X, nsamples=2048, mask_mode="shared", random=rs8, l1_reg=False), shared)
+    with pytest.raises(ValueError):
+        expl.shap_values(X, l1_reg="ridge")
 
 
 def test_explainer_takes_the_lambda_a_shap_user_writes(params):
