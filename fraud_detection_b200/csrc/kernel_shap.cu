@@ -571,7 +571,7 @@ extern "C" int fdb_kshap_plan_set_num_features(fdb_kshap_plan* p, int k) {
     if (k > 0) {
         DeviceGuard guard(p->ctx->device);
         FDB_REQUIRE(guard.ok, FDB_ERR_CUDA, "cannot select device %d", p->ctx->device);
-        int rc = fdb_kshap_prepare_lars(p);
+        int rc = fdb_kshap_prepare_lasso(p, 2);
         if (rc != FDB_OK) return rc;
     }
     p->num_features = k;
@@ -638,7 +638,9 @@ extern "C" int fdb_kshap_explain_dev(fdb_kshap_plan* p, void* stream, int64_t n_
     FDB_REQUIRE(cur == p->ctx->device, FDB_ERR_STATE, "the plan lives on device %d but the current device is %d", p->ctx->device, cur);
     fdb_ctx* ctx = p->ctx;
     const bool fx = evaluator == FDB_KSHAP_EVAL_FACTORED;
-    const bool need_ey = !fx || ey_out != nullptr || p->l1_mode != FDB_KSHAP_L1_NONE;
+    // num_features(k) selects from X'W y alone, which the factored evaluator leaves in its records; the criteria and the
+    // Lasso penalty also need sum kw e^2 and the weighted mean of e, i.e. the expectations themselves
+    const bool need_ey = !fx || ey_out != nullptr || p->l1_mode > FDB_KSHAP_L1_NUM_FEATURES;
     // rows per evaluate -> solve round: bounded by the ey scratch when expectations go through HBM; the factored path
     // leaves only 256 B per row behind, so it takes large rounds (every CTA gets an equal share of the units)
     int64_t batch = need_ey ? FDB_KSHAP_BATCH_ROWS : FDB_KSHAP_FX_BATCH_ROWS;
@@ -683,13 +685,9 @@ extern "C" int fdb_kshap_explain_dev(fdb_kshap_plan* p, void* stream, int64_t n_
                                                                                  p->link);
             FDB_CUDA(cudaGetLastError());
         }
-        if (p->l1_mode == FDB_KSHAP_L1_NUM_FEATURES) {
-            int rc = fdb_kshap_launch_lars_solve(p, st, xb, r0, nb, sb, phi + r0 * FDB_F, abs_sum, r0 > 0 ? 1 : 0, n_rows);
-            if (rc != FDB_OK) return rc;
-            continue;
-        }
-        if (p->l1_mode != FDB_KSHAP_L1_NONE) {
-            int rc = fdb_kshap_launch_lasso_solve(p, st, xb, r0, nb, sb, phi + r0 * FDB_F, abs_sum, r0 > 0 ? 1 : 0, n_rows);
+        if (p->l1_mode != FDB_KSHAP_L1_NONE) {       // feature selection + reduced WLS (kshap_lasso.cu)
+            int rc = fdb_kshap_launch_lasso_solve(p, st, xb, r0, nb, sb, phi + r0 * FDB_F, abs_sum, r0 > 0 ? 1 : 0, n_rows,
+                                                  (fx && !need_ey) ? p->d_gpart : nullptr, fx_slots, fx_units, fx_grid);
             if (rc != FDB_OK) return rc;
             continue;
         }

@@ -573,7 +573,9 @@ __global__ void kshap_build_fx_tiles(const uint32_t* __restrict__ bits, const fl
     unsigned char* tile = out + (size_t)(m >> 7) * FDB_FX_TILE_BYTES;
     const int ml = m & 127;
     for (int jf = 0; jf < 32; ++jf) {
-        int x = jf < FDB_F - 1 ? (int)((b >> jf) & 1u) - z29 : 0;
+        // columns 0..28: x_mj = z_mj - z_m29 (the WLS regressors); column 29: z_m29 itself, so that the fused GEMM also leaves
+        // T_29 = sum kw z_m29 e_m behind and num_features(k) can rebuild every T_j = sum kw z_mj e_m from the records
+        int x = jf < FDB_F - 1 ? (int)((b >> jf) & 1u) - z29 : (jf == FDB_F - 1 ? z29 : 0);
         if (w == 0.f) x = 0;                                        // padding coalitions
         const uint16_t h = x > 0 ? 0x3F80 : (x < 0 ? 0xBF80 : 0);   // +1 / -1 / 0 in bf16
         *reinterpret_cast<uint16_t*>(tile + (jf >> 3) * 2048 + (ml >> 3) * 128 + (jf & 7) * 16 + (ml & 7) * 2) = h;

@@ -55,7 +55,7 @@ struct fdb_kshap_plan {
     double* d_lg = nullptr;            // [S][30][32] centred (scaled) Gram of the augmented system (kshap_lasso.cu)
     double* d_lginv = nullptr;         // [S][30][32] its inverse
     double* d_lvec = nullptr;          // [S][96] column sums, 1 / sd, Q, n
-    int lasso_scaled = -1;             // which variant d_lg holds: 1 unit-variance columns (criteria), 0 centred only (alpha)
+    int lasso_scaled = -1;             // which variant d_lg holds: 1 unit-variance columns (criteria), 0 centred only (alpha), 2 raw (num_features)
     uint32_t varying = 0x3FFFFFFFu;    // features that differ from the background for the rows of this plan (bit 29 always set)
     float* d_gpart = nullptr;          // [gpart_rows][slots][32] X'W y records written by K2f, folded by K3 (grown on demand)
     size_t ey_cap = 0, gpart_cap = 0;  // floats the two scratch buffers hold
@@ -308,10 +308,8 @@ int fdb_kshap_prepare_lasso(fdb_kshap_plan* p, int scale);
 int fdb_kshap_refresh_lasso(fdb_kshap_plan* p, cudaStream_t st);
 void fdb_kshap_free_lasso(fdb_kshap_plan* p);
 int fdb_kshap_launch_lasso_solve(fdb_kshap_plan* p, cudaStream_t st, const float* x, int64_t row_offset, int n_rows,
-                                 const int32_t* set_idx, float* phi, double* abs_sum, int accumulate, int64_t total_rows);
-int fdb_kshap_launch_lars_solve(fdb_kshap_plan* p, cudaStream_t st, const float* x, int64_t row_offset, int n_rows,
-                                const int32_t* set_idx, float* phi, double* abs_sum, int accumulate, int64_t total_rows);
-
+                                 const int32_t* set_idx, float* phi, double* abs_sum, int accumulate, int64_t total_rows,
+                                 const float* gpart, int gslots, long long fx_units, int fx_grid);
 // on-device coalition sampler (kshap_sampler.cu)
 int fdb_kshap_resolve_nsamples(int nsamples);
 int fdb_kshap_sample_on_device(fdb_kshap_plan* pl, cudaStream_t stream, int nsamples, unsigned long long seed);

@@ -1,7 +1,8 @@
-// Kernel SHAP solve with shap's adaptive feature selection:  l1_reg = "aic" | "bic" | "auto" | <alpha>.
+// Kernel SHAP solve with shap's feature selections:  l1_reg = "num_features(k)" | "aic" | "bic" | "auto" | <alpha>.
 //
 // Reference (oracle/kernel_shap.py::solve, restating shap/explainers/_kernel.py::solve [recalled]):
 //   X_aug = sqrt(w_aug) * [Z; Z - 1],  y_aug = sqrt(w_aug) * [e; e - d],  w_aug = [kw (M - s); kw s]      (2 n_masks rows)
+//   "num_features(k)": sel = lars_path(X_aug, y_aug, max_iter=k)[1]      (method "lar"; shap's default, k = 10 [recalled])
 //   "aic" / "bic":  sel = nonzero(make_pipeline(StandardScaler(with_mean=False), LassoLarsIC(criterion)).fit(X_aug, y_aug).coef_)
 //   alpha        :  sel = nonzero(Lasso(alpha).fit(X_aug, y_aug).coef_)
 //   "auto"       :  "aic" when nsamples / (2^M - 2) < 0.2, no selection otherwise (decided by the caller)
@@ -75,7 +76,8 @@ struct LassoScratch {
     uint32_t nz[kMaxPath + 1];
 };
 
-// Per coalition set: centred (scale != 0: unit-variance) Gram of the augmented matrix, its inverse, column sums, 1 / sd.
+// Per coalition set: Gram of the augmented matrix - scale 1: centred, unit-variance columns (criteria); 0: centred (alpha);
+// 2: raw (num_features: lars_path gets the matrix as it is) - its inverse (not for 2), column sums, 1 / sd.
 __global__ void __launch_bounds__(32) kshap_lasso_prepare(const uint32_t* __restrict__ bits, const float* __restrict__ kw,
                                                           int m_pad, const double* __restrict__ gz, const double* __restrict__ bv,
                                                           const double* __restrict__ s0, double* __restrict__ lg,
@@ -93,12 +95,13 @@ __global__ void __launch_bounds__(32) kshap_lasso_prepare(const uint32_t* __rest
     for (int m = lane; m < m_pad; m += 32) {
         const double w = (double)sk[m];
         if (!(w > 0.0)) continue;
+        cnt += 1.0;
+        if (scale == 2) continue;
         const uint32_t b = sb[m] & varying;
         const double sc = (double)__popc(b);
         const double q = sqrt(w * sc);
         const double r = sqrt(w * (Mf - sc)) + q;
         qacc += q;
-        cnt += 1.0;
 #pragma unroll
         for (int j = 0; j < FDB_F; ++j) g[j] += ((b >> j) & 1u) ? r : 0.0;
     }
@@ -108,12 +111,12 @@ __global__ void __launch_bounds__(32) kshap_lasso_prepare(const uint32_t* __rest
     const double* G0 = gz + (size_t)s * FDB_F * 32;
     const double Bj = bv[(size_t)s * 32 + lane];
     const double S0 = s0[s];
-    const double c = is_var ? g[0] - Q : 0.0;
+    const double c = (is_var && scale != 2) ? g[0] - Q : 0.0;                     // scale 2: raw Gram, nothing is centred
     const double mu = c / n;
     const double ajj = is_var ? Mf * G0[lane * 32 + lane] - 2.0 * Bj + S0 : 0.0;
     const double var = ajj / n - mu * mu;
     double isd = 1.0;
-    if (scale && is_var && var > 10.0 * DBL_EPSILON) isd = 1.0 / sqrt(var);       // StandardScaler: near-constant columns keep scale 1
+    if (scale == 1 && is_var && var > 10.0 * DBL_EPSILON) isd = 1.0 / sqrt(var);       // StandardScaler: near-constant columns keep scale 1
     // a[i] = G[i][lane]
     double a[FDB_F], inv[FDB_F];
 #pragma unroll
@@ -130,9 +133,10 @@ __global__ void __launch_bounds__(32) kshap_lasso_prepare(const uint32_t* __rest
         if (lane < FDB_F) lg[((size_t)s * FDB_F + i) * 32 + lane] = v;
     }
     // Gauss-Jordan without pivoting (G is symmetric positive definite for any set the WLS itself can use)
-    bool singular = false;
+    bool singular = scale == 2;                                                    // the LAR walk needs no inverse
 #pragma unroll
     for (int k = 0; k < FDB_F; ++k) {
+        if (singular) break;
         const double pk = shfl_d(a[k], k);
         if (!(fabs(pk) > 1e-300)) { singular = true; break; }
         const double r = 1.0 / pk;
@@ -206,9 +210,13 @@ struct RowProducts {
     double d;       // link(f(x)) - link(fnull)
 };
 
-// LARS-lasso walk on (G, X'y); records RSS and support of every path point in S.rss / S.nz; returns the point count - 1
+// LARS walk on (G, X'y).  LAR = false (method "lasso", to alpha = 0): a coefficient that reaches zero leaves the active set;
+// RSS and support of every path point are recorded in S.rss / S.nz; returns the point count - 1.  LAR = true (method
+// "lar", lars_path(max_iter)): a sign change only flips the stored sign and skips the next add; stops after max_iter
+// steps; returns the number of active features, S.act holds them in order of entry.
+template <bool LAR>
 __device__ int lasso_path(LassoScratch& S, const double* __restrict__ G, const RowProducts& R, double n_aug, bool is_var,
-                          int n_var, int lane) {
+                          int n_var, int lane, int max_iter) {
     const double eps = DBL_EPSILON, tiny32 = (double)FLT_MIN, eq_tol = (double)FLT_EPSILON;
     double Cov = is_var ? R.xy : 0.0;
     bool inactive = is_var;
@@ -218,7 +226,7 @@ __device__ int lasso_path(LassoScratch& S, const double* __restrict__ G, const R
     bool drop = false;
     double prev_alpha = DBL_MAX;
     double yv = 0.0;                         // lane a: (L^-1 sign)_a, extended by one entry per added feature
-    if (lane == 0) { S.rss[0] = R.yy; S.nz[0] = 0u; }
+    if (!LAR && lane == 0) { S.rss[0] = R.yy; S.nz[0] = 0u; }
     while (true) {
         double best = inactive ? fabs(Cov) : -1.0;
         int bidx = lane;
@@ -231,7 +239,7 @@ __device__ int lasso_path(LassoScratch& S, const double* __restrict__ G, const R
         const double C = best >= 0.0 ? best : 0.0;
         const double alpha = C / n_aug;
         if (alpha <= eq_tol) break;
-        if (n_iter >= kMaxPath || n_active >= n_var) break;
+        if (n_iter >= max_iter || n_active >= n_var) break;
         if (!drop) {
             // append feature bidx to the factorisation: L[n][:n] = L^-1 G[act, bidx], L[n][n] = sqrt(G_bb - |.|^2)
             const int n = n_active;
@@ -258,7 +266,7 @@ __device__ int lasso_path(LassoScratch& S, const double* __restrict__ G, const R
             ++n_active;
             __syncwarp();
         }
-        if (n_iter > 0 && prev_alpha < alpha) break;                 // alpha no longer decreasing: numerical end of the path
+        if (!LAR && n_iter > 0 && prev_alpha < alpha) break;         // alpha no longer decreasing: numerical end of the path
         // equiangular direction: (L L') ls = sign, scaled by AA = 1 / sqrt(ls . sign)
         const int n = n_active;
         const double sg = lane < n ? S.sgn[lane] : 0.0;
@@ -289,13 +297,22 @@ __device__ int lasso_path(LassoScratch& S, const double* __restrict__ G, const R
         bool leaving = false;
         if (z_pos < gamma) {
             leaving = my_a >= 0 && zz == z_pos;
-            gamma = z_pos;
+            if (!LAR) gamma = z_pos;
             drop = true;
         }
         ++n_iter;
         if (my_a >= 0) coef += gamma * my_ls;
         if (inactive) Cov -= gamma * corr;
         prev_alpha = alpha;
+        if (LAR) {
+            if (drop) {                                              // sign flip only; L^-1 sign has to follow it
+                if (leaving) S.sgn[my_a] = -S.sgn[my_a];
+                __syncwarp();
+                yv = trsv_lower(S, n, lane < n ? S.sgn[lane] : 0.0, lane, 0.0);
+            }
+            __syncwarp();
+            continue;
+        }
         // path point n_iter: q = G coef, RSS = y'y - 2 coef.X'y + coef.q, support = |coef| > eps
         double q = 0.0;
         for (int a = 0; a < n; ++a) {
@@ -326,7 +343,7 @@ __device__ int lasso_path(LassoScratch& S, const double* __restrict__ G, const R
         }
         __syncwarp();
     }
-    return n_iter;
+    return LAR ? n_active : n_iter;
 }
 
 // Lasso(alpha) support: cyclic coordinate descent on the Gram form from w = 0 with sklearn's stopping rule
@@ -367,7 +384,9 @@ __device__ uint32_t lasso_cd_support(const double* __restrict__ G, const RowProd
 
 struct Coef30 { double w[FDB_F]; };
 
-// MODE 0: information criterion (factor = 2 for AIC, log n for BIC, chosen by `bic`); MODE 1: Lasso(alpha)
+// MODE 0: information criterion (factor = 2 for AIC, log n for BIC, chosen by `bic`); MODE 1: Lasso(alpha);
+// MODE 2: num_features(kfeat), LAR walk on the raw Gram - it needs T only, which the factored evaluator's fused X'W y GEMM
+// has already left in `gpart` (column j < 29: T_j - T_29, column 29: T_29) when that evaluator ran: no pass over ey then.
 template <int MODE>
 __global__ void __launch_bounds__(128) kshap_lasso_solve(
     const float* __restrict__ x, int64_t row_offset, int n_rows, const int32_t* __restrict__ set_idx, int n_sets,
@@ -376,7 +395,8 @@ __global__ void __launch_bounds__(128) kshap_lasso_solve(
     const double* __restrict__ lg, const double* __restrict__ lginv, const double* __restrict__ lvec,
     const Coef30 wc, double intercept, double fnull, int link, int bic, double alpha_l1,
     float* __restrict__ phi, double* __restrict__ abs_sum, int accumulate, int64_t total_rows,
-    double* __restrict__ partials, unsigned int* __restrict__ ticket, uint32_t varying) {
+    double* __restrict__ partials, unsigned int* __restrict__ ticket, uint32_t varying, int kfeat,
+    const float* __restrict__ gpart, int gslots, long long fx_units, int fx_grid, int fx_tiles) {
     __shared__ LassoScratch scr[4];
     __shared__ float s_tab[32];                                   // sqrt(M - s) + sqrt(s) by coalition size
     const int lane = threadIdx.x & 31;
@@ -404,7 +424,16 @@ __global__ void __launch_bounds__(128) kshap_lasso_solve(
         const float* sk = kw + (size_t)s * m_pad;
         const float* er = ey + (size_t)r * m_pad;
         double e2 = 0.0, p1 = 0.0;
-        {
+        if (MODE == 2 && gpart != nullptr) {
+            // records of the CTAs that worked on this row's block of 128 rows, folded in CTA order (as K3 does)
+            const long long ub = (long long)(r >> 7) * fx_tiles;
+            const int nseg = (int)((((ub + fx_tiles) * fx_grid - 1) / fx_units) - (((ub + 1) * fx_grid - 1) / fx_units)) + 1;
+            const float* gp = gpart + (size_t)r * gslots * 32 + lane;
+            float g = 0.f;
+            for (int q = 0; q < nseg; ++q) g += gp[(size_t)q * 32];
+            const double t29 = shfl_d((double)g, FDB_F - 1);
+            R.T = !is_var ? 0.0 : (lane < FDB_F - 1 ? (double)g + t29 : t29);
+        } else {
             double gj[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) gj[j] = 0.0;
@@ -414,8 +443,10 @@ __global__ void __launch_bounds__(128) kshap_lasso_solve(
                 if (kwv != 0.f) {                                   // lanes diverge only on the padding of the last words
                     const double e = (double)fdb_kshap_link(er[m0 + lane], link) - lnull;
                     const double v = (double)kwv * e;
-                    e2 = fma(v, e, e2);
-                    p1 = fma((double)(sqrtf(kwv) * s_tab[__popc(b)]), e, p1);
+                    if (MODE != 2) {
+                        e2 = fma(v, e, e2);
+                        p1 = fma((double)(sqrtf(kwv) * s_tab[__popc(b)]), e, p1);
+                    }
 #pragma unroll
                     for (int j = 0; j < FDB_F; ++j) gj[j] += ((b >> j) & 1u) ? v : 0.0;
                 }
@@ -439,7 +470,7 @@ __global__ void __launch_bounds__(128) kshap_lasso_solve(
             double u = 0.0;
             for (int i = 0; i < FDB_F; ++i) u += (lane < FDB_F ? Gi[i * 32 + lane] : 0.0) * shfl_d(R.xy, i);
             const double sigma2 = (R.yy - warp_sum(R.xy * u)) / (n_aug - Mf - 1.0);
-            const int n_pts = lasso_path(S, G, R, n_aug, is_var, n_var, lane);
+            const int n_pts = lasso_path<false>(S, G, R, n_aug, is_var, n_var, lane, kMaxPath);
             __syncwarp();
             const double factor = bic ? log(n_aug) : 2.0;
             double best = DBL_MAX;
@@ -457,8 +488,14 @@ __global__ void __launch_bounds__(128) kshap_lasso_solve(
                 }
             }
             sel = S.nz[bk] & varying;
-        } else {
+        } else if (MODE == 1) {
             sel = lasso_cd_support(G, R, alpha_l1 * n_aug, is_var, lane) & varying;
+        } else {
+            const int n_act = lasso_path<true>(S, G, R, n_aug, is_var, n_var, lane, kfeat);
+            __syncwarp();
+            sel = 0u;
+            for (int a = 0; a < n_act; ++a) sel |= 1u << S.act[a];
+            sel &= varying;
         }
         __syncwarp();
 
@@ -550,7 +587,8 @@ static int launch_prepare(fdb_kshap_plan* p, cudaStream_t st) {
     return FDB_OK;
 }
 
-// scale = 1: unit-variance columns (the StandardScaler step in front of LassoLarsIC); 0: plain centring (Lasso(alpha))
+// scale = 1: unit-variance columns (the StandardScaler step in front of LassoLarsIC); 0: plain centring (Lasso(alpha));
+// 2: the raw Gram (num_features(k): lars_path on the augmented matrix as it is)
 int fdb_kshap_prepare_lasso(fdb_kshap_plan* p, int scale) {
     int rc = fdb_kshap_prepare_lars(p);                       // Z'WZ, B, S0
     if (rc != FDB_OK) return rc;
@@ -580,22 +618,29 @@ void fdb_kshap_free_lasso(fdb_kshap_plan* p) {
 }
 
 int fdb_kshap_launch_lasso_solve(fdb_kshap_plan* p, cudaStream_t st, const float* x, int64_t row_offset, int n_rows,
-                                 const int32_t* set_idx, float* phi, double* abs_sum, int accumulate, int64_t total_rows) {
+                                 const int32_t* set_idx, float* phi, double* abs_sum, int accumulate, int64_t total_rows,
+                                 const float* gpart, int gslots, long long fx_units, int fx_grid) {
     int grid = (n_rows + 3) / 4;
     const int cap = p->ctx->sm_count * 8;
     if (grid > cap) grid = cap;
     Coef30 wc;
     for (int j = 0; j < FDB_F; ++j) wc.w[j] = p->coef[j];
-    if (p->l1_mode == FDB_KSHAP_L1_ALPHA)
-        kshap_lasso_solve<1><<<grid, 128, 0, st>>>(x, row_offset, n_rows, set_idx, p->n_sets, p->d_bits, p->d_kw, p->m_pad, p->d_ey,
-                                                  p->d_gz, p->d_bv, p->d_s0, p->d_lg, p->d_lginv, p->d_lvec, wc, p->intercept,
-                                                  p->fnull, p->link, 0, p->l1_alpha, phi, abs_sum, accumulate, total_rows,
-                                                  p->d_partials, p->d_ticket, p->varying);
-    else
-        kshap_lasso_solve<0><<<grid, 128, 0, st>>>(x, row_offset, n_rows, set_idx, p->n_sets, p->d_bits, p->d_kw, p->m_pad, p->d_ey,
-                                                  p->d_gz, p->d_bv, p->d_s0, p->d_lg, p->d_lginv, p->d_lvec, wc, p->intercept,
-                                                  p->fnull, p->link, p->l1_mode == FDB_KSHAP_L1_BIC ? 1 : 0, 0.0, phi, abs_sum,
-                                                  accumulate, total_rows, p->d_partials, p->d_ticket, p->varying);
+    const int tiles = p->m_pad / 128;
+#define FDB_LASSO_ARGS(bic, alpha, kfeat, gp)                                                                                   \
+    x, row_offset, n_rows, set_idx, p->n_sets, p->d_bits, p->d_kw, p->m_pad, p->d_ey, p->d_gz, p->d_bv, p->d_s0, p->d_lg,       \
+        p->d_lginv, p->d_lvec, wc, p->intercept, p->fnull, p->link, bic, alpha, phi, abs_sum, accumulate, total_rows,           \
+        p->d_partials, p->d_ticket, p->varying, kfeat, gp, gslots, fx_units, fx_grid, tiles
+    if (p->l1_mode == FDB_KSHAP_L1_ALPHA) {
+        FDB_REQUIRE(p->lasso_scaled == 0, FDB_ERR_STATE, "selection products were prepared for another l1 mode");
+        kshap_lasso_solve<1><<<grid, 128, 0, st>>>(FDB_LASSO_ARGS(0, p->l1_alpha, 0, nullptr));
+    } else if (p->l1_mode == FDB_KSHAP_L1_NUM_FEATURES) {
+        FDB_REQUIRE(p->lasso_scaled == 2, FDB_ERR_STATE, "selection products were prepared for another l1 mode");
+        kshap_lasso_solve<2><<<grid, 128, 0, st>>>(FDB_LASSO_ARGS(0, 0.0, p->num_features, gpart));
+    } else {
+        FDB_REQUIRE(p->lasso_scaled == 1, FDB_ERR_STATE, "selection products were prepared for another l1 mode");
+        kshap_lasso_solve<0><<<grid, 128, 0, st>>>(FDB_LASSO_ARGS(p->l1_mode == FDB_KSHAP_L1_BIC ? 1 : 0, 0.0, 0, nullptr));
+    }
+#undef FDB_LASSO_ARGS
     FDB_CUDA(cudaGetLastError());
     return FDB_OK;
 }

@@ -243,3 +243,40 @@ def test_auto_on_rows_with_few_varying_features(params):
     assert agree >= len(X) - 2
     np.testing.assert_allclose(auto.sum(1) + expl.expected_value, f(X), atol=1e-5)
     np.testing.assert_allclose(aic.sum(1) + expl.expected_value, f(X), atol=1e-5)
+
+
+@pytest.mark.parametrize("link", ["identity", "logit"])
+def test_num_features_from_the_factored_evaluators_records(params, link):
+    """num_features(k) under the factored evaluator takes T = Z'W e from the records of the fused X'W y GEMM (no pass over
+    the expectations, no ey through HBM): same selected features and attributions as the pass over the exported ey, and
+    the oracle on that ey."""
+    bg, X, f = _setup(params, 100, 300, seed=55)
+    Z, kw, _ = ks.sample_coalitions(30, 2048, np.random.RandomState(55))
+    plan = _plan(params, bg, [(Z, kw)], link=link)
+    fnull = float(f(bg).mean())
+    lf = ks.LINKS[link]
+    for k in (3, 10):
+        plan.set_l1(L1_NUM_FEATURES, k)
+        phi_rec, _, abs_rec = _run(plan, X, FX, want_ey=False)       # records path
+        phi_ey, ey, abs_ey = _run(plan, X, FX, want_ey=True)         # expectations through HBM, float64 pass over them
+        same = [np.array_equal(a != 0, b != 0) for a, b in zip(phi_rec, phi_ey)]
+        assert sum(same) >= len(X) - 3, f"{len(X) - sum(same)} rows select differently from the records"
+        for a, b, ok in zip(phi_rec, phi_ey, same):
+            assert np.count_nonzero(a) <= k
+            if ok:
+                assert np.all(np.abs(a - b) <= 1e-4 * np.abs(b).max() + 1e-7)
+        np.testing.assert_allclose(phi_rec.sum(1) + lf(fnull), lf(f(_rows32(X))), atol=2e-4 if link == "logit" else 1e-5)
+        np.testing.assert_allclose(abs_rec[:30], np.abs(phi_rec).sum(0), rtol=1e-6, atol=1e-12)
+        agree = 0
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            for i, x in enumerate(_rows32(X)[:32]):
+                if link == "logit" and ey[i].max() > 0.99:
+                    agree += 1
+                    continue
+                ref = ks.solve(Z, kw, ey[i].astype(np.float64), float(f(x[None])[0]), fnull, link=link, l1_reg=f"num_features({k})")
+                if np.array_equal(ref != 0, phi_rec[i] != 0):
+                    agree += 1
+                    assert np.all(np.abs(phi_rec[i] - ref) <= 1e-4 * np.abs(ref).max() + 1e-7)
+        assert agree >= 31
+    plan.close()
