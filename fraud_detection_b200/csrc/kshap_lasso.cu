@@ -433,6 +433,30 @@ __global__ void __launch_bounds__(128) kshap_lasso_solve(
             for (int q = 0; q < nseg; ++q) g += gp[(size_t)q * 32];
             const double t29 = shfl_d((double)g, FDB_F - 1);
             R.T = !is_var ? 0.0 : (lane < FDB_F - 1 ? (double)g + t29 : t29);
+        } else if (MODE == 2) {
+            // num_features(k) needs T only; float32 sums (as K3's own X'W y pass), a third of the float64 pass's time
+            const float lnull_f = (float)lnull;
+            float gj[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) gj[j] = 0.f;
+            for (int m0 = 0; m0 < m_pad; m0 += 32) {
+                const uint32_t b = sb[m0 + lane] & varying;
+                const float kwv = sk[m0 + lane];
+                const float v = kwv != 0.f ? kwv * (fdb_kshap_link(er[m0 + lane], link) - lnull_f) : 0.f;
+#pragma unroll
+                for (int j = 0; j < FDB_F; ++j) gj[j] += ((b >> j) & 1u) ? v : 0.f;
+            }
+#pragma unroll
+            for (int half = 16; half >= 1; half >>= 1) {
+                const bool up = (lane & half) != 0;
+#pragma unroll
+                for (int i = 0; i < half; ++i) {
+                    const float send = up ? gj[i] : gj[i + half];
+                    const float keep = up ? gj[i + half] : gj[i];
+                    gj[i] = keep + __shfl_xor_sync(0xffffffffu, send, half);
+                }
+            }
+            R.T = is_var ? (double)gj[0] : 0.0;
         } else {
             double gj[32];
 #pragma unroll
@@ -443,10 +467,8 @@ __global__ void __launch_bounds__(128) kshap_lasso_solve(
                 if (kwv != 0.f) {                                   // lanes diverge only on the padding of the last words
                     const double e = (double)fdb_kshap_link(er[m0 + lane], link) - lnull;
                     const double v = (double)kwv * e;
-                    if (MODE != 2) {
-                        e2 = fma(v, e, e2);
-                        p1 = fma((double)(sqrtf(kwv) * s_tab[__popc(b)]), e, p1);
-                    }
+                    e2 = fma(v, e, e2);
+                    p1 = fma((double)(sqrtf(kwv) * s_tab[__popc(b)]), e, p1);
 #pragma unroll
                     for (int j = 0; j < FDB_F; ++j) gj[j] += ((b >> j) & 1u) ? v : 0.0;
                 }

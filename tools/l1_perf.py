@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Time per 100,000 explained rows of every l1_reg mode of the Kernel SHAP solve (shared coalition set, config-3 shape):
-none | num_features(10) | aic | bic | alpha.     python tools/l1_perf.py [rows] [modes...]"""
+none | num_features(10) | aic | bic | alpha.     python tools/l1_perf.py [rows] [tc] [modes...]"""
 import os
 import sys
 import time
@@ -13,7 +13,8 @@ from fraud_detection_b200 import KernelShapPlan, sampler  # noqa: E402
 from oracle import scoring, synth  # noqa: E402
 
 rows = int(sys.argv[1]) if len(sys.argv) > 1 else 100_000
-want = set(sys.argv[2:])
+want = set(a for a in sys.argv[2:] if a != "tc")
+evaluator = 0 if "tc" in sys.argv[2:] else -1          # "tc": the general tcgen05 evaluator (expectations through HBM)
 prm = scoring.load_params()
 bg = scoring.transform(prm, synth.rows(100, seed=43))
 X = torch.from_numpy(scoring.transform(prm, synth.rows(rows, seed=7)).astype(np.float32)).cuda()
@@ -27,7 +28,7 @@ for mode, par, name in ((0, 0, "none"), (1, 10, "num_features(10)"), (2, 0, "aic
     for rep in range(4):
         torch.cuda.synchronize()
         t = time.perf_counter()
-        phi = plan.explain_dev(X)
+        phi = plan.explain_dev(X, evaluator=evaluator)
         torch.cuda.synchronize()
         best = min(best, time.perf_counter() - t)
     print(f"{name:18s} {best * 1e3:8.2f} ms per {rows} rows   {rows / best / 1e6:7.2f} M rows/s   "
