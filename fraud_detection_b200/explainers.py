@@ -425,7 +425,8 @@ class B200KernelExplainer:
     squares is solved per row (K3).  ``mask_mode="shared"`` draws ONE coalition set for all rows
     - a different sampler from the reference, meant for throughput runs (SURVEY.md section 7);
     single-set plans use the factored evaluator (K2f: one exponential per (row, coalition)).
-    ``masks=(Z, kw)`` or a list of per-row pairs feeds exported reference masks instead.
+    ``masks=(Z, kw)`` or a list of per-row pairs feeds exported reference masks instead (for rows where fewer than
+    30 features vary: one pair per input row, Z over that row's varying features, as shap's ``maskMatrix`` is).
     ``sampler="device"`` draws the coalition sets on the GPU (same schedule, Philox stream: statistically but
     not bitwise equivalent to shap; ~5 orders of magnitude faster than the Python sampler).
     ``l1_reg`` defaults to ``"num_features(10)"`` like the pinned shap release [recalled]: LARS feature selection on
@@ -510,11 +511,23 @@ class B200KernelExplainer:
             out[r, np.nonzero(varying[r])[0][0]] = lf(fx) - lf(self.fnull)
         rows = np.nonzero(nvar == N_FEATURES)[0]
         part = np.nonzero((nvar >= 2) & (nvar < N_FEATURES))[0]
-        if masks is not None and len(part):
-            raise NotImplementedError("exported masks are taken for rows where all 30 features vary; rows with fewer "
-                                      "varying features draw their coalitions with the library's sampler")
         # Host-drawn coalition sets, taken in ROW order: the reference consumes one np.random stream row by row.
         host_sets: dict = {}
+        if masks is not None and len(part):
+            # exported masks for rows where fewer than 30 features vary: shap's maskMatrix has one column per VARYING
+            # feature of that row, so the sets cannot be shared between rows - one (Z, kw) pair per input row
+            if not isinstance(masks, list) or len(masks) != A.shape[0]:
+                raise ValueError("rows with fewer than 30 varying features need masks as a list with one (Z, kw) pair per "
+                                 "input row, Z over that row's varying features (shap's maskMatrix)")
+            for r in part:
+                Z, w = masks[int(r)]
+                Z = np.asarray(Z)
+                if Z.ndim != 2 or Z.shape[1] != nvar[r] or len(w) != Z.shape[0]:
+                    raise ValueError(f"row {int(r)} has {int(nvar[r])} varying features; its mask matrix must be (n, {int(nvar[r])})")
+                host_sets[int(r)] = (_sampler.masks_to_bits(Z), np.asarray(w, dtype=np.float64))
+            masks = [masks[int(r)] for r in rows]
+        elif isinstance(masks, list) and len(masks) == A.shape[0] != len(rows):
+            masks = [masks[int(r)] for r in rows]          # one pair per INPUT row: rows with M <= 1 need none
         if masks is None and mask_mode == "per_row":
             draw = part if sampler == "device" else np.nonzero(nvar >= 2)[0]
             for r in draw:
@@ -527,8 +540,8 @@ class B200KernelExplainer:
             return self._shared_cache[key]
 
         if len(part):
-            self._explain_partial(A, varying, part, host_sets if mask_mode == "per_row" else None, shared_set,
-                                  l1, nsamples, evaluator, out)
+            self._explain_partial(A, varying, part, host_sets if (mask_mode == "per_row" or masks is not None) else None,
+                                  shared_set, l1, nsamples, evaluator, out)
         if len(rows) == 0:
             return out[0] if single else out
         Xr = np.ascontiguousarray(A[rows], dtype=np.float32)

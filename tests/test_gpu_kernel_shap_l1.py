@@ -280,3 +280,36 @@ def test_num_features_from_the_factored_evaluators_records(params, link):
                     assert np.all(np.abs(phi_rec[i] - ref) <= 1e-4 * np.abs(ref).max() + 1e-7)
         assert agree >= 31
     plan.close()
+
+
+def test_exported_masks_for_rows_with_few_varying_features(params):
+    """masks= as a shap run exports them (maskMatrix has one column per VARYING feature of the row): one pair per input row."""
+    from fraud_detection_b200 import B200KernelExplainer
+    from test_gpu_kernel_shap import _partially_varying_case
+    bg, X, f = _partially_varying_case(params, 6, seed=32)
+    expl = B200KernelExplainer((params.coef, params.intercept), bg)
+    rs = np.random.RandomState(5)
+    pairs = []
+    for x in X:
+        m = len(ks.varying_features(x, bg))
+        pairs.append(ks.sample_coalitions(m, 700, rs)[:2] if m >= 2 else None)
+    for l1 in (False, "num_features(3)"):
+        phi = expl.shap_values(X, l1_reg=l1, masks=pairs)
+        ref = np.zeros_like(phi)
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            for r, x in enumerate(X):
+                ref[r] = ks.explain_row(f, x, bg, l1_reg=l1, masks=pairs[r])
+        agree = 0
+        for r in range(len(X)):
+            if np.array_equal(phi[r] != 0, ref[r] != 0):
+                agree += 1
+                assert np.all(np.abs(phi[r] - ref[r]) <= 1e-4 * max(np.abs(ref[r]).max(), 1e-12) + 1e-7), (l1, r)
+        assert agree >= (len(X) if l1 is False else len(X) - 1)
+        np.testing.assert_allclose(phi.sum(1) + expl.expected_value, f(X), atol=1e-5)
+    with pytest.raises(ValueError):
+        expl.shap_values(X, l1_reg=False, masks=pairs[5])          # one shared pair cannot serve rows of different M
+    with pytest.raises(ValueError):
+        bad = list(pairs)
+        bad[0] = pairs[5]
+        expl.shap_values(X, l1_reg=False, masks=bad)
