@@ -313,3 +313,38 @@ def test_exported_masks_for_rows_with_few_varying_features(params):
         bad = list(pairs)
         bad[0] = pairs[5]
         expl.shap_values(X, l1_reg=False, masks=bad)
+
+
+@pytest.mark.parametrize("l1", ["bic", "num_features(5)"])
+def test_row_stream_redraws_keep_the_selection_products_fresh(params, l1):
+    """KernelShapStream(l1_reg=...): the stream-ordered redraw of a plan's sets must also rebuild the per-set products
+    the selection reads.  After three batches (plan 0 has been redrawn once on its stream) the sets of plan 0 are
+    exported and the oracle, fed the expectations of a second pass over the same sets, must select the same features as
+    the stream call did."""
+    from fraud_detection_b200 import KernelShapStream, sampler
+    bg, X, f = _setup(params, 50, 8, seed=9)
+    fnull = float(f(bg).mean())
+    X32 = _rows32(X)
+    x = torch.from_numpy(np.ascontiguousarray(X, dtype=np.float32)).cuda()
+    stream = KernelShapStream(params.coef, params.intercept, bg, batch_rows=8, nsamples=512, seed=21, l1_reg=l1)
+    out = [stream.explain(x) for _ in range(3)]             # each call returns its own tensor, valid after synchronize()
+    stream.synchronize()
+    torch.cuda.synchronize()
+    phi3 = out[2].cpu().numpy().astype(np.float64)
+    plan = stream.plans[0]                                  # served batches 0 and 2; its sets now are those of batch 2
+    phi_again, ey, _ = _run(plan, X, TC)
+    np.testing.assert_array_equal(phi_again, phi3)
+    assert not np.array_equal(out[0].cpu().numpy(), out[2].cpu().numpy())       # the redraw did change the sets
+    same = 0
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        for i, xr in enumerate(X32):
+            bits, kw = plan.masks(i)
+            keep = kw > 0
+            Z = sampler.bits_to_masks(bits[keep]).astype(np.float64)
+            ref = ks.solve(Z, kw[keep].astype(np.float64), ey[i][keep].astype(np.float64), float(f(xr[None])[0]), fnull, l1_reg=l1)
+            if np.array_equal(ref != 0, phi3[i] != 0):
+                same += 1
+                assert np.all(np.abs(phi3[i] - ref) <= 1e-4 * np.abs(ref).max() + 1e-7)
+    assert same >= len(X) - 1
+    stream.close()
