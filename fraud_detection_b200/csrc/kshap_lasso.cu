@@ -30,6 +30,7 @@
 
 namespace {
 
+constexpr int kMaxSel = 16;           // num_features(k): k <= 16
 constexpr int kMaxPath = 96;          // path points kept per row (sklearn: max_iter = 500; 30 features need ~31 + drops)
 constexpr int kVecStride = 96;        // per set: [0..31] column sums c_j, [32..63] 1 / sd_j, [64] Q, [65] n
 
@@ -51,6 +52,23 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 __device__ __forceinline__ double min_pos(double v) { return v > 0.0 ? v : DBL_MAX; }
+// Non-negative doubles order like their bit patterns: the minimum / maximum over the warp takes two integer REDUX
+// instructions (high words, then low words among the lanes that hold the extreme high word) instead of a ten-shuffle
+// butterfly, and it returns one lane's value bit for bit (the callers compare for equality afterwards).
+__device__ __forceinline__ double warp_min_nonneg(double v) {
+    const unsigned hi = (unsigned)__double2hiint(v), lo = (unsigned)__double2loint(v);
+    const unsigned mh = __reduce_min_sync(0xffffffffu, hi);
+    const unsigned ml = __reduce_min_sync(0xffffffffu, hi == mh ? lo : 0xffffffffu);
+    return __hiloint2double((int)mh, (int)ml);
+}
+// maximum of non-negative doubles and the lowest lane that holds it
+__device__ __forceinline__ double warp_argmax_nonneg(double v, int& who) {
+    const unsigned hi = (unsigned)__double2hiint(v), lo = (unsigned)__double2loint(v);
+    const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
+    const unsigned ml = __reduce_max_sync(0xffffffffu, hi == mh ? lo : 0u);
+    who = __ffs(__ballot_sync(0xffffffffu, hi == mh && lo == ml)) - 1;
+    return __hiloint2double((int)mh, (int)ml);
+}
 
 // lanes own coalitions and hold 32 per-feature partial sums each; afterwards lane j holds the total of feature j in v[0]
 __device__ __forceinline__ void transpose_reduce(double (&v)[32], int lane) {
@@ -66,14 +84,16 @@ __device__ __forceinline__ void transpose_reduce(double (&v)[32], int lane) {
     }
 }
 
-struct LassoScratch {
-    double L[FDB_F][FDB_F + 1];       // Cholesky factor of the active Gram block; afterwards the reduced WLS system [A | rhs]
-    double ls[FDB_F];                 // equiangular direction, by active position; afterwards the WLS solution
-    double sgn[FDB_F];
-    double dinv[FDB_F];               // 1 / L[a][a]
-    int act[FDB_F];
-    double rss[kMaxPath + 1];
-    uint32_t nz[kMaxPath + 1];
+// NMAX: most features ever active (30; num_features(k) stops at kMaxSel = 16); NPATH: path points recorded (criteria only)
+template <int NMAX, int NPATH>
+struct LassoScratchT {
+    double L[NMAX][NMAX + 1];         // Cholesky factor of the active Gram block; afterwards the reduced WLS system [A | rhs]
+    double ls[NMAX];                  // equiangular direction, by active position; afterwards the WLS solution
+    double sgn[NMAX];
+    double dinv[NMAX];                // 1 / L[a][a]
+    int act[NMAX];
+    double rss[NPATH + 1];
+    uint32_t nz[NPATH + 1];
 };
 
 // Per coalition set: Gram of the augmented matrix - scale 1: centred, unit-variance columns (criteria); 0: centred (alpha);
@@ -166,7 +186,8 @@ __global__ void __launch_bounds__(32) kshap_lasso_prepare(const uint32_t* __rest
 
 // forward substitution  L w = t  (t: lane i holds t_i); returns w_i in lane i.  `doff` (the ill-conditioned retry of
 // sklearn: L.diag += 2^i eps) is added to the diagonal; the regular case multiplies by the stored reciprocals.
-__device__ __forceinline__ double trsv_lower(const LassoScratch& S, int n, double t, int lane, double doff) {
+template <class SC>
+__device__ __forceinline__ double trsv_lower(const SC& S, int n, double t, int lane, double doff) {
     double w = 0.0;
     for (int a = 0; a < n; ++a) {
         const double ta = shfl_d(t, a);
@@ -177,7 +198,8 @@ __device__ __forceinline__ double trsv_lower(const LassoScratch& S, int n, doubl
     return w;
 }
 // backward substitution  L' x = t
-__device__ __forceinline__ double trsv_lower_t(const LassoScratch& S, int n, double t, int lane, double doff) {
+template <class SC>
+__device__ __forceinline__ double trsv_lower_t(const SC& S, int n, double t, int lane, double doff) {
     double x = 0.0;
     for (int a = n - 1; a >= 0; --a) {
         const double ta = shfl_d(t, a);
@@ -188,7 +210,8 @@ __device__ __forceinline__ double trsv_lower_t(const LassoScratch& S, int n, dou
     return x;
 }
 // Cholesky factor of G[act, act] from scratch (after a drop): lane i owns row i
-__device__ __forceinline__ void chol_rebuild(LassoScratch& S, int n, const double* __restrict__ G, int lane) {
+template <class SC>
+__device__ __forceinline__ void chol_rebuild(SC& S, int n, const double* __restrict__ G, int lane) {
     const int fi = lane < n ? S.act[lane] : 0;
     for (int k = 0; k < n; ++k) {
         double sv = 0.0;
@@ -214,8 +237,8 @@ struct RowProducts {
 // RSS and support of every path point are recorded in S.rss / S.nz; returns the point count - 1.  LAR = true (method
 // "lar", lars_path(max_iter)): a sign change only flips the stored sign and skips the next add; stops after max_iter
 // steps; returns the number of active features, S.act holds them in order of entry.
-template <bool LAR>
-__device__ int lasso_path(LassoScratch& S, const double* __restrict__ G, const RowProducts& R, double n_aug, bool is_var,
+template <bool LAR, class SC>
+__device__ int lasso_path(SC& S, const double* __restrict__ G, const RowProducts& R, double n_aug, bool is_var,
                           int n_var, int lane, int max_iter) {
     const double eps = DBL_EPSILON, tiny32 = (double)FLT_MIN, eq_tol = (double)FLT_EPSILON;
     double Cov = is_var ? R.xy : 0.0;
@@ -228,17 +251,9 @@ __device__ int lasso_path(LassoScratch& S, const double* __restrict__ G, const R
     double yv = 0.0;                         // lane a: (L^-1 sign)_a, extended by one entry per added feature
     if (!LAR && lane == 0) { S.rss[0] = R.yy; S.nz[0] = 0u; }
     while (true) {
-        double best = inactive ? fabs(Cov) : -1.0;
-        int bidx = lane;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const double ob = shfl_xor_d(best, o);
-            const int oi = __shfl_xor_sync(0xffffffffu, bidx, o);
-            if (ob > best || (ob == best && oi < bidx)) { best = ob; bidx = oi; }
-        }
-        const double C = best >= 0.0 ? best : 0.0;
-        const double alpha = C / n_aug;
-        if (alpha <= eq_tol) break;
+        int bidx;
+        const double C = warp_argmax_nonneg(inactive ? fabs(Cov) : 0.0, bidx);      // ties: the lowest feature index
+        if (C <= eq_tol * n_aug) break;                                  // alpha = C / n <= alpha_min + tolerance
         if (n_iter >= max_iter || n_active >= n_var) break;
         if (!drop) {
             // append feature bidx to the factorisation: L[n][:n] = L^-1 G[act, bidx], L[n][n] = sqrt(G_bb - |.|^2)
@@ -254,11 +269,12 @@ __device__ int lasso_path(LassoScratch& S, const double* __restrict__ G, const R
             if (lane < n) S.L[n][lane] = w;
             const double csig = shfl_d(Cov, bidx);
             const double sg_n = csig > 0.0 ? 1.0 : (csig < 0.0 ? -1.0 : 0.0);
-            const double y_n = (sg_n - warp_sum(lane < n ? w * yv : 0.0)) / diag;
+            const double dinv = 1.0 / diag;
+            const double y_n = (sg_n - warp_sum(lane < n ? w * yv : 0.0)) * dinv;
             if (lane == n) yv = y_n;
             if (lane == 0) {
                 S.L[n][n] = diag;
-                S.dinv[n] = 1.0 / diag;
+                S.dinv[n] = dinv;
                 S.act[n] = bidx;
                 S.sgn[n] = sg_n;
             }
@@ -266,7 +282,7 @@ __device__ int lasso_path(LassoScratch& S, const double* __restrict__ G, const R
             ++n_active;
             __syncwarp();
         }
-        if (!LAR && n_iter > 0 && prev_alpha < alpha) break;         // alpha no longer decreasing: numerical end of the path
+        if (!LAR && n_iter > 0 && prev_alpha < C) break;             // alpha (= C / n) no longer decreasing: numerical end of the path
         // equiangular direction: (L L') ls = sign, scaled by AA = 1 / sqrt(ls . sign)
         const int n = n_active;
         const double sg = lane < n ? S.sgn[lane] : 0.0;
@@ -287,12 +303,11 @@ __device__ int lasso_path(LassoScratch& S, const double* __restrict__ G, const R
             for (int a = 0; a < n; ++a) corr += G[S.act[a] * 32 + lane] * S.ls[a];
             corr = rint(corr * 1e15) / 1e15;                         // np.around(..., decimals=15)
         }
-        const double g1 = warp_min(inactive ? min_pos((C - Cov) / (AA - corr + tiny32)) : DBL_MAX);
-        const double g2 = warp_min(inactive ? min_pos((C + Cov) / (AA + corr + tiny32)) : DBL_MAX);
-        double gamma = fmin(fmin(g1, g2), C / AA);
+        const double g12 = inactive ? fmin(min_pos((C - Cov) / (AA - corr + tiny32)), min_pos((C + Cov) / (AA + corr + tiny32))) : DBL_MAX;
+        double gamma = fmin(warp_min_nonneg(g12), C / AA);
         const double my_ls = my_a >= 0 ? S.ls[my_a] : 0.0;
         const double zz = my_a >= 0 ? min_pos(-coef / (my_ls + tiny32)) : DBL_MAX;
-        const double z_pos = warp_min(zz);
+        const double z_pos = warp_min_nonneg(zz);
         drop = false;
         bool leaving = false;
         if (z_pos < gamma) {
@@ -303,7 +318,7 @@ __device__ int lasso_path(LassoScratch& S, const double* __restrict__ G, const R
         ++n_iter;
         if (my_a >= 0) coef += gamma * my_ls;
         if (inactive) Cov -= gamma * corr;
-        prev_alpha = alpha;
+        prev_alpha = C;
         if (LAR) {
             if (drop) {                                              // sign flip only; L^-1 sign has to follow it
                 if (leaving) S.sgn[my_a] = -S.sgn[my_a];
@@ -397,7 +412,8 @@ __global__ void __launch_bounds__(128) kshap_lasso_solve(
     float* __restrict__ phi, double* __restrict__ abs_sum, int accumulate, int64_t total_rows,
     double* __restrict__ partials, unsigned int* __restrict__ ticket, uint32_t varying, int kfeat,
     const float* __restrict__ gpart, int gslots, long long fx_units, int fx_grid, int fx_tiles) {
-    __shared__ LassoScratch scr[4];
+    using Scratch = LassoScratchT<MODE == 2 ? kMaxSel : FDB_F, MODE == 0 ? kMaxPath : 0>;
+    __shared__ Scratch scr[4];
     __shared__ float s_tab[32];                                   // sqrt(M - s) + sqrt(s) by coalition size
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -406,7 +422,7 @@ __global__ void __launch_bounds__(128) kshap_lasso_solve(
     const double Mf = (double)n_var;
     if (threadIdx.x < 32) s_tab[lane] = lane <= n_var ? (float)(sqrt(Mf - (double)lane) + sqrt((double)lane)) : 0.f;
     __syncthreads();
-    LassoScratch& S = scr[warp];
+    Scratch& S = scr[warp];
     const double lnull = link == 1 ? log(fnull / (1.0 - fnull)) : fnull;
     double wk = 0.0;
 #pragma unroll
