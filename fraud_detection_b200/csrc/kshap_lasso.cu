@@ -182,50 +182,6 @@ __global__ void __launch_bounds__(32) kshap_lasso_prepare(const uint32_t* __rest
     V[64 + lane] = lane == 0 ? Q : (lane == 1 ? n : 0.0);
 }
 
-// ---- warp-parallel dense pieces over the n x n lower-triangular factor in shared memory (lane i = row / position i)
-
-// forward substitution  L w = t  (t: lane i holds t_i); returns w_i in lane i.  `doff` (the ill-conditioned retry of
-// sklearn: L.diag += 2^i eps) is added to the diagonal; the regular case multiplies by the stored reciprocals.
-template <class SC>
-__device__ __forceinline__ double trsv_lower(const SC& S, int n, double t, int lane, double doff) {
-    double w = 0.0;
-    for (int a = 0; a < n; ++a) {
-        const double ta = shfl_d(t, a);
-        const double wa = doff == 0.0 ? ta * S.dinv[a] : ta / (S.L[a][a] + doff);
-        if (lane == a) w = wa;
-        if (lane > a && lane < n) t -= S.L[lane][a] * wa;
-    }
-    return w;
-}
-// backward substitution  L' x = t
-template <class SC>
-__device__ __forceinline__ double trsv_lower_t(const SC& S, int n, double t, int lane, double doff) {
-    double x = 0.0;
-    for (int a = n - 1; a >= 0; --a) {
-        const double ta = shfl_d(t, a);
-        const double xa = doff == 0.0 ? ta * S.dinv[a] : ta / (S.L[a][a] + doff);
-        if (lane == a) x = xa;
-        if (lane < a) t -= S.L[a][lane] * xa;
-    }
-    return x;
-}
-// Cholesky factor of G[act, act] from scratch (after a drop): lane i owns row i
-template <class SC>
-__device__ __forceinline__ void chol_rebuild(SC& S, int n, const double* __restrict__ G, int lane) {
-    const int fi = lane < n ? S.act[lane] : 0;
-    for (int k = 0; k < n; ++k) {
-        double sv = 0.0;
-        if (lane >= k && lane < n) {
-            sv = G[S.act[k] * 32 + fi];
-            for (int b = 0; b < k; ++b) sv -= S.L[lane][b] * S.L[k][b];
-        }
-        const double dk = fmax(sqrt(fabs(shfl_d(sv, k))), DBL_EPSILON);
-        if (lane == k) { S.L[k][k] = dk; S.dinv[k] = 1.0 / dk; }
-        else if (lane > k && lane < n) S.L[lane][k] = sv / dk;
-        __syncwarp();
-    }
-}
-
 struct RowProducts {
     double xy;      // lane j: centred (scaled) X'y of feature j, 0 outside `varying`
     double yy;      // centred y'y
@@ -236,7 +192,17 @@ struct RowProducts {
 // LARS walk on (G, X'y).  LAR = false (method "lasso", to alpha = 0): a coefficient that reaches zero leaves the active set;
 // RSS and support of every path point are recorded in S.rss / S.nz; returns the point count - 1.  LAR = true (method
 // "lar", lars_path(max_iter)): a sign change only flips the stored sign and skips the next add; stops after max_iter
-// steps; returns the number of active features, S.act holds them in order of entry.
+// steps; returns the number of active features (S.act).
+//
+// sklearn keeps the Cholesky factor of the active Gram block and solves two triangular systems per path point - 2n
+// dependent steps for one warp.  Here the INVERSE of the active block lives in S.L (lane i = row of active position i):
+//   add feature b:  g = G[act, b],  u = Ainv g,  s = G_bb - g.u  (sqrt|s| is sklearn's new Cholesky pivot, same 1e-7
+//                   degeneracy test),  Ainv <- [[Ainv + u u'/s, -u/s], [-u'/s, 1/s]]
+//                   and the unnormalised direction Ainv.sign follows without a solve:  ls0 <- [ls0 + u t, -t],
+//                   t = (u.sign - sign_b) / s
+//   drop position k: Ainv <- Ainv - c c'/Ainv_kk without row / column k (c = column k); the last position moves into k
+// - every step is a lane-parallel sweep over one row, nothing is sequential across lanes.  tests/lasso_gram_model.py
+// walks sklearn's factor, tools-side checks of this form against lars_path are in tests/test_lasso_gram_cpu.py.
 template <bool LAR, class SC>
 __device__ int lasso_path(SC& S, const double* __restrict__ G, const RowProducts& R, double n_aug, bool is_var,
                           int n_var, int lane, int max_iter) {
@@ -247,61 +213,78 @@ __device__ int lasso_path(SC& S, const double* __restrict__ G, const RowProducts
     int my_a = -1;                           // position of this lane's feature in the active list
     int n_active = 0, n_iter = 0;
     bool drop = false;
-    double prev_alpha = DBL_MAX;
-    double yv = 0.0;                         // lane a: (L^-1 sign)_a, extended by one entry per added feature
+    double prev_C = DBL_MAX;
+    double ls0 = 0.0, sgv = 0.0;             // lane a: (Ainv sign)_a and sign_a of active position a
     if (!LAR && lane == 0) { S.rss[0] = R.yy; S.nz[0] = 0u; }
+    // ls0 = Ainv sign from scratch (after a drop or a sign flip)
+    auto direction_from_scratch = [&](int n) {
+        double v = 0.0;
+        if (lane < n)
+            for (int a = 0; a < n; ++a) v += S.L[lane][a] * S.sgn[a];
+        ls0 = v;
+    };
     while (true) {
         int bidx;
         const double C = warp_argmax_nonneg(inactive ? fabs(Cov) : 0.0, bidx);      // ties: the lowest feature index
         if (C <= eq_tol * n_aug) break;                                  // alpha = C / n <= alpha_min + tolerance
         if (n_iter >= max_iter || n_active >= n_var) break;
         if (!drop) {
-            // append feature bidx to the factorisation: L[n][:n] = L^-1 G[act, bidx], L[n][n] = sqrt(G_bb - |.|^2)
             const int n = n_active;
-            const double t = lane < n ? G[bidx * 32 + S.act[lane]] : 0.0;
-            const double w = trsv_lower(S, n, t, lane, 0.0);
-            const double v = warp_sum(lane < n ? w * w : 0.0);
-            const double diag = fmax(sqrt(fabs(G[bidx * 32 + bidx] - v)), eps);
-            if (diag < 1e-7) {                                       // sklearn: degenerate regressor, zero its Cov and go on
+            const double g = lane < n ? G[bidx * 32 + S.act[lane]] : 0.0;
+            if (lane < n) S.dinv[lane] = g;                              // dinv[] / ls[] double as broadcast buffers here
+            __syncwarp();
+            double u = 0.0;
+            if (lane < n)
+                for (int a = 0; a < n; ++a) u += S.L[lane][a] * S.dinv[a];
+            const double sres = G[bidx * 32 + bidx] - warp_sum(g * u);
+            const double diag = fmax(sqrt(fabs(sres)), eps);
+            if (diag < 1e-7) {                                           // sklearn: degenerate regressor, zero its Cov and go on
                 if (lane == bidx) Cov = 0.0;
+                __syncwarp();
                 continue;
             }
-            if (lane < n) S.L[n][lane] = w;
+            const double sinv = 1.0 / (diag * diag);
             const double csig = shfl_d(Cov, bidx);
             const double sg_n = csig > 0.0 ? 1.0 : (csig < 0.0 ? -1.0 : 0.0);
-            const double dinv = 1.0 / diag;
-            const double y_n = (sg_n - warp_sum(lane < n ? w * yv : 0.0)) * dinv;
-            if (lane == n) yv = y_n;
-            if (lane == 0) {
-                S.L[n][n] = diag;
-                S.dinv[n] = dinv;
+            const double t = (warp_sum(u * sgv) - sg_n) * sinv;
+            if (lane < n) S.ls[lane] = u;
+            __syncwarp();
+            if (lane < n) {
+                const double us = u * sinv;
+                for (int a = 0; a < n; ++a) S.L[lane][a] += us * S.ls[a];
+                S.L[lane][n] = -us;
+                S.L[n][lane] = -us;
+                ls0 += u * t;
+            } else if (lane == n) {
+                S.L[n][n] = sinv;
                 S.act[n] = bidx;
                 S.sgn[n] = sg_n;
+                ls0 = -t;
+                sgv = sg_n;
             }
             if (lane == bidx) { inactive = false; coef = 0.0; my_a = n; }
             ++n_active;
             __syncwarp();
         }
-        if (!LAR && n_iter > 0 && prev_alpha < C) break;             // alpha (= C / n) no longer decreasing: numerical end of the path
-        // equiangular direction: (L L') ls = sign, scaled by AA = 1 / sqrt(ls . sign)
+        if (!LAR && n_iter > 0 && prev_C < C) break;                     // alpha (= C / n) no longer decreasing: numerical end of the path
+        // equiangular direction ls = AA Ainv sign, AA = 1 / sqrt(sign . Ainv sign)
         const int n = n_active;
-        const double sg = lane < n ? S.sgn[lane] : 0.0;
-        double lsv = 0.0, AA = 0.0, doff = 0.0;
-        for (int attempt = 0;; ++attempt) {
-            lsv = trsv_lower_t(S, n, attempt == 0 ? yv : trsv_lower(S, n, sg, lane, doff), lane, doff);
-            if (attempt == 0 && n == 1 && shfl_d(lsv, 0) == 0.0) { lsv = lane == 0 ? 1.0 : 0.0; AA = 1.0; break; }
-            double tmp = warp_sum(lane < n ? lsv * sg : 0.0);
-            if (attempt > 0) tmp = fmax(tmp, eps);
+        double lsv, AA;
+        if (n == 1 && shfl_d(ls0, 0) == 0.0) {
+            lsv = lane == 0 ? 1.0 : 0.0;
+            AA = 1.0;
+        } else {
+            double tmp = warp_sum(ls0 * sgv);
+            if (!(tmp > 0.0)) tmp = eps;                                 // sklearn retries on a perturbed factor; same floor
             AA = 1.0 / sqrt(tmp);
-            if (isfinite(AA) || attempt > 60) { lsv *= AA; break; }
-            doff += ldexp(eps, attempt);
+            lsv = ls0 * AA;
         }
         if (lane < n) S.ls[lane] = lsv;
         __syncwarp();
         double corr = 0.0;
         if (inactive) {
             for (int a = 0; a < n; ++a) corr += G[S.act[a] * 32 + lane] * S.ls[a];
-            corr = rint(corr * 1e15) / 1e15;                         // np.around(..., decimals=15)
+            corr = rint(corr * 1e15) / 1e15;                             // np.around(..., decimals=15)
         }
         const double g12 = inactive ? fmin(min_pos((C - Cov) / (AA - corr + tiny32)), min_pos((C + Cov) / (AA + corr + tiny32))) : DBL_MAX;
         double gamma = fmin(warp_min_nonneg(g12), C / AA);
@@ -318,12 +301,13 @@ __device__ int lasso_path(SC& S, const double* __restrict__ G, const RowProducts
         ++n_iter;
         if (my_a >= 0) coef += gamma * my_ls;
         if (inactive) Cov -= gamma * corr;
-        prev_alpha = C;
+        prev_C = C;
         if (LAR) {
-            if (drop) {                                              // sign flip only; L^-1 sign has to follow it
+            if (drop) {                                                  // sign flip only; the direction has to follow it
                 if (leaving) S.sgn[my_a] = -S.sgn[my_a];
                 __syncwarp();
-                yv = trsv_lower(S, n, lane < n ? S.sgn[lane] : 0.0, lane, 0.0);
+                if (lane < n) sgv = S.sgn[lane];
+                direction_from_scratch(n);
             }
             __syncwarp();
             continue;
@@ -338,22 +322,39 @@ __device__ int lasso_path(SC& S, const double* __restrict__ G, const RowProducts
         const uint32_t nz = __ballot_sync(0xffffffffu, fabs(coef) > eps);
         if (lane == 0) { S.rss[n_iter] = rss; S.nz[n_iter] = nz; }
         if (drop) {
-            // the coefficient that reached zero leaves: Cov from scratch, list compacted, factor rebuilt
+            // the coefficients that reached zero leave, one position at a time
             if (leaving) { Cov = R.xy - q; coef = 0.0; inactive = true; }
-            const uint32_t out = __ballot_sync(0xffffffffu, leaving);
+            uint32_t out = __ballot_sync(0xffffffffu, leaving);          // by FEATURE lane
             __syncwarp();
-            if (lane == 0) {
-                int k = 0;
-                for (int a = 0; a < n; ++a)
-                    if (!((out >> S.act[a]) & 1u)) { S.act[k] = S.act[a]; S.sgn[k] = S.sgn[a]; ++k; }
+            while (out) {
+                const int f = __ffs(out) - 1;
+                out &= out - 1;
+                const int k = __shfl_sync(0xffffffffu, my_a, f);         // its active position
+                const int nn = n_active, last = nn - 1;
+                const double pinv = 1.0 / S.L[k][k];
+                if (lane < nn && lane != k) {
+                    const double ck = S.L[lane][k] * pinv;
+                    for (int a = 0; a < nn; ++a) S.L[lane][a] -= ck * S.L[k][a];
+                }
+                __syncwarp();
+                if (k != last) {                                         // the last position takes the freed slot
+                    if (lane == k)
+                        for (int a = 0; a < nn; ++a) S.L[k][a] = S.L[last][a];
+                    __syncwarp();
+                    if (lane < nn) S.L[lane][k] = S.L[lane][last];
+                    __syncwarp();
+                    if (lane == k) S.L[k][k] = S.L[last][last];
+                    const int fl = S.act[last];
+                    __syncwarp();
+                    if (lane == 0) { S.act[k] = fl; S.sgn[k] = S.sgn[last]; }
+                    if (lane == fl) my_a = k;
+                }
+                if (lane == f) my_a = -1;
+                n_active = last;
+                __syncwarp();
             }
-            n_active = n - __popc(out);
-            __syncwarp();
-            my_a = -1;
-            for (int a = 0; a < n_active; ++a)
-                if (S.act[a] == lane) my_a = a;
-            chol_rebuild(S, n_active, G, lane);
-            yv = trsv_lower(S, n_active, lane < n_active ? S.sgn[lane] : 0.0, lane, 0.0);
+            sgv = lane < n_active ? S.sgn[lane] : 0.0;
+            direction_from_scratch(n_active);
             if (n_active == 0) drop = false;
         }
         __syncwarp();

@@ -140,6 +140,118 @@ def lasso_path_gram(G: np.ndarray, xy: np.ndarray, yy: float, n: float, max_iter
     return points
 
 
+def lasso_path_inv(G: np.ndarray, xy: np.ndarray, yy: float, n: float, max_iter: int = 96, lar: bool = False):
+    """The device's own form of the walk (csrc/kshap_lasso.cu::lasso_path): the INVERSE of the active Gram block instead
+    of its Cholesky factor.  Appending a feature is a rank-one border update, the unnormalised direction Ainv.sign
+    follows without a solve, a drop is a rank-one downdate with the last position moving into the freed slot.
+    `lar=False`: method "lasso", returns [(rss, nonzero mask)] like `lasso_path_gram`; `lar=True`: method "lar" stopped
+    after `max_iter` steps (num_features(k)), returns the active features in order of entry."""
+    M = len(xy)
+    cov = xy.copy()
+    inactive = np.ones(M, bool)
+    coef = np.zeros(M)
+    active: list[int] = []
+    sign: list[float] = []
+    Ainv = np.zeros((M, M))
+    ls0 = np.zeros(M)
+    points = [(yy, np.zeros(M, bool))]
+    n_iter, drop, prev_C = 0, False, np.inf
+
+    def min_pos(v):
+        v = v[v > 0]
+        return float(v.min()) if len(v) else np.finfo(np.float64).max
+
+    while True:
+        if inactive.any():
+            cand = np.where(inactive, np.abs(cov), 0.0)
+            j = int(np.argmax(cand))
+            C = float(cand[j])
+        else:
+            j, C = -1, 0.0
+        if C <= EQ_TOL * n:
+            break
+        if n_iter >= max_iter or len(active) >= M:
+            break
+        if not drop:
+            k = len(active)
+            g = np.array([G[j, a] for a in active])
+            u = Ainv[:k, :k] @ g
+            diag = max(np.sqrt(abs(G[j, j] - g @ u)), EPS)            # sklearn's new Cholesky pivot
+            if diag < 1e-7:
+                cov[j] = 0.0
+                continue
+            s_inv = 1.0 / (diag * diag)
+            sg_new = float(np.sign(cov[j]))
+            t = ((u @ np.array(sign) if k else 0.0) - sg_new) * s_inv
+            Ainv[:k, :k] += np.outer(u, u) * s_inv
+            Ainv[:k, k] = Ainv[k, :k] = -u * s_inv
+            Ainv[k, k] = s_inv
+            ls0[:k] += u * t
+            ls0[k] = -t
+            active.append(j)
+            sign.append(sg_new)
+            inactive[j] = False
+        if not lar and n_iter > 0 and prev_C < C:
+            break
+        k = len(active)
+        sg = np.array(sign)
+        if k == 1 and ls0[0] == 0:
+            ls, AA = np.array([1.0]), 1.0
+        else:
+            tmp = float(ls0[:k] @ sg)
+            AA = 1.0 / np.sqrt(tmp if tmp > 0 else EPS)
+            ls = ls0[:k] * AA
+        corr = np.around(G[active].T @ ls, 15)
+        ia = np.nonzero(inactive)[0]
+        g1 = min_pos((C - cov[ia]) / (AA - corr[ia] + TINY32))
+        g2 = min_pos((C + cov[ia]) / (AA + corr[ia] + TINY32))
+        gamma = min(g1, g2, C / AA)
+        z = -coef[active] / (ls + TINY32)
+        z_pos = min_pos(z)
+        drop, out = False, []
+        if z_pos < gamma:
+            out = [int(i) for i in np.nonzero(z == z_pos)[0][::-1]]
+            if not lar:
+                gamma = z_pos
+            drop = True
+        n_iter += 1
+        coef[active] += gamma * ls
+        cov[ia] -= gamma * corr[ia]
+        prev_C = C
+        if lar:
+            if drop:                                                    # sign flip only; the direction follows it
+                for i in out:
+                    sign[i] = -sign[i]
+                ls0[:k] = Ainv[:k, :k] @ np.array(sign)
+            continue
+        qv = G @ coef
+        points.append((float(yy - 2.0 * coef @ xy + coef @ qv), np.abs(coef) > EPS))
+        if drop:
+            for i in out:
+                k = len(active)
+                f = active[i]
+                cov[f] = xy[f] - qv[f]
+                coef[f] = 0.0
+                inactive[f] = True
+                c = Ainv[:k, i].copy()
+                Ainv[:k, :k] -= np.outer(c, c) / Ainv[i, i]
+                last = k - 1
+                if i != last:                                           # the last position takes the freed slot
+                    Ainv[i, :k] = Ainv[last, :k]
+                    Ainv[:k, i] = Ainv[:k, last]
+                    Ainv[i, i] = Ainv[last, last]
+                    active[i], sign[i] = active[last], sign[last]
+                active.pop()
+                sign.pop()
+                Ainv[last, :] = 0.0
+                Ainv[:, last] = 0.0
+            k = len(active)
+            ls0[:] = 0.0
+            if k:
+                ls0[:k] = Ainv[:k, :k] @ np.array(sign)
+    return active if lar else points
+
+
 def select_ic(P: dict, xy: np.ndarray, yy: float, criterion: str) -> np.ndarray:
     """Indices LassoLarsIC keeps: argmin over the path of n log(2 pi s2) + rss / s2 + factor * df."""
     n, M = P["n"], P["M"]

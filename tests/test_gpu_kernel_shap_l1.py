@@ -348,3 +348,32 @@ def test_row_stream_redraws_keep_the_selection_products_fresh(params, l1):
                 assert np.all(np.abs(phi3[i] - ref) <= 1e-4 * np.abs(ref).max() + 1e-7)
     assert same >= len(X) - 1
     stream.close()
+
+
+@pytest.mark.parametrize("link", ["identity", "logit"])
+def test_information_criterion_paths_with_sign_change_drops(params, link):
+    """70 coalitions: on a third of the rows a coefficient crosses zero along the LARS-lasso path and leaves the active
+    set (none does at 2048 coalitions), so this is the case that runs the kernel's drop step - downdate of the active
+    block's inverse, the last position moving into the freed slot, the feature re-entering later."""
+    import lasso_gram_model as gm
+    bg, X, f = _setup(params, 40, 96, seed=200)
+    Z, kw, _ = ks.sample_coalitions(30, 70, np.random.RandomState(70))
+    fnull = float(f(bg).mean())
+    plan = _plan(params, bg, [(Z, kw)], link=link)
+    plan.set_l1(L1_AIC)
+    _, ey, _ = _run(plan, X, TC)
+    lf = ks.LINKS[link]
+    P = gm.set_products(Z, kw)
+    with_drops = 0
+    for i, x in enumerate(_rows32(X)):
+        if link == "logit" and ey[i].max() > 0.99:
+            continue
+        e = lf(ey[i].astype(np.float64)) - lf(fnull)
+        xy, yy = gm.row_products(P, Z, kw, e, lf(float(f(x[None])[0])) - lf(fnull))
+        sizes = [m.sum() for _, m in gm.lasso_path_gram(P["G"], xy, yy, P["n"])]
+        with_drops += any(b < a for a, b in zip(sizes, sizes[1:]))
+    assert with_drops >= 15, f"only {with_drops} rows have a drop on their path: the case no longer exercises the drop step"
+    for mode, name in ((L1_AIC, "aic"), (L1_BIC, "bic")):
+        plan.set_l1(mode)
+        _compare(plan, X, Z, kw, f, fnull, TC, name, link=link, allow=4)
+    plan.close()

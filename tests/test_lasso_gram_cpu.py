@@ -71,10 +71,14 @@ def test_lasso_path_with_drops_matches_lars_path():
             G, xy, yy = X.T @ X, X.T @ y, float(y @ y)
             _, _, coefs = lars_path(X, y, Gram=G.copy(), Xy=xy.copy(), method="lasso", alpha_min=0.0, max_iter=500)
             ref = [(float(np.sum((y - X @ c) ** 2)), np.abs(c) > np.finfo(float).eps) for c in coefs.T]
-            got = gm.lasso_path_gram(G, xy, yy, float(n))
             sizes = [m.sum() for _, m in ref]
             drops += sum(b < a for a, b in zip(sizes, sizes[1:]))
-            assert len(ref) == len(got)
-            for (r0, m0), (r1, m1) in zip(ref, got):
-                assert np.array_equal(m0, m1) and abs(r0 - r1) <= 1e-8 * yy
+            for walk in (gm.lasso_path_gram, gm.lasso_path_inv):          # sklearn's factor form, the kernel's inverse form
+                got = walk(G, xy, yy, float(n))
+                assert len(ref) == len(got)
+                for (r0, m0), (r1, m1) in zip(ref, got):
+                    assert np.array_equal(m0, m1) and abs(r0 - r1) <= 1e-8 * yy
+            for k in (3, 6):                                               # method "lar", max_iter = k: num_features(k)
+                sel = lars_path(X, y, Gram=G.copy(), Xy=xy.copy(), max_iter=k)[1]
+                assert list(sel) == list(gm.lasso_path_inv(G, xy, yy, float(n), max_iter=k, lar=True))
     assert drops >= 10, "the cases no longer exercise the drop step"
