@@ -63,6 +63,7 @@ _SIGS = {
     "fdb_kshap_plan_info": (_i, [_vp, C.POINTER(C.c_int)]),
     "fdb_kshap_plan_set_num_features": (_i, [_vp, _i]),
     "fdb_kshap_plan_set_l1": (_i, [_vp, _i, C.c_double]),
+    "fdb_format_json_rows": (_i, [_vp, _i64, _i, _vp, _i64, _vp]),
     "fdb_kshap_explain_dev": (_i, [_vp, _vp, _i64, _vp, _vp, _i, _vp, _vp, _vp]),
     "fdb_kshap_explain_host": (_i, [_vp, _i64, _vp, _vp, _i, _vp, _vp]),
     "fdb_probe_pipes": (_i, [_vp, _dp]),

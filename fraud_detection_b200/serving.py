@@ -17,6 +17,10 @@ One worker thread drains the queue: it takes the first waiting request, keeps co
 future with its own row.  Errors raised for a batch are re-checked row by row so that one
 malformed request fails alone.
 
+``explanation_records`` / ``json_rows`` produce what the explanation task stores per row
+(api/worker.py:82-88: ``json.dumps(shap_values[0].tolist())``) for a whole batch, with the text
+formatted in the library - byte for byte what ``json.dumps`` writes.
+
 ``attributions_for_task`` restates the row preparation of the deployed XAI task
 (xai_tasks.py:86-107), including its quirks (missing keys read as 0.0, no scaler - Q2 in
 SURVEY.md section 3); ``apply_scaler=True`` is the opt-in fix.
@@ -159,3 +163,37 @@ def attributions_for_task(model, feature_names, input_data: dict, scaler=None, a
         _lib.dvec(np.asarray(model.coef_).ravel()), float(np.asarray(model.intercept_).ravel()[0]),
         _lib.np_ptr(proba), 1, None, _lib.np_ptr(phi), None, None))
     return float(proba[0]), {f: float(a) for f, a in zip(feature_names, phi[0].tolist())}
+
+
+def json_rows(values) -> list:
+    """``[json.dumps(row.tolist()) for row in values]`` for a 2-D array, formatted by the library
+    (``fdb_format_json_rows``: shortest round-trip digits laid out as ``float.__repr__`` does) -
+    the text the explanation task stores (api/worker.py:86)."""
+    from . import _lib
+    A = np.ascontiguousarray(values, dtype=np.float64)
+    if A.ndim != 2:
+        raise ValueError(f"expected a 2-D array of attribution rows, got shape {A.shape}")
+    n, c = A.shape
+    buf = np.empty(max(n * (c * 28 + 2), 1), dtype=np.uint8)
+    off = np.empty(n + 1, dtype=np.int64)
+    _lib.check(_lib.lib.fdb_format_json_rows(_lib.np_ptr(A), n, c, _lib.np_ptr(buf), buf.size, _lib.np_ptr(off)))
+    text = buf[:int(off[-1])].tobytes().decode("ascii")
+    o = off.tolist()
+    return [text[o[i]:o[i + 1]] for i in range(n)]
+
+
+def explanation_records(transaction_ids, correlation_ids, shap_values, feature_names) -> list:
+    """The rows the explanation task hands to its store (api/worker.py:82-88), for a whole batch:
+    ``{'transaction_id', 'correlation_id', 'shap_values': json.dumps(row.tolist()),
+    'feature_names': json.dumps(list(X.columns))}`` per explained row.  ``shap_values`` is the
+    ``(N, 30)`` result of ``explainer.shap_values``; a single id / 1-D row gives one record."""
+    import json
+    phi = np.asarray(shap_values, dtype=np.float64)
+    if phi.ndim == 1:
+        phi = phi[None, :]
+        transaction_ids, correlation_ids = [transaction_ids], [correlation_ids]
+    if not (len(transaction_ids) == len(correlation_ids) == phi.shape[0]):
+        raise ValueError("one transaction id and one correlation id per explained row")
+    names = json.dumps(list(feature_names))
+    return [{"transaction_id": t, "correlation_id": c, "shap_values": s, "feature_names": names}
+            for t, c, s in zip(transaction_ids, correlation_ids, json_rows(phi))]

@@ -208,6 +208,17 @@ int fdb_linear_pass_noalloc(void* stream, int dtype, int64_t n_rows, const void*
                             void* proba, int proba_cols, void* logit, void* phi, uint8_t* cls, double* abs_sum);
 
 /* ---------------------------------------------------------------------------------
+ * Result sink (api/worker.py:82-88): the task stores json.dumps(shap_values[0].tolist()).
+ * fdb_format_json_rows writes exactly that text for every row of a (n_rows, n_cols) float64
+ * HOST array - shortest round-trip digits, Python's fixed / exponent layout, "NaN" /
+ * "Infinity" like json.dumps, ", " separators - back to back into `out`; row r occupies
+ * [offsets[r], offsets[r + 1]) (offsets has n_rows + 1 entries).  out_cap >=
+ * n_rows * (n_cols * 28 + 2) always fits; a smaller buffer may return FDB_ERR_ARG.
+ * Host code only (no GPU needed); rows are independent, callers may split them over threads.
+ * ------------------------------------------------------------------------------- */
+int fdb_format_json_rows(const double* values, int64_t n_rows, int n_cols, char* out, int64_t out_cap, int64_t* offsets);
+
+/* ---------------------------------------------------------------------------------
  * Measurement aid (no counterpart in the reference): instruction-pipe rates of this GPU,
  * measured with small saturating kernels at the clock the device runs them at.  They are
  * the denominators of the Kernel SHAP rooflines in bench.py (MEASURED_PEAKS.json has no

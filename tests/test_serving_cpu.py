@@ -86,3 +86,28 @@ def test_asyncio_entry_point(params):
             return res
     res = asyncio.run(go())
     assert len(res) == 20 and all(r.proba.shape == (2,) for r in res)
+
+
+def test_json_rows_is_byte_for_byte_json_dumps():
+    """The result sink of the explanation task (api/worker.py:82-88) stores json.dumps(shap_values[0].tolist()); the
+    library's formatter must write exactly that text (host code - runs without a GPU)."""
+    import json
+    from fraud_detection_b200.serving import explanation_records, json_rows
+    rng = np.random.default_rng(0)
+    A = rng.standard_normal((3000, 30)) * np.exp(rng.uniform(-40, 40, (3000, 30)))
+    A[0, :14] = [0.0, -0.0, 1e-4, 1e-5, 9.999e-5, 1e15, 1e16, 123456789012345678.0, 5e-324, 1.7976931348623157e308,
+                 np.nan, np.inf, -np.inf, 2.2250738585072014e-308]
+    A[1, :8] = [1.0, -1.5, 100.0, 0.1, 1 / 3, 1e22, 1e23, 0.30000000000000004]
+    A[2] = np.float32(rng.standard_normal(30)).astype(np.float64)          # float32 attributions widened, as tolist() does
+    assert json_rows(A) == [json.dumps(r.tolist()) for r in A]
+    assert json_rows(np.zeros((0, 30))) == [] and json_rows(np.zeros((2, 0))) == ["[]", "[]"]
+    with pytest.raises(ValueError):
+        json_rows(np.zeros(30))
+    names = [f"feature_{i}" for i in range(30)]
+    recs = explanation_records(["t0", "t1"], ["c0", "c1"], A[:2], names)
+    assert recs[1] == {"transaction_id": "t1", "correlation_id": "c1", "shap_values": json.dumps(A[1].tolist()),
+                       "feature_names": json.dumps(names)}
+    one = explanation_records("t", "c", A[2], names)
+    assert len(one) == 1 and json.loads(one[0]["shap_values"]) == A[2].tolist()
+    with pytest.raises(ValueError):
+        explanation_records(["t0"], ["c0", "c1"], A[:2], names)
