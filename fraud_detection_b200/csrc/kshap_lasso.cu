@@ -589,7 +589,7 @@ __global__ void __launch_bounds__(128) kshap_lasso_solve(
         }
         if (fabs(p) < 1e-10) p = 0.0;
         if (lane < FDB_F) phi[(size_t)r * FDB_F + lane] = (float)p;
-        abs_acc += fabs(p);
+        abs_acc += fabs((double)(float)p);          // of the value as stored, so that a recount over phi reproduces the sums
     }
     if (abs_sum == nullptr) return;
     __shared__ double s_acc[4][32];

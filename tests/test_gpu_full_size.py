@@ -139,3 +139,58 @@ def test_factored_evaluator_over_several_rounds(params):
         got = phi_fx[r].cpu().numpy()
         assert np.all(np.abs(got - ref) <= 1e-4 * np.abs(ref).max() + 1e-8)
     plan.close()
+
+
+@pytest.mark.parametrize("l1,mode,param", [("num_features(10)", 1, 10.0), ("aic", 2, 0.0)])
+def test_config3_full_size_with_feature_selection(params, l1, mode, param):
+    """Config 3 at its full size with shap's feature selections in front of the solve (num_features(10) is shap's own
+    default): properties that need no oracle on every one of the 100,000 rows - additivity over the kept features, at
+    most k kept, bitwise-equal reruns, |phi| column sums against a recount - the two evaluators against each other,
+    and rows spread over the rounds against the oracle (real sklearn) fed the GPU's own expectations."""
+    import warnings
+    from fraud_detection_b200 import KernelShapPlan, sampler
+    rows = 100_000
+    bg = scoring.transform(params, synth.rows(100, seed=43))
+    X = scoring.transform(params, synth.rows(rows, seed=1)).astype(np.float32)
+    bits, kw = sampler.sample_coalitions(30, 2048, np.random.RandomState(0))
+    plan = KernelShapPlan(params.coef, params.intercept, bg, bits, kw)
+    plan.set_l1(mode, param)
+    x = torch.from_numpy(X).cuda()
+    abs_sum = torch.empty(32, dtype=torch.float64, device="cuda")
+    phi = plan.explain_dev(x, abs_sum=abs_sum).clone()          # factored evaluator; num_features reads its X'W y records
+    phi_again = plan.explain_dev(x).clone()
+    phi_tc = plan.explain_dev(x, evaluator=0).clone()           # general evaluator, expectations through HBM
+    torch.cuda.synchronize()
+    f = lambda A: scoring.predict_proba(params, A)[:, 1]  # noqa: E731
+    fx = f(X.astype(np.float64))
+    np.testing.assert_allclose(phi.double().sum(1).cpu().numpy() + plan.expected_value, fx, rtol=0, atol=1e-5)
+    np.testing.assert_allclose(phi_tc.double().sum(1).cpu().numpy() + plan.expected_value, fx, rtol=0, atol=1e-5)
+    assert torch.equal(phi, phi_again)
+    kept = (phi != 0).sum(1)
+    if mode == 1:
+        assert int(kept.max()) <= 10
+    else:
+        assert 1 <= int(kept.min()) and float(kept.float().mean()) < 30
+    a = abs_sum.cpu().numpy()
+    assert a[30] == rows
+    np.testing.assert_allclose(a[:30], phi.double().abs().sum(0).cpu().numpy(), rtol=1e-9)
+    # the evaluators see expectations that differ in the last float32 bits: the same features on nearly every row
+    same = ((phi != 0) == (phi_tc != 0)).all(1)
+    assert float(same.float().mean()) > 0.995
+    scale = phi_tc.abs().max(1, keepdim=True).values
+    assert bool((((phi - phi_tc).abs() <= 1e-4 * scale + 1e-8).all(1) | ~same).all())
+    # rows spread over the rounds against the oracle, fed the expectations of those rows
+    pick = [0, 25_087, 25_088, 50_176, 75_264, rows - 1]
+    xs = x[pick].contiguous()
+    ey = torch.empty((len(pick), plan.n_masks), dtype=torch.float32, device="cuda")
+    got = plan.explain_dev(xs, evaluator=0, ey=ey).cpu().numpy().astype(np.float64)
+    Z = sampler.bits_to_masks(bits)
+    fnull = float(f(bg).mean())
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        for i, r in enumerate(pick):
+            ref = ks.solve(Z, kw, ey[i].cpu().numpy().astype(np.float64), float(fx[r]), fnull, l1_reg=l1)
+            assert np.array_equal(ref != 0, got[i] != 0), r
+            assert np.all(np.abs(got[i] - ref) <= 1e-4 * np.abs(ref).max() + 1e-9), r
+            assert np.array_equal(got[i] != 0, phi_tc[r].cpu().numpy() != 0), r
+    plan.close()
