@@ -19,9 +19,11 @@
 // and its inverse.  Per explained row ONE pass over the coalition expectations gives T_j = sum kw z_mj e_m,
 // E2 = sum kw e^2 and P1 = sum (sqrt(kw (M - s)) + sqrt(kw s)) e, from which
 //   X'y_j = (M T_j - d B_j - sum T + d S0 - (R_j - Q) (P1 - d Q) / n) / sd_j,   y'y = M E2 - 2 d sum T + d^2 S0 - (P1 - d Q)^2 / n.
-// The LARS-lasso walk (adds, sign-change drops with a refactorisation of the active block, RSS and support recorded at
-// every path point), the criterion, the coordinate descent and the reduced WLS all run in float64, one warp per row,
-// lane j = feature j (tests/lasso_gram_model.py is the same algorithm in numpy, checked against sklearn on the CPU).
+// num_features(k) needs T and d only (raw Gram, nothing centred); after the factored evaluator T comes from the records of
+// its fused X'W y GEMM and no pass over the expectations is made at all.
+// The LARS walk (adds, sign-change drops / flips, RSS and support recorded at every path point of the lasso variant), the
+// criterion, the coordinate descent and the reduced WLS all run in float64, one warp per row, lane j = feature j
+// (tests/lasso_gram_model.py is the same algorithm in numpy, checked against sklearn on the CPU).
 
 #include <float.h>
 #include <math.h>
@@ -36,11 +38,6 @@ constexpr int kVecStride = 96;        // per set: [0..31] column sums c_j, [32..
 
 __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 __device__ __forceinline__ double shfl_xor_d(double v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
-__device__ __forceinline__ double warp_min(double v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v = fmin(v, shfl_xor_d(v, o));
-    return v;
-}
 __device__ __forceinline__ double warp_max(double v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v = fmax(v, shfl_xor_d(v, o));
@@ -202,7 +199,7 @@ struct RowProducts {
 //                   t = (u.sign - sign_b) / s
 //   drop position k: Ainv <- Ainv - c c'/Ainv_kk without row / column k (c = column k); the last position moves into k
 // - every step is a lane-parallel sweep over one row, nothing is sequential across lanes.  tests/lasso_gram_model.py
-// walks sklearn's factor, tools-side checks of this form against lars_path are in tests/test_lasso_gram_cpu.py.
+// holds both forms (sklearn's factor, this inverse); tests/test_lasso_gram_cpu.py checks both against lars_path.
 template <bool LAR, class SC>
 __device__ int lasso_path(SC& S, const double* __restrict__ G, const RowProducts& R, double n_aug, bool is_var,
                           int n_var, int lane, int max_iter) {
