@@ -365,23 +365,28 @@ __device__ uint32_t lasso_cd_support(const double* __restrict__ G, const RowProd
     const double tol = 1e-4;
     const double gjj = lane < FDB_F ? G[lane * 32 + lane] : 1.0;
     double w = 0.0, q = 0.0;                 // lane j: w_j and (G w)_j
+    const bool ok = is_var && gjj != 0.0;
     for (int it = 0; it < 1000; ++it) {
-        double w_max = 0.0, d_w_max = 0.0;
-        for (int j = 0; j < FDB_F; ++j) {
-            const double wj = shfl_d(w, j), dj = shfl_d(gjj, j);
-            const double t = shfl_d(R.xy - q, j) + dj * wj;
-            const bool var_j = __shfl_sync(0xffffffffu, (int)is_var, j) != 0;
-            if (!var_j || dj == 0.0) continue;
+        // One cyclic sweep.  A coordinate whose update returns the value it already has changes nothing (sklearn skips
+        // the residual update too), so the sweep jumps from one CHANGING coordinate to the next: every lane evaluates
+        // its own update from its current (G w)_j, the lowest changing lane at or after the cursor is applied, repeat.
+        // The iterates are those of the coordinate-by-coordinate loop; a sweep costs (changes + 1) steps instead of 30.
+        double d_w_max = 0.0;
+        int pos = 0;
+        while (true) {
+            const double t = R.xy - q + gjj * w;
             const double mag = fabs(t) - lam;
-            const double nw = mag > 0.0 ? copysign(mag, t) / dj : 0.0;
-            const double dw = nw - wj;
-            if (dw != 0.0) {
-                if (lane < FDB_F) q += G[j * 32 + lane] * dw;
-                if (lane == j) w = nw;
-            }
+            const double nw = (ok && mag > 0.0) ? copysign(mag, t) / gjj : 0.0;
+            const unsigned m = __ballot_sync(0xffffffffu, ok && lane >= pos && nw != w);
+            if (m == 0u) break;
+            const int j = __ffs(m) - 1;
+            const double dw = shfl_d(nw - w, j);
+            if (lane < FDB_F) q += G[j * 32 + lane] * dw;
+            if (lane == j) w = nw;
             d_w_max = fmax(d_w_max, fabs(dw));
-            w_max = fmax(w_max, fabs(nw));
+            pos = j + 1;
         }
+        const double w_max = warp_max(fabs(w));
         if (w_max == 0.0 || d_w_max / w_max < tol || it == 999) {
             const double dual = warp_max(is_var ? fabs(R.xy - q) : 0.0);
             const double wxy = warp_sum(w * R.xy), wq = warp_sum(w * q), l1 = warp_sum(fabs(w));
