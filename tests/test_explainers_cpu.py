@@ -52,3 +52,46 @@ def test_background_subsample_rules(params):
     with pytest.raises(ValueError):
         _background(data, subsample="bogus")
     assert "resample_without_replacement" in SUBSAMPLE_RULES
+
+
+def test_l1_reg_values_are_parsed_like_shap_takes_them():
+    """Every l1_reg value KernelExplainer.shap_values accepts maps to a device mode; "auto" is decided per row from
+    M = number of varying features: AIC when the coalitions cover under 20 % of the 2^M - 2 possible ones."""
+    from fraud_detection_b200.explainers import L1_AIC, L1_ALPHA, L1_BIC, L1_NONE, L1_NUM_FEATURES, _L1Spec
+    assert _L1Spec(False).resolve(30, "auto") == (L1_NONE, 0.0) == _L1Spec(0).resolve(30, 2048)
+    assert _L1Spec("num_features(10)").resolve(30, "auto") == (L1_NUM_FEATURES, 10.0)
+    assert _L1Spec("aic").resolve(5, "auto") == (L1_AIC, 0.0) and _L1Spec("bic").resolve(30, "auto") == (L1_BIC, 0.0)
+    assert _L1Spec(0.01).resolve(30, "auto") == (L1_ALPHA, 0.01)
+    auto = _L1Spec("auto")
+    assert auto.resolve(30, "auto") == (L1_AIC, 0.0)            # 2108 of 2^30 - 2
+    assert auto.resolve(12, 1024) == (L1_NONE, 0.0)             # 1024 of 4094 = 0.25
+    assert auto.resolve(13, 1024) == (L1_AIC, 0.0)              # 1024 of 8190 = 0.125
+    assert auto.resolve(6, "auto") == (L1_NONE, 0.0)            # capped at the 62 possible coalitions: fraction 1
+    for bad in ("ridge", "num_features(0)", "num_features(17)", -1.0, float("nan")):
+        with pytest.raises(ValueError):
+            _L1Spec(bad)
+
+
+def test_oracle_auto_rule_follows_the_evaluated_fraction(params):
+    """The oracle's own "auto": same rule, through explain_row (no GPU, real sklearn)."""
+    import warnings
+    from oracle import kernel_shap as ks
+    Xs = scoring.transform(params, synth.rows(60, seed=5))
+    bg, x = Xs[:20], Xs[40]
+    f = lambda A: scoring.predict_proba(params, A)[:, 1]  # noqa: E731
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        auto = ks.explain_row(f, x, bg, nsamples=300, l1_reg="auto", random=np.random.RandomState(1))
+        aic = ks.explain_row(f, x, bg, nsamples=300, l1_reg="aic", random=np.random.RandomState(1))
+        none = ks.explain_row(f, x, bg, nsamples=300, l1_reg=False, random=np.random.RandomState(1))
+    np.testing.assert_array_equal(auto, aic)                     # 300 of 2^30 - 2 coalitions
+    assert np.count_nonzero(none) == 30 and np.count_nonzero(aic) < 30
+    # few varying features: everything is enumerated, "auto" selects nothing
+    x6 = bg[0].copy()
+    x6[:6] = x[:6]
+    bg1 = bg[:1]
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        a = ks.explain_row(f, x6, bg1, nsamples=300, l1_reg="auto", random=np.random.RandomState(2))
+        n = ks.explain_row(f, x6, bg1, nsamples=300, l1_reg=False, random=np.random.RandomState(2))
+    np.testing.assert_array_equal(a, n)
