@@ -70,6 +70,11 @@ __global__ void __launch_bounds__(32) kshap_sample_sets(const SamplerParams p) {
     __shared__ __align__(16) uint32_t s_bits[kMaxSamples];
     __shared__ __align__(16) uint32_t s_cnt[kMaxSamples / 2];       // 16-bit draw counts, two per word (at most 4 x nsamples draws in all)
     __shared__ __align__(16) unsigned short h_slot[kHashSlots];
+#ifdef FDB_SAMPLER_PAD
+    __shared__ uint32_t s_pad[FDB_SAMPLER_PAD / 4];                  // occupancy experiment only (tools/variant_build.py)
+    if (p.nsamples < 0) s_pad[threadIdx.x] = 1u;
+    if (p.nsamples < -1) p.bits[0] = s_pad[(threadIdx.x + 1) & 31];
+#endif
     const uint32_t allw = 0xffffffffu;
     const int s = blockIdx.x, lane = threadIdx.x;
     uint32_t* ob = p.bits + (size_t)s * p.m_pad;
