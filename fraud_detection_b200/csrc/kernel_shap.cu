@@ -306,13 +306,23 @@ void fdb_kshap_split(double v, int fmt, int n, uint16_t* out) {
 // Stream-ordered part of the refresh for plans with several sets: per-set (X'WX)^-1 (and the Z'WZ products when feature
 // selection is on), enqueued on `st` with no host synchronisation.  Singular sets are counted in d_bad.
 static int refresh_set_products_async(fdb_kshap_plan* p, cudaStream_t st) {
-    kshap_wls_prepare<<<p->n_sets, 32, 0, st>>>(p->d_bits, p->d_kw, p->m_pad, p->d_ainv, p->d_c2, p->d_status, p->varying, p->d_bad);
-    FDB_CUDA(cudaGetLastError());
+    // (X'WX)^-1 is NOT rebuilt here but by the first solve that needs it (ensure_inverses): a plan whose rows go through a
+    // feature selection (l1_reg) never reads it, and its 32,768 Gauss-Jordan inversions are a quarter of a redraw
+    p->ainv_valid = false;
     if (p->d_gz) {
         int rc = fdb_kshap_refresh_lars(p, st);
         if (rc != FDB_OK) return rc;
         return fdb_kshap_refresh_lasso(p, st);
     }
+    return FDB_OK;
+}
+
+// per-set (X'WX)^-1 for the current sets, stream-ordered (singular sets are counted in d_bad)
+static int ensure_inverses(fdb_kshap_plan* p, cudaStream_t st) {
+    if (p->ainv_valid) return FDB_OK;
+    kshap_wls_prepare<<<p->n_sets, 32, 0, st>>>(p->d_bits, p->d_kw, p->m_pad, p->d_ainv, p->d_c2, p->d_status, p->varying, p->d_bad);
+    FDB_CUDA(cudaGetLastError());
+    p->ainv_valid = true;
     return FDB_OK;
 }
 
@@ -326,6 +336,7 @@ static int refresh_set_products(fdb_kshap_plan* p) {
     kshap_wls_prepare<<<p->n_sets, 32>>>(p->d_bits, p->d_kw, p->m_pad, p->d_ainv, p->d_c2, p->d_status, p->varying, p->d_bad);
     FDB_CUDA(cudaGetLastError());
     FDB_CUDA(cudaDeviceSynchronize());
+    p->ainv_valid = true;
     FDB_CUDA(cudaMemset(p->d_bad, 0, sizeof(int)));
     std::vector<int> st(p->n_sets);
     FDB_CUDA(cudaMemcpy(st.data(), p->d_status, (size_t)p->n_sets * 4, cudaMemcpyDeviceToHost));
@@ -694,6 +705,10 @@ extern "C" int fdb_kshap_explain_dev(fdb_kshap_plan* p, void* stream, int64_t n_
         int grid = (nb + 3) / 4;
         const int cap = ctx->sm_count * 8;
         if (grid > cap) grid = cap;
+        if (!p->ainv_valid) {                      // sets were redrawn on a stream since the inverses were built
+            int rc = ensure_inverses(p, st);
+            if (rc != FDB_OK) return rc;
+        }
         kshap_wls_solve<<<grid, 128, 0, st>>>(xb, r0, nb, sb, p->n_sets, p->d_bits, p->d_kw, p->m_pad, p->d_ey, p->d_ainv,
                                              p->d_c2, p->d_wq, (float)p->intercept, (float)p->fnull, p->link,
                                              phi + r0 * FDB_F, abs_sum, r0 > 0 ? 1 : 0, n_rows, p->d_partials,

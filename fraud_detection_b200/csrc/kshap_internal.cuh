@@ -62,6 +62,8 @@ struct fdb_kshap_plan {
     int64_t stage_rows = 0;            // rows the host-API staging buffers hold
     void* sampler_state = nullptr;     // device-sampled plans: the uploaded sampling schedule (kshap_sampler.cu)
     int* d_bad = nullptr;              // number of coalition sets whose X'WX came out singular since the last check (resample_dev)
+    bool ainv_valid = true;            // d_ainv / d_c2 match the current sets (a stream-ordered redraw leaves them stale; the
+                                       //   next K3 launch rebuilds them first, the feature-selection solves never need them)
     double* d_partials = nullptr;      // [FDB_MAX_GRID][32] per-CTA |phi| column sums of K3 / K3L (the plan's own: plans on
     unsigned int* d_ticket = nullptr;  //   different streams, and K1 calls on the same context, never share an arrival ticket)
 };
@@ -203,7 +205,7 @@ __device__ __forceinline__ bool fdb_kshap_weighted_gram_row_mma(const uint32_t* 
     const float inv_wmin = 1.0f / wmin;
     const int g = lane >> 2, t = lane & 3;
     float acc[2][4][4];
-    bool bad = false;
+    float worst = 0.f, largest = 0.f;       // how far a weight is from a whole multiple of wmin, and the largest multiple seen
     auto zero_acc = [&]() {
 #pragma unroll
         for (int r = 0; r < 2; ++r)
@@ -226,8 +228,9 @@ __device__ __forceinline__ bool fdb_kshap_weighted_gram_row_mma(const uint32_t* 
                 cnt[i] = in_enum ? 1.0f : 0.0f;
             } else {
                 const float q = ww[i] * inv_wmin, rq = rintf(q);
-                if (!in_enum && (fabsf(q - rq) > 1e-3f * fmaxf(rq, 1.0f) || rq > 2048.f)) bad = true;
                 cnt[i] = in_enum ? 0.0f : rq;
+                worst = fmaxf(worst, in_enum ? 0.f : fabsf(q - rq));       // judged once, after the loop
+                largest = fmaxf(largest, cnt[i]);
             }
         }
         const __half2 hab2 = __floats2half2_rn(cnt[0], cnt[1]), hcd2 = __floats2half2_rn(cnt[2], cnt[3]);
@@ -291,7 +294,9 @@ __device__ __forceinline__ bool fdb_kshap_weighted_gram_row_mma(const uint32_t* 
     }
     dump(tile + 32 * 33);
     __syncwarp();
-    if (__any_sync(full, bad)) return false;
+    // draw counts: every weight a whole multiple of the smallest (float32 rounding of count * scale stays below 3e-4 for
+    // counts <= 2048, which the half-precision operands hold exactly); anything else takes the generic path
+    if (__any_sync(full, worst > 0.01f || largest > 2048.f)) return false;
     const double dw0 = has_enum ? (double)w0 : 0.0, dwm = (double)wmin;
 #pragma unroll
     for (int j = 0; j < NF; ++j) a[j] = dw0 * (double)tile[lane * 33 + j] + dwm * (double)tile[(32 + lane) * 33 + j];
