@@ -614,6 +614,25 @@ def bench_kernel_shap(args, torch, dist, device, rank, world, model, scaler, pro
                            "note": "value = per batch: draw the sets + per-set (X'WX)^-1 + evaluate + solve, two plans alternating on two "
                                    "streams (KernelShapStream), wall clock over 8 batches, fresh sets every batch; evaluate_only keeps the "
                                    "sets; plan_ms = creating one plan incl. allocation"}
+    # ... and with shap's own default in front of the solve, l1_reg="num_features(10)" [recalled]: the same stream, the
+    # plans switched to the LAR selection (their sets are redrawn every batch, the Z'WZ products with them)
+    for pl in stream.plans:
+        pl.set_l1(1, 10.0)
+    for i in range(4):
+        stream.explain(x2, phi=phis[i & 1])
+    stream.synchronize()
+    sync()
+    t0 = time.perf_counter()
+    for i in range(n_stream):
+        stream.explain(x2, phi=phis[i & 1])
+    stream.synchronize()
+    ts = torch.tensor([(time.perf_counter() - t0) / n_stream], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+    out["per_row_sets"]["num_features_10"] = {"value": pr * world / float(ts.item()), "unit": "explained rows/s",
+                                              "stream_ms_per_batch": float(ts.item()) * 1e3,
+                                              "note": "fresh set per row AND num_features(10): what an unmodified "
+                                                      "KernelExplainer.shap_values(X) call does"}
     stream.close()
 
     # Rooflines against pipe rates measured in this process (fdb_probe_pipes), nominal figures beside them.

@@ -309,10 +309,14 @@ static int refresh_set_products_async(fdb_kshap_plan* p, cudaStream_t st) {
     // (X'WX)^-1 is NOT rebuilt here but by the first solve that needs it (ensure_inverses): a plan whose rows go through a
     // feature selection (l1_reg) never reads it, and its 32,768 Gauss-Jordan inversions are a quarter of a redraw
     p->ainv_valid = false;
-    if (p->d_gz) {
+    if (p->d_gz && p->l1_mode != FDB_KSHAP_L1_NONE) {          // Z'WZ products: every selection reads them
         int rc = fdb_kshap_refresh_lars(p, st);
         if (rc != FDB_OK) return rc;
-        return fdb_kshap_refresh_lasso(p, st);
+        if (p->l1_mode > FDB_KSHAP_L1_NUM_FEATURES) return fdb_kshap_refresh_lasso(p, st);
+        p->lasso_scaled = -1;                                  // centred Gram products (criteria / alpha) are stale now
+    } else if (p->d_gz) {
+        p->gz_valid = false;
+        p->lasso_scaled = -1;
     }
     return FDB_OK;
 }
@@ -357,8 +361,10 @@ static int refresh_set_products(fdb_kshap_plan* p) {
         if (p->d_lg) {
             const int scale = p->lasso_scaled;
             fdb_kshap_free_lasso(p);
-            rc = fdb_kshap_prepare_lasso(p, scale);
-            if (rc != FDB_OK) return rc;
+            if (scale >= 0) {                                  // -1: stale already, the next fdb_kshap_plan_set_l1 rebuilds them
+                rc = fdb_kshap_prepare_lasso(p, scale);
+                if (rc != FDB_OK) return rc;
+            }
         }
     }
     return FDB_OK;
@@ -582,7 +588,7 @@ extern "C" int fdb_kshap_plan_set_num_features(fdb_kshap_plan* p, int k) {
     if (k > 0) {
         DeviceGuard guard(p->ctx->device);
         FDB_REQUIRE(guard.ok, FDB_ERR_CUDA, "cannot select device %d", p->ctx->device);
-        int rc = fdb_kshap_prepare_lasso(p, 2);
+        int rc = fdb_kshap_prepare_lars(p);
         if (rc != FDB_OK) return rc;
     }
     p->num_features = k;

@@ -45,7 +45,7 @@ struct fdb_kshap_plan {
     float fx_half_spread = 0.f;        // largest half-spread (log2) of a coalition's background exponents around o_m
     unsigned char* d_fxtile = nullptr; // factored evaluator: per tile, x^T image (B operand of the fused X'W y GEMM) + o_m + kw_m
     double* d_gz = nullptr;            // [S][30][32] Z'WZ, built on demand for l1_reg = num_features(k)
-    double* d_bv = nullptr;            // [S][32]
+    double* d_bv = nullptr;            // [S][32] B_j = sum kw s z_mj; entry 31 = rows of the augmented system (2 x coalitions with weight)
     double* d_s0 = nullptr;            // [S]
     std::vector<double> bg_host;       // background rows (host copy, for rebuilding set-dependent operands)
     bool sampled = false;              // sets were drawn on the device and may be redrawn (fdb_kshap_plan_resample)
@@ -55,13 +55,14 @@ struct fdb_kshap_plan {
     double* d_lg = nullptr;            // [S][30][32] centred (scaled) Gram of the augmented system (kshap_lasso.cu)
     double* d_lginv = nullptr;         // [S][30][32] its inverse
     double* d_lvec = nullptr;          // [S][96] column sums, 1 / sd, Q, n
-    int lasso_scaled = -1;             // which variant d_lg holds: 1 unit-variance columns (criteria), 0 centred only (alpha), 2 raw (num_features)
+    int lasso_scaled = -1;             // which variant d_lg holds: 1 unit-variance columns (criteria), 0 centred only (alpha)
     uint32_t varying = 0x3FFFFFFFu;    // features that differ from the background for the rows of this plan (bit 29 always set)
     float* d_gpart = nullptr;          // [gpart_rows][slots][32] X'W y records written by K2f, folded by K3 (grown on demand)
     size_t ey_cap = 0, gpart_cap = 0;  // floats the two scratch buffers hold
     int64_t stage_rows = 0;            // rows the host-API staging buffers hold
     void* sampler_state = nullptr;     // device-sampled plans: the uploaded sampling schedule (kshap_sampler.cu)
     int* d_bad = nullptr;              // number of coalition sets whose X'WX came out singular since the last check (resample_dev)
+    bool gz_valid = true;              // d_gz / d_bv / d_s0 match the current sets (a redraw with no selection active skips them)
     bool ainv_valid = true;            // d_ainv / d_c2 match the current sets (a stream-ordered redraw leaves them stale; the
                                        //   next K3 launch rebuilds them first, the feature-selection solves never need them)
     double* d_partials = nullptr;      // [FDB_MAX_GRID][32] per-CTA |phi| column sums of K3 / K3L (the plan's own: plans on

@@ -31,8 +31,12 @@ __global__ void __launch_bounds__(32) kshap_gram_prepare(const uint32_t* __restr
     // B_i = sum_m kw s_m z_mi = sum_j Gz_ij and S0 = sum_m kw s_m = trace(Gz), because s_m = sum_j z_mj
     double a[FDB_F];
     double unused;
-    fdb_kshap_weighted_gram_row<FDB_F>(
-        sb, sk, m_pad, lane, [varying](uint32_t z) { return z & varying; }, [](uint32_t) { return false; }, a, unused);
+    __shared__ float s_tile[2 * 32 * 33];
+    auto word = [varying](uint32_t z) { return z & varying; };
+    auto flag = [](uint32_t) { return false; };
+    // draw-count weights (sampled sets, shap's own sets) take the tensor-core Gram, anything else the exact generic path
+    if (!fdb_kshap_weighted_gram_row_mma<FDB_F>(sb, sk, m_pad, lane, word, flag, s_tile, a, unused))
+        fdb_kshap_weighted_gram_row<FDB_F>(sb, sk, m_pad, lane, word, flag, a, unused);
     double b = 0.0;
 #pragma unroll
     for (int j = 0; j < FDB_F; ++j) b += a[j];
@@ -50,7 +54,12 @@ __global__ void __launch_bounds__(32) kshap_gram_prepare(const uint32_t* __restr
         gz[((size_t)s * FDB_F + lane) * 32 + 30] = 0.0;
         gz[((size_t)s * FDB_F + lane) * 32 + 31] = 0.0;
     }
-    bv[(size_t)s * 32 + lane] = lane < FDB_F ? b : 0.0;
+    // rows of the augmented system: two per coalition that carries weight (padding and merged duplicates carry none)
+    int cnt = 0;
+    for (int m = lane; m < m_pad; m += 32) cnt += sk[m] > 0.f ? 1 : 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    bv[(size_t)s * 32 + lane] = lane < FDB_F ? b : (lane == 31 ? 2.0 * (double)cnt : 0.0);
     if (lane == 0) s0[s] = tot;
 }
 
@@ -58,10 +67,13 @@ __global__ void __launch_bounds__(32) kshap_gram_prepare(const uint32_t* __restr
 }  // namespace
 
 int fdb_kshap_prepare_lars(fdb_kshap_plan* p) {
-    if (p->d_gz != nullptr) return FDB_OK;
-    FDB_CUDA(cudaMalloc((void**)&p->d_gz, (size_t)p->n_sets * FDB_F * 32 * 8));
-    FDB_CUDA(cudaMalloc((void**)&p->d_bv, (size_t)p->n_sets * 32 * 8));
-    FDB_CUDA(cudaMalloc((void**)&p->d_s0, (size_t)p->n_sets * 8));
+    if (p->d_gz != nullptr && p->gz_valid) return FDB_OK;
+    if (p->d_gz == nullptr) {
+        FDB_CUDA(cudaMalloc((void**)&p->d_gz, (size_t)p->n_sets * FDB_F * 32 * 8));
+        FDB_CUDA(cudaMalloc((void**)&p->d_bv, (size_t)p->n_sets * 32 * 8));
+        FDB_CUDA(cudaMalloc((void**)&p->d_s0, (size_t)p->n_sets * 8));
+    }
+    p->gz_valid = true;
     kshap_gram_prepare<<<p->n_sets, 32>>>(p->d_bits, p->d_kw, p->m_pad, p->d_gz, p->d_bv, p->d_s0, p->varying);
     FDB_CUDA(cudaGetLastError());
     FDB_CUDA(cudaDeviceSynchronize());

@@ -93,8 +93,8 @@ struct LassoScratchT {
     uint32_t nz[NPATH + 1];
 };
 
-// Per coalition set: Gram of the augmented matrix - scale 1: centred, unit-variance columns (criteria); 0: centred (alpha);
-// 2: raw (num_features: lars_path gets the matrix as it is) - its inverse (not for 2), column sums, 1 / sd.
+// Per coalition set: Gram of the augmented matrix - scale 1: centred, unit-variance columns (criteria); 0: centred only
+// (alpha) - its inverse, column sums, 1 / sd.  (num_features(k) walks the raw Gram, read straight from the Z'WZ products.)
 __global__ void __launch_bounds__(32) kshap_lasso_prepare(const uint32_t* __restrict__ bits, const float* __restrict__ kw,
                                                           int m_pad, const double* __restrict__ gz, const double* __restrict__ bv,
                                                           const double* __restrict__ s0, double* __restrict__ lg,
@@ -113,7 +113,6 @@ __global__ void __launch_bounds__(32) kshap_lasso_prepare(const uint32_t* __rest
         const double w = (double)sk[m];
         if (!(w > 0.0)) continue;
         cnt += 1.0;
-        if (scale == 2) continue;
         const uint32_t b = sb[m] & varying;
         const double sc = (double)__popc(b);
         const double q = sqrt(w * sc);
@@ -128,7 +127,7 @@ __global__ void __launch_bounds__(32) kshap_lasso_prepare(const uint32_t* __rest
     const double* G0 = gz + (size_t)s * FDB_F * 32;
     const double Bj = bv[(size_t)s * 32 + lane];
     const double S0 = s0[s];
-    const double c = (is_var && scale != 2) ? g[0] - Q : 0.0;                     // scale 2: raw Gram, nothing is centred
+    const double c = is_var ? g[0] - Q : 0.0;
     const double mu = c / n;
     const double ajj = is_var ? Mf * G0[lane * 32 + lane] - 2.0 * Bj + S0 : 0.0;
     const double var = ajj / n - mu * mu;
@@ -150,10 +149,9 @@ __global__ void __launch_bounds__(32) kshap_lasso_prepare(const uint32_t* __rest
         if (lane < FDB_F) lg[((size_t)s * FDB_F + i) * 32 + lane] = v;
     }
     // Gauss-Jordan without pivoting (G is symmetric positive definite for any set the WLS itself can use)
-    bool singular = scale == 2;                                                    // the LAR walk needs no inverse
+    bool singular = false;
 #pragma unroll
     for (int k = 0; k < FDB_F; ++k) {
-        if (singular) break;
         const double pk = shfl_d(a[k], k);
         if (!(fabs(pk) > 1e-300)) { singular = true; break; }
         const double r = 1.0 / pk;
@@ -179,6 +177,19 @@ __global__ void __launch_bounds__(32) kshap_lasso_prepare(const uint32_t* __rest
     V[64 + lane] = lane == 0 ? Q : (lane == 1 ? n : 0.0);
 }
 
+// The Gram matrix the walk reads: stored per set (criteria, alpha: centred / scaled, kshap_lasso_prepare) or, for
+// num_features(k), the raw X_aug'X_aug = M Gz_ij - B_i - B_j + S0 put together on the fly from the Z'WZ products.
+struct GramStored {
+    const double* g;
+    __device__ __forceinline__ double operator()(int i, int j) const { return g[i * 32 + j]; }
+};
+struct GramRaw {
+    const double* gz;
+    const double* bv;
+    double Mf, S0;
+    __device__ __forceinline__ double operator()(int i, int j) const { return Mf * gz[i * 32 + j] - bv[i] - bv[j] + S0; }
+};
+
 struct RowProducts {
     double xy;      // lane j: centred (scaled) X'y of feature j, 0 outside `varying`
     double yy;      // centred y'y
@@ -200,8 +211,8 @@ struct RowProducts {
 //   drop position k: Ainv <- Ainv - c c'/Ainv_kk without row / column k (c = column k); the last position moves into k
 // - every step is a lane-parallel sweep over one row, nothing is sequential across lanes.  tests/lasso_gram_model.py
 // holds both forms (sklearn's factor, this inverse); tests/test_lasso_gram_cpu.py checks both against lars_path.
-template <bool LAR, class SC>
-__device__ int lasso_path(SC& S, const double* __restrict__ G, const RowProducts& R, double n_aug, bool is_var,
+template <bool LAR, class SC, class GM>
+__device__ int lasso_path(SC& S, const GM& G, const RowProducts& R, double n_aug, bool is_var,
                           int n_var, int lane, int max_iter) {
     const double eps = DBL_EPSILON, tiny32 = (double)FLT_MIN, eq_tol = (double)FLT_EPSILON;
     double Cov = is_var ? R.xy : 0.0;
@@ -227,13 +238,13 @@ __device__ int lasso_path(SC& S, const double* __restrict__ G, const RowProducts
         if (n_iter >= max_iter || n_active >= n_var) break;
         if (!drop) {
             const int n = n_active;
-            const double g = lane < n ? G[bidx * 32 + S.act[lane]] : 0.0;
+            const double g = lane < n ? G(bidx, S.act[lane]) : 0.0;
             if (lane < n) S.dinv[lane] = g;                              // dinv[] / ls[] double as broadcast buffers here
             __syncwarp();
             double u = 0.0;
             if (lane < n)
                 for (int a = 0; a < n; ++a) u += S.L[lane][a] * S.dinv[a];
-            const double sres = G[bidx * 32 + bidx] - warp_sum(g * u);
+            const double sres = G(bidx, bidx) - warp_sum(g * u);
             const double diag = fmax(sqrt(fabs(sres)), eps);
             if (diag < 1e-7) {                                           // sklearn: degenerate regressor, zero its Cov and go on
                 if (lane == bidx) Cov = 0.0;
@@ -280,7 +291,7 @@ __device__ int lasso_path(SC& S, const double* __restrict__ G, const RowProducts
         __syncwarp();
         double corr = 0.0;
         if (inactive) {
-            for (int a = 0; a < n; ++a) corr += G[S.act[a] * 32 + lane] * S.ls[a];
+            for (int a = 0; a < n; ++a) corr += G(S.act[a], lane) * S.ls[a];
             corr = rint(corr * 1e15) / 1e15;                             // np.around(..., decimals=15)
         }
         const double g12 = inactive ? fmin(min_pos((C - Cov) / (AA - corr + tiny32)), min_pos((C + Cov) / (AA + corr + tiny32))) : DBL_MAX;
@@ -313,7 +324,7 @@ __device__ int lasso_path(SC& S, const double* __restrict__ G, const RowProducts
         double q = 0.0;
         for (int a = 0; a < n; ++a) {
             const int f = S.act[a];
-            q += G[f * 32 + lane] * shfl_d(coef, f);
+            q += G(f, lane) * shfl_d(coef, f);
         }
         const double rss = R.yy - warp_sum(coef * (2.0 * R.xy - q));
         const uint32_t nz = __ballot_sync(0xffffffffu, fabs(coef) > eps);
@@ -496,13 +507,23 @@ __global__ void __launch_bounds__(128) kshap_lasso_solve(
             R.T = is_var ? gj[0] : 0.0;
         }
         const double E2 = warp_sum(e2), P1 = warp_sum(p1), Tsum = warp_sum(R.T);
-        const double* G = lg + (size_t)s * FDB_F * 32;
-        const double* V = lvec + (size_t)s * kVecStride;
-        const double Bj = bv[(size_t)s * 32 + lane], S0 = s0v[s];
-        const double cj = V[lane], isd = V[32 + lane], Q = V[64], n_aug = V[65];
-        const double ysum = P1 - R.d * Q;
-        R.xy = is_var ? (Mf * R.T - R.d * Bj - Tsum + R.d * S0 - cj * ysum / n_aug) * isd : 0.0;
-        R.yy = Mf * E2 - 2.0 * R.d * Tsum + R.d * R.d * S0 - ysum * ysum / n_aug;
+        const double* Bs = bv + (size_t)s * 32;
+        const double Bj = lane < FDB_F ? Bs[lane] : 0.0, S0 = s0v[s];
+        const double* G = nullptr;
+        double n_aug;
+        if (MODE == 2) {                                            // raw system: nothing centred, nothing scaled
+            n_aug = Bs[31];
+            R.xy = is_var ? Mf * R.T - R.d * Bj - Tsum + R.d * S0 : 0.0;
+            R.yy = 0.0;
+        } else {
+            G = lg + (size_t)s * FDB_F * 32;
+            const double* V = lvec + (size_t)s * kVecStride;
+            const double cj = V[lane], isd = V[32 + lane], Q = V[64];
+            n_aug = V[65];
+            const double ysum = P1 - R.d * Q;
+            R.xy = is_var ? (Mf * R.T - R.d * Bj - Tsum + R.d * S0 - cj * ysum / n_aug) * isd : 0.0;
+            R.yy = Mf * E2 - 2.0 * R.d * Tsum + R.d * R.d * S0 - ysum * ysum / n_aug;
+        }
 
         uint32_t sel;
         if (MODE == 0) {
@@ -511,7 +532,7 @@ __global__ void __launch_bounds__(128) kshap_lasso_solve(
             double u = 0.0;
             for (int i = 0; i < FDB_F; ++i) u += (lane < FDB_F ? Gi[i * 32 + lane] : 0.0) * shfl_d(R.xy, i);
             const double sigma2 = (R.yy - warp_sum(R.xy * u)) / (n_aug - Mf - 1.0);
-            const int n_pts = lasso_path<false>(S, G, R, n_aug, is_var, n_var, lane, kMaxPath);
+            const int n_pts = lasso_path<false>(S, GramStored{G}, R, n_aug, is_var, n_var, lane, kMaxPath);
             __syncwarp();
             const double factor = bic ? log(n_aug) : 2.0;
             double best = DBL_MAX;
@@ -532,7 +553,7 @@ __global__ void __launch_bounds__(128) kshap_lasso_solve(
         } else if (MODE == 1) {
             sel = lasso_cd_support(G, R, alpha_l1 * n_aug, is_var, lane) & varying;
         } else {
-            const int n_act = lasso_path<true>(S, G, R, n_aug, is_var, n_var, lane, kfeat);
+            const int n_act = lasso_path<true>(S, GramRaw{gz + (size_t)s * FDB_F * 32, Bs, Mf, S0}, R, n_aug, is_var, n_var, lane, kfeat);
             __syncwarp();
             sel = 0u;
             for (int a = 0; a < n_act; ++a) sel |= 1u << S.act[a];
@@ -628,8 +649,7 @@ static int launch_prepare(fdb_kshap_plan* p, cudaStream_t st) {
     return FDB_OK;
 }
 
-// scale = 1: unit-variance columns (the StandardScaler step in front of LassoLarsIC); 0: plain centring (Lasso(alpha));
-// 2: the raw Gram (num_features(k): lars_path on the augmented matrix as it is)
+// scale = 1: unit-variance columns (the StandardScaler step in front of LassoLarsIC); 0: plain centring (Lasso(alpha))
 int fdb_kshap_prepare_lasso(fdb_kshap_plan* p, int scale) {
     int rc = fdb_kshap_prepare_lars(p);                       // Z'WZ, B, S0
     if (rc != FDB_OK) return rc;
@@ -675,7 +695,6 @@ int fdb_kshap_launch_lasso_solve(fdb_kshap_plan* p, cudaStream_t st, const float
         FDB_REQUIRE(p->lasso_scaled == 0, FDB_ERR_STATE, "selection products were prepared for another l1 mode");
         kshap_lasso_solve<1><<<grid, 128, 0, st>>>(FDB_LASSO_ARGS(0, p->l1_alpha, 0, nullptr));
     } else if (p->l1_mode == FDB_KSHAP_L1_NUM_FEATURES) {
-        FDB_REQUIRE(p->lasso_scaled == 2, FDB_ERR_STATE, "selection products were prepared for another l1 mode");
         kshap_lasso_solve<2><<<grid, 128, 0, st>>>(FDB_LASSO_ARGS(0, 0.0, p->num_features, gpart));
     } else {
         FDB_REQUIRE(p->lasso_scaled == 1, FDB_ERR_STATE, "selection products were prepared for another l1 mode");
