@@ -12,7 +12,10 @@ if k:
     pr = k["per_row_sets"]
     print(f"Kernel SHAP cfg3 {k['value'] / 1e6:.2f} M rows/s (general {k['general_evaluator']['value'] / 1e6:.2f})  "
           f"cfg4 {k['config4']['value'] / 1e6:.3f} M rows/s ({k['config4']['ms_per_step']:.1f} ms)  "
-          f"per-row stream {pr['value'] / 1e6:.2f} (evaluate only {pr['evaluate_only_value'] / 1e6:.2f}) M rows/s  e2e {k['e2e']['value'] / 1e6:.2f}")
+          f"per-row stream {pr['value'] / 1e6:.2f} (evaluate only {pr['evaluate_only_value'] / 1e6:.2f}, "
+          f"with num_features(10) {pr.get('num_features_10', {}).get('value', float('nan')) / 1e6:.2f}) M rows/s  e2e {k['e2e']['value'] / 1e6:.2f}")
+    if "l1_reg_modes" in k:
+        print("l1_reg modes (shared set)", {n: f"{v['value'] / 1e6:.2f} M rows/s" for n, v in k["l1_reg_modes"].items()})
     r = k["roofline"]
     print("probes", {a: f"{b:.4g}" for a, b in r["probes"].items()})
     print(f"K2  {r['general']['achieved']:.2f} of {r['general']['peak']:.2f} {r['general']['unit']} = {r['general']['frac']:.3f}")
