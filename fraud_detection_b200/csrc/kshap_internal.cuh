@@ -217,14 +217,14 @@ __device__ __forceinline__ bool fdb_kshap_weighted_gram_row_mma(const uint32_t* 
     };
     // one k-step: 16 coalitions (this thread's four: words bw, weights ww) starting at m0; `enumerated` selects which
     // weights count (see above)
-    auto kstep = [&](int m0, bool enumerated, const uint32_t (&bw)[4], const float (&ww)[4]) {
+    auto kstep = [&](int m0, bool enumerated, bool maybe_enum, const uint32_t (&bw)[4], const float (&ww)[4]) {
         uint32_t mb[4];
         float cnt[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const uint32_t v = (word(bw[i]) & ((1u << NF) - 1u)) | (flag(bw[i]) ? (1u << NF) : 0u);
             mb[i] = (v >> g) & 0x01010101u;                  // features g, g + 8, g + 16, g + 24 in bytes 0..3
-            const bool in_enum = has_enum && m0 < 64 && ww[i] == w0;
+            const bool in_enum = maybe_enum && has_enum && m0 < 64 && ww[i] == w0;       // only the first 64 coalitions can be
             if (enumerated) {
                 cnt[i] = in_enum ? 1.0f : 0.0f;
             } else {
@@ -279,19 +279,27 @@ __device__ __forceinline__ bool fdb_kshap_weighted_gram_row_mma(const uint32_t* 
             uint32_t bw[4];
             float ww[4];
             load4(m0, bw, ww);
-            kstep(m0, true, bw, ww);
+            kstep(m0, true, true, bw, ww);
         }
     dump(tile);
     zero_acc();
     // 64 coalitions per trip (m_pad is a multiple of 128): the loads of four k-steps are issued together, ahead of the
     // fragment arithmetic, so a warp keeps 16 loads in flight instead of stalling on four per k-step
-    for (int m1 = 0; m1 < m_pad; m1 += 64) {
+    {
+        uint32_t bw[4][4];
+        float ww[4][4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) load4(16 * q, bw[q], ww[q]);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) kstep(16 * q, false, true, bw[q], ww[q]);
+    }
+    for (int m1 = 64; m1 < m_pad; m1 += 64) {                  // beyond the enumerated block: no per-coalition membership test
         uint32_t bw[4][4];
         float ww[4][4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) load4(m1 + 16 * q, bw[q], ww[q]);
 #pragma unroll
-        for (int q = 0; q < 4; ++q) kstep(m1 + 16 * q, false, bw[q], ww[q]);
+        for (int q = 0; q < 4; ++q) kstep(m1 + 16 * q, false, false, bw[q], ww[q]);
     }
     dump(tile + 32 * 33);
     __syncwarp();
