@@ -158,9 +158,27 @@ __global__ void __launch_bounds__(32) kshap_sample_sets(const SamplerParams p) {
                     s_bits[slot + 1] = full ^ mask;
                     atomicAdd(&s_cnt[(slot + 1) >> 1], 1u << (((slot + 1) & 1) * 16));
                 }
+            }
+            {
+                // Hash insert of this round's new coalitions without a 16-bit atomicCAS (an emulated loop around a 32-bit
+                // CAS: it was a fifth of the kernel's instructions): every inserting lane walks to the first empty slot and
+                // stores its index with a plain 16-bit store; where two lanes picked the same slot one store wins, the
+                // other lane sees a foreign index after the warp barrier and walks on.  One trip in nearly every round.
+                bool pending = is_new && processed;
                 uint32_t h = (mask * 2654435761u) >> kHashShift;
-                while (atomicCAS(&h_slot[h], (unsigned short)0xFFFFu, (unsigned short)slot) != 0xFFFFu)
-                    h = (h + 1) & (kHashSlots - 1);
+                volatile unsigned short* hs = h_slot;
+                while (__any_sync(allw, pending)) {
+                    if (pending) {
+                        while (hs[h] != 0xFFFFu) h = (h + 1) & (kHashSlots - 1);
+                        hs[h] = (unsigned short)slot;
+                    }
+                    __syncwarp();
+                    if (pending) {
+                        if (hs[h] == (unsigned short)slot) pending = false;
+                        else h = (h + 1) & (kHashSlots - 1);
+                    }
+                    __syncwarp();
+                }
             }
             slot = __shfl_sync(allw, slot, leader);                                      // merged proposals follow their leader
             __syncwarp();
