@@ -22,7 +22,7 @@
 namespace {
 
 // Per coalition set: Gz = Z'WZ (30 x 30, row stride 32), B_j = sum kw s z_j, S0 = sum kw s.  One warp per set.
-__global__ void __launch_bounds__(32) kshap_gram_prepare(const uint32_t* __restrict__ bits, const float* __restrict__ kw,
+__global__ void __launch_bounds__(32, 16) kshap_gram_prepare(const uint32_t* __restrict__ bits, const float* __restrict__ kw,
                                                          int m_pad, double* __restrict__ gz, double* __restrict__ bv,
                                                          double* __restrict__ s0, uint32_t varying) {
     const int s = blockIdx.x, lane = threadIdx.x;
